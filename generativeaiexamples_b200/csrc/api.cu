@@ -1,0 +1,677 @@
+// C ABI of libb200r.so (see include/b200r.h for the reference call each entry
+// point replaces).  Host-side runtime: HBM corpus buffer, pinned staging rings,
+// per-index search workspace, error plumbing.  No CPU compute path exists here.
+#include "../../include/b200r.h"
+#include "common.cuh"
+#include "kernels.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+using namespace b200r;
+
+// ---------------------------------------------------------------------------
+// errors
+// ---------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e__ = (call);                                                                    \
+        if (e__ != cudaSuccess)                                                                      \
+            return fail(e__ == cudaErrorMemoryAllocation ? B200R_E_NOMEM : B200R_E_CUDA, "%s: %s (%s:%d)", #call, \
+                        cudaGetErrorString(e__), __FILE__, __LINE__);                                \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+// ---------------------------------------------------------------------------
+// the index
+// ---------------------------------------------------------------------------
+constexpr size_t kStageHalfBytes = 32u << 20;  // pinned / device staging, per half
+constexpr int64_t kMaxRows = 0xFFFFFFFEll;     // ids are 32-bit inside the kernels
+
+struct b200r_index {
+    b200r_config cfg{};
+    int d = 0, d_pad = 0, row_bytes = 0;
+    bool bf16 = false, l2 = false;
+    int device = 0, num_sms = 0;
+    size_t smem_optin = 0;
+
+    uint8_t* rows = nullptr;  // [capacity][row_bytes]
+    float* norms = nullptr;   // [capacity] squared norms of the stored rows
+    int64_t ntotal = 0, capacity = 0;
+
+    cudaStream_t stream = nullptr;  // the index's own stream
+    // add(): double-buffered host->device staging
+    uint8_t* pin_add = nullptr;
+    uint8_t* dev_add = nullptr;
+    cudaEvent_t add_ev[2] = {nullptr, nullptr};
+    // search(): workspace
+    float* q_pin = nullptr;
+    float* q_raw = nullptr;   // device, as given
+    float* q_dev = nullptr;   // device, padded / normalised
+    int64_t q_cap = 0;        // query slots allocated
+    Cand* scratch = nullptr;
+    unsigned* counter = nullptr;
+    float* out_d = nullptr;
+    int64_t* out_i = nullptr;
+    uint8_t* out_pin = nullptr;
+    int64_t out_cap = 0;  // nq*k entries allocated
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
+    bool timing = false;
+
+    std::mutex mu;
+    b200r_stats st{};
+};
+
+static int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+static int ensure_capacity(b200r_index* ix, int64_t need, cudaStream_t st) {
+    if (need <= ix->capacity) return B200R_OK;
+    if (need > kMaxRows) return fail(B200R_E_UNSUPPORTED, "index is limited to %lld rows per GPU", (long long)kMaxRows);
+    int64_t cap = std::max<int64_t>(need, ix->capacity + ix->capacity / 2);
+    cap = std::max<int64_t>(cap, 1024);
+    uint8_t* nr = nullptr;
+    float* nn = nullptr;
+    cudaError_t e = cudaMalloc(&nr, (size_t)cap * ix->row_bytes);
+    if (e != cudaSuccess && cap > need) {  // retry without head-room
+        cudaGetLastError();
+        cap = need;
+        e = cudaMalloc(&nr, (size_t)cap * ix->row_bytes);
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(B200R_E_NOMEM, "cudaMalloc of %.2f GB for %lld rows failed: %s", cap * (double)ix->row_bytes / 1e9,
+                    (long long)cap, cudaGetErrorString(e));
+    }
+    e = cudaMalloc(&nn, (size_t)cap * sizeof(float));
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(nr);
+        return fail(B200R_E_NOMEM, "cudaMalloc of row norms failed: %s", cudaGetErrorString(e));
+    }
+    if (ix->ntotal > 0) {
+        CU(cudaMemcpyAsync(nr, ix->rows, (size_t)ix->ntotal * ix->row_bytes, cudaMemcpyDeviceToDevice, st));
+        CU(cudaMemcpyAsync(nn, ix->norms, (size_t)ix->ntotal * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    }
+    CU(cudaStreamSynchronize(st));
+    if (ix->rows) cudaFree(ix->rows);
+    if (ix->norms) cudaFree(ix->norms);
+    ix->rows = nr;
+    ix->norms = nn;
+    ix->capacity = cap;
+    return B200R_OK;
+}
+
+static void free_index(b200r_index* ix) {
+    if (!ix) return;
+    DeviceGuard g(ix->device);
+    if (ix->stream) cudaStreamSynchronize(ix->stream);
+    cudaFree(ix->rows);
+    cudaFree(ix->norms);
+    cudaFreeHost(ix->pin_add);
+    cudaFree(ix->dev_add);
+    cudaFreeHost(ix->q_pin);
+    cudaFree(ix->q_raw);
+    cudaFree(ix->q_dev);
+    cudaFree(ix->scratch);
+    cudaFree(ix->counter);
+    cudaFree(ix->out_d);
+    cudaFree(ix->out_i);
+    cudaFreeHost(ix->out_pin);
+    for (auto& e : ix->add_ev)
+        if (e) cudaEventDestroy(e);
+    if (ix->t0) cudaEventDestroy(ix->t0);
+    if (ix->t1) cudaEventDestroy(ix->t1);
+    if (ix->stream) cudaStreamDestroy(ix->stream);
+    cudaGetLastError();
+    delete ix;
+}
+
+extern "C" int b200r_version(void) { return B200R_VERSION; }
+extern "C" const char* b200r_last_error(void) { return g_err.c_str(); }
+
+extern "C" int b200r_create(const b200r_config* cfg, b200r_index** out) {
+    if (!cfg || !out) return fail(B200R_E_INVALID, "b200r_create: null argument");
+    *out = nullptr;
+    if (cfg->dim <= 0) return fail(B200R_E_INVALID, "dim must be positive, got %d", cfg->dim);
+    if (cfg->metric != B200R_METRIC_INNER_PRODUCT && cfg->metric != B200R_METRIC_L2)
+        return fail(B200R_E_INVALID, "metric must be B200R_METRIC_INNER_PRODUCT or B200R_METRIC_L2");
+    if (cfg->storage != B200R_F32 && cfg->storage != B200R_BF16)
+        return fail(B200R_E_INVALID, "storage must be B200R_F32 or B200R_BF16");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(B200R_E_CUDA, "no CUDA device available (%s); libb200r has no CPU path",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    }
+    if (cfg->device < 0 || cfg->device >= ndev)
+        return fail(B200R_E_INVALID, "device %d out of range (%d visible)", cfg->device, ndev);
+    DeviceGuard g(cfg->device);
+    if (!g.ok) return fail(B200R_E_CUDA, "cudaSetDevice(%d) failed", cfg->device);
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10)
+        return fail(B200R_E_UNSUPPORTED, "device %d is sm_%d%d; libb200r is built for sm_100a (B200) only", cfg->device,
+                    prop.major, prop.minor);
+
+    b200r_index* ix = new b200r_index();
+    ix->cfg = *cfg;
+    ix->d = cfg->dim;
+    ix->bf16 = cfg->storage == B200R_BF16;
+    ix->l2 = cfg->metric == B200R_METRIC_L2;
+    ix->d_pad = (int)round_up(cfg->dim, ix->bf16 ? 8 : 4);
+    ix->row_bytes = ix->d_pad * (ix->bf16 ? 2 : 4);
+    ix->device = cfg->device;
+    ix->num_sms = prop.multiProcessorCount;
+    ix->smem_optin = prop.sharedMemPerBlockOptin;
+    ix->st.num_sms = ix->num_sms;
+    if (ix->row_bytes > 64 * 1024) {
+        delete ix;
+        return fail(B200R_E_UNSUPPORTED, "dim %d too large: a row must fit 64 KB", cfg->dim);
+    }
+#define CU_OR_FREE(call)                                                                          \
+    do {                                                                                          \
+        cudaError_t e__ = (call);                                                                 \
+        if (e__ != cudaSuccess) {                                                                 \
+            free_index(ix);                                                                       \
+            cudaGetLastError();                                                                   \
+            return fail(e__ == cudaErrorMemoryAllocation ? B200R_E_NOMEM : B200R_E_CUDA, "%s: %s", #call, \
+                        cudaGetErrorString(e__));                                                 \
+        }                                                                                         \
+    } while (0)
+    CU_OR_FREE(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
+    CU_OR_FREE(cudaEventCreateWithFlags(&ix->add_ev[0], cudaEventDisableTiming));
+    CU_OR_FREE(cudaEventCreateWithFlags(&ix->add_ev[1], cudaEventDisableTiming));
+    CU_OR_FREE(cudaEventCreate(&ix->t0));
+    CU_OR_FREE(cudaEventCreate(&ix->t1));
+    CU_OR_FREE(cudaMalloc(&ix->scratch, scan_scratch_bytes(ix->num_sms)));
+    CU_OR_FREE(cudaMalloc(&ix->counter, 256));
+    CU_OR_FREE(cudaMemset(ix->counter, 0, 256));
+#undef CU_OR_FREE
+    if (cfg->reserve_rows > 0) {
+        int rc = ensure_capacity(ix, cfg->reserve_rows, ix->stream);
+        if (rc != B200R_OK) {
+            free_index(ix);
+            return rc;
+        }
+    }
+    *out = ix;
+    return B200R_OK;
+}
+
+extern "C" int b200r_destroy(b200r_index* ix) {
+    free_index(ix);
+    return B200R_OK;
+}
+
+extern "C" int b200r_ntotal(const b200r_index* ix, int64_t* out) {
+    if (!ix || !out) return fail(B200R_E_INVALID, "b200r_ntotal: null argument");
+    *out = ix->ntotal;
+    return B200R_OK;
+}
+
+extern "C" int b200r_set_id_base(b200r_index* ix, int64_t id_base) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_set_id_base: null index");
+    std::lock_guard<std::mutex> lk(ix->mu);
+    ix->cfg.id_base = id_base;
+    return B200R_OK;
+}
+
+extern "C" int b200r_set_timing(b200r_index* ix, int32_t enabled) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_set_timing: null index");
+    ix->timing = enabled != 0;
+    return B200R_OK;
+}
+
+extern "C" int b200r_stats_get(b200r_index* ix, b200r_stats* out) {
+    if (!ix || !out) return fail(B200R_E_INVALID, "b200r_stats_get: null argument");
+    std::lock_guard<std::mutex> lk(ix->mu);
+    ix->st.ntotal = ix->ntotal;
+    ix->st.capacity_rows = ix->capacity;
+    *out = ix->st;
+    return B200R_OK;
+}
+
+extern "C" int b200r_reset(b200r_index* ix) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_reset: null index");
+    std::lock_guard<std::mutex> lk(ix->mu);
+    ix->ntotal = 0;
+    return B200R_OK;
+}
+
+// ---------------------------------------------------------------------------
+// add
+// ---------------------------------------------------------------------------
+extern "C" int b200r_add(b200r_index* ix, const void* x, int64_t n, int dtype, int mem_kind, void* stream) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_add: null index");
+    if (n < 0) return fail(B200R_E_INVALID, "b200r_add: n = %lld", (long long)n);
+    if (n == 0) return B200R_OK;
+    if (!x) return fail(B200R_E_INVALID, "b200r_add: null data");
+    if (dtype != B200R_F32) return fail(B200R_E_UNSUPPORTED, "b200r_add: input vectors must be fp32");
+    if (mem_kind != B200R_HOST && mem_kind != B200R_DEVICE) return fail(B200R_E_INVALID, "b200r_add: bad mem_kind");
+    std::lock_guard<std::mutex> lk(ix->mu);
+    DeviceGuard g(ix->device);
+    cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
+    int rc = ensure_capacity(ix, ix->ntotal + n, st);
+    if (rc != B200R_OK) return rc;
+    const bool norm = ix->cfg.normalize_on_add != 0;
+    uint8_t* dst = ix->rows + (size_t)ix->ntotal * ix->row_bytes;
+    float* dstn = ix->norms + ix->ntotal;
+    if (mem_kind == B200R_DEVICE) {
+        CU(launch_ingest((const float*)x, n, ix->d, ix->d_pad, norm, ix->bf16, dst, dstn, st));
+        ix->st.n_kernel_launches++;
+    } else {
+        if (!ix->pin_add) {
+            CU(cudaMallocHost(&ix->pin_add, 2 * kStageHalfBytes));
+            CU(cudaMalloc(&ix->dev_add, 2 * kStageHalfBytes));
+        }
+        const size_t in_row = (size_t)ix->d * sizeof(float);
+        const int64_t chunk = std::max<int64_t>(1, (int64_t)(kStageHalfBytes / in_row));
+        int half = 0;
+        bool used[2] = {false, false};
+        for (int64_t r0 = 0; r0 < n; r0 += chunk, half ^= 1) {
+            const int64_t m = std::min(chunk, n - r0);
+            if (used[half]) CU(cudaEventSynchronize(ix->add_ev[half]));
+            uint8_t* ph = ix->pin_add + half * kStageHalfBytes;
+            uint8_t* dh = ix->dev_add + half * kStageHalfBytes;
+            memcpy(ph, (const uint8_t*)x + (size_t)r0 * in_row, (size_t)m * in_row);
+            CU(cudaMemcpyAsync(dh, ph, (size_t)m * in_row, cudaMemcpyHostToDevice, st));
+            CU(launch_ingest((const float*)dh, m, ix->d, ix->d_pad, norm, ix->bf16, dst + (size_t)r0 * ix->row_bytes,
+                             dstn + r0, st));
+            CU(cudaEventRecord(ix->add_ev[half], st));
+            used[half] = true;
+            ix->st.n_kernel_launches++;
+        }
+        CU(cudaStreamSynchronize(st));
+    }
+    ix->ntotal += n;
+    ix->st.n_rows_added += n;
+    return B200R_OK;
+}
+
+// ---------------------------------------------------------------------------
+// search
+// ---------------------------------------------------------------------------
+static int ensure_search_ws(b200r_index* ix, int64_t nq_slots, int64_t nq, int k) {
+    if (nq_slots > ix->q_cap) {
+        cudaFreeHost(ix->q_pin);
+        cudaFree(ix->q_raw);
+        cudaFree(ix->q_dev);
+        ix->q_pin = ix->q_raw = ix->q_dev = nullptr;
+        ix->q_cap = 0;
+        const int64_t cap = std::max<int64_t>(nq_slots, 64);
+        CU(cudaMallocHost(&ix->q_pin, (size_t)cap * ix->d * sizeof(float)));
+        CU(cudaMalloc(&ix->q_raw, (size_t)cap * ix->d * sizeof(float)));
+        CU(cudaMalloc(&ix->q_dev, (size_t)cap * ix->d_pad * sizeof(float)));
+        ix->q_cap = cap;
+    }
+    const int64_t need = nq * k;
+    if (need > ix->out_cap) {
+        cudaFree(ix->out_d);
+        cudaFree(ix->out_i);
+        cudaFreeHost(ix->out_pin);
+        ix->out_d = nullptr;
+        ix->out_i = nullptr;
+        ix->out_pin = nullptr;
+        ix->out_cap = 0;
+        const int64_t cap = std::max<int64_t>(need, 4096);
+        CU(cudaMalloc(&ix->out_d, (size_t)cap * sizeof(float)));
+        CU(cudaMalloc(&ix->out_i, (size_t)cap * sizeof(int64_t)));
+        CU(cudaMallocHost(&ix->out_pin, (size_t)cap * (sizeof(float) + sizeof(int64_t)) + 64));
+        ix->out_cap = cap;
+    }
+    return B200R_OK;
+}
+
+extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
+                            int out_mem_kind, void* stream) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_search: null index");
+    if (nq < 0) return fail(B200R_E_INVALID, "b200r_search: nq = %lld", (long long)nq);
+    if (k <= 0) return fail(B200R_E_INVALID, "b200r_search: k must be > 0, got %d", k);  // faiss: assert k > 0
+    if (nq == 0) return B200R_OK;
+    if (!q || !D || !I) return fail(B200R_E_INVALID, "b200r_search: null buffer");
+    if ((q_mem_kind != B200R_HOST && q_mem_kind != B200R_DEVICE) ||
+        (out_mem_kind != B200R_HOST && out_mem_kind != B200R_DEVICE))
+        return fail(B200R_E_INVALID, "b200r_search: bad mem_kind");
+    if (k > kScanMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_search: k = %d exceeds the supported maximum %d", k, kScanMaxK);
+    if (ix->cfg.search_path == B200R_PATH_GEMM)
+        return fail(B200R_E_UNSUPPORTED, "b200r_search: the GEMM path is not built in this version");
+
+    std::lock_guard<std::mutex> lk(ix->mu);
+    DeviceGuard g(ix->device);
+    cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
+    const int64_t nq_slots = round_up(nq, kScanMaxNQ);
+    int rc = ensure_search_ws(ix, nq_slots, nq, k);
+    if (rc != B200R_OK) return rc;
+
+    if (ix->timing) CU(cudaEventRecord(ix->t0, st));
+    const float* q_src = (const float*)q;
+    if (q_mem_kind == B200R_HOST) {
+        memcpy(ix->q_pin, q, (size_t)nq * ix->d * sizeof(float));
+        CU(cudaMemcpyAsync(ix->q_raw, ix->q_pin, (size_t)nq * ix->d * sizeof(float), cudaMemcpyHostToDevice, st));
+        q_src = ix->q_raw;
+    }
+    CU(launch_prep_queries(q_src, nq, ix->d, ix->d_pad, nq_slots, ix->cfg.normalize_queries != 0, ix->q_dev, st));
+    ix->st.n_kernel_launches++;
+
+    float* od = out_mem_kind == B200R_DEVICE ? D : ix->out_d;
+    int64_t* oi = out_mem_kind == B200R_DEVICE ? I : ix->out_i;
+
+    ScanParams p{};
+    p.corpus = ix->rows;
+    p.n_rows = ix->ntotal;
+    p.d = ix->d_pad;
+    p.row_bytes = ix->row_bytes;
+    p.k = k;
+    p.evict_first = ((size_t)ix->ntotal * ix->row_bytes > (size_t)96 << 20) ? 1 : 0;
+    p.scratch = ix->scratch;
+    p.counter = ix->counter;
+    p.id_base = ix->cfg.id_base;
+    for (int64_t q0 = 0; q0 < nq; q0 += kScanMaxNQ) {
+        const int nqg = (int)std::min<int64_t>(kScanMaxNQ, nq - q0);
+        p.q = ix->q_dev + (size_t)q0 * ix->d_pad;
+        p.out_d = od + (size_t)q0 * k;
+        p.out_i = oi + (size_t)q0 * k;
+        int grid = 0;
+        CU(launch_scan(p, nqg, ix->l2, ix->bf16, ix->num_sms, ix->smem_optin, st, &grid));
+        ix->st.n_kernel_launches++;
+        ix->st.last_grid = grid;
+        ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
+    }
+    ix->st.last_path = B200R_PATH_SCAN;
+    if (ix->timing) CU(cudaEventRecord(ix->t1, st));
+
+    if (out_mem_kind == B200R_HOST) {
+        float* pd = (float*)ix->out_pin;
+        int64_t* pi = (int64_t*)(ix->out_pin + round_up((size_t)nq * k * sizeof(float), 16));
+        // out_pin holds cap*(4+8)+64 bytes, so the 16-byte rounding always fits
+        CU(cudaMemcpyAsync(pd, ix->out_d, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(pi, ix->out_i, (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        memcpy(D, pd, (size_t)nq * k * sizeof(float));
+        memcpy(I, pi, (size_t)nq * k * sizeof(int64_t));
+    }
+    if (ix->timing) {
+        CU(cudaEventSynchronize(ix->t1));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, ix->t0, ix->t1));
+        ix->st.last_search_ms = ms;
+    }
+    ix->st.n_search_calls++;
+    ix->st.n_queries += nq;
+    return B200R_OK;
+}
+
+// ---------------------------------------------------------------------------
+// remove_ids / reconstruct
+// ---------------------------------------------------------------------------
+extern "C" int b200r_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, int64_t* n_removed) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_remove_ids: null index");
+    if (n < 0 || (n > 0 && !ids)) return fail(B200R_E_INVALID, "b200r_remove_ids: bad ids");
+    if (n_removed) *n_removed = 0;
+    std::lock_guard<std::mutex> lk(ix->mu);
+    std::vector<int64_t> del;
+    del.reserve((size_t)n);
+    for (int64_t i = 0; i < n; i++)
+        if (ids[i] >= 0 && ids[i] < ix->ntotal) del.push_back(ids[i]);
+    std::sort(del.begin(), del.end());
+    del.erase(std::unique(del.begin(), del.end()), del.end());
+    const int64_t m = (int64_t)del.size();
+    if (m == 0) return B200R_OK;
+    const int64_t new_total = ix->ntotal - m;
+    const int64_t first = del[0];  // rows before it stay where they are
+    std::vector<int64_t> adj((size_t)m);
+    for (int64_t i = 0; i < m; i++) adj[(size_t)i] = del[(size_t)i] - i;
+
+    DeviceGuard g(ix->device);
+    cudaStream_t st = ix->stream;
+    int64_t* adj_dev = nullptr;
+    uint8_t* bounce = nullptr;
+    const int64_t chunk_rows = std::max<int64_t>(1, (int64_t)((64u << 20) / ix->row_bytes));
+    CU(cudaMalloc(&adj_dev, (size_t)m * sizeof(int64_t)));
+    cudaError_t e = cudaMalloc(&bounce, (size_t)chunk_rows * ix->row_bytes);
+    if (e != cudaSuccess) {
+        cudaFree(adj_dev);
+        cudaGetLastError();
+        return fail(B200R_E_NOMEM, "b200r_remove_ids: bounce buffer: %s", cudaGetErrorString(e));
+    }
+    int rc = B200R_OK;
+    auto body = [&]() -> int {
+        CU(cudaMemcpyAsync(adj_dev, adj.data(), (size_t)m * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+        for (int64_t o0 = first; o0 < new_total; o0 += chunk_rows) {
+            const int64_t o1 = std::min(new_total, o0 + chunk_rows);
+            // rows: gather the survivors of this output range, then put them in place.
+            // Sources of later ranges lie above o1, so they are still intact.
+            CU(launch_gather_rows(ix->rows, bounce, o0, o1, ix->row_bytes, adj_dev, m, st));
+            CU(cudaMemcpyAsync(ix->rows + (size_t)o0 * ix->row_bytes, bounce, (size_t)(o1 - o0) * ix->row_bytes,
+                               cudaMemcpyDeviceToDevice, st));
+            CU(launch_gather_rows(ix->norms, bounce, o0, o1, (int)sizeof(float), adj_dev, m, st));
+            CU(cudaMemcpyAsync(ix->norms + o0, bounce, (size_t)(o1 - o0) * sizeof(float), cudaMemcpyDeviceToDevice, st));
+            ix->st.n_kernel_launches += 2;
+        }
+        CU(cudaStreamSynchronize(st));
+        return B200R_OK;
+    };
+    rc = body();
+    cudaFree(adj_dev);
+    cudaFree(bounce);
+    if (rc != B200R_OK) return rc;
+    ix->ntotal = new_total;
+    ix->st.n_rows_removed += m;
+    if (n_removed) *n_removed = m;
+    return B200R_OK;
+}
+
+extern "C" int b200r_reconstruct(b200r_index* ix, int64_t key, float* out) {
+    if (!ix || !out) return fail(B200R_E_INVALID, "b200r_reconstruct: null argument");
+    std::lock_guard<std::mutex> lk(ix->mu);
+    if (key < 0 || key >= ix->ntotal)
+        return fail(B200R_E_INVALID, "b200r_reconstruct: key %lld out of range [0, %lld)", (long long)key,
+                    (long long)ix->ntotal);
+    DeviceGuard g(ix->device);
+    float* tmp = nullptr;
+    CU(cudaMalloc(&tmp, (size_t)ix->d * sizeof(float)));
+    cudaError_t e = launch_row_to_f32(ix->rows + (size_t)key * ix->row_bytes, ix->d, ix->bf16, tmp, ix->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, tmp, (size_t)ix->d * sizeof(float), cudaMemcpyDeviceToHost, ix->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ix->stream);
+    cudaFree(tmp);
+    ix->st.n_kernel_launches++;
+    if (e != cudaSuccess) return fail(B200R_E_CUDA, "b200r_reconstruct: %s", cudaGetErrorString(e));
+    return B200R_OK;
+}
+
+// ---------------------------------------------------------------------------
+// stand-alone normalise and merge
+// ---------------------------------------------------------------------------
+extern "C" int b200r_normalize_l2(float* x, int64_t n, int32_t d, int mem_kind, int32_t device, void* stream) {
+    if (n < 0 || d <= 0) return fail(B200R_E_INVALID, "b200r_normalize_l2: bad shape");
+    if (n == 0) return B200R_OK;
+    if (!x) return fail(B200R_E_INVALID, "b200r_normalize_l2: null data");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(B200R_E_CUDA, "cudaSetDevice(%d) failed", device);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (mem_kind == B200R_DEVICE) {
+        CU(launch_normalize(x, n, d, st));
+        return B200R_OK;
+    }
+    if (mem_kind != B200R_HOST) return fail(B200R_E_INVALID, "b200r_normalize_l2: bad mem_kind");
+    const size_t row = (size_t)d * sizeof(float);
+    const int64_t chunk = std::max<int64_t>(1, (int64_t)((64u << 20) / row));
+    float* dev = nullptr;
+    CU(cudaMalloc(&dev, (size_t)std::min(chunk, n) * row));
+    cudaError_t e = cudaSuccess;
+    for (int64_t r0 = 0; r0 < n && e == cudaSuccess; r0 += chunk) {
+        const int64_t m = std::min(chunk, n - r0);
+        e = cudaMemcpyAsync(dev, x + r0 * d, (size_t)m * row, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = launch_normalize(dev, m, d, st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(x + r0 * d, dev, (size_t)m * row, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    }
+    cudaFree(dev);
+    if (e != cudaSuccess) return fail(B200R_E_CUDA, "b200r_normalize_l2: %s", cudaGetErrorString(e));
+    return B200R_OK;
+}
+
+extern "C" int b200r_merge_topk(int32_t metric, const float* cand_D, const int64_t* cand_I, int64_t nq, int32_t n_lists,
+                                int32_t k_in, int64_t stride_D, int64_t stride_I, int32_t k_out, float* D, int64_t* I,
+                                int32_t device, void* stream) {
+    if (metric != B200R_METRIC_INNER_PRODUCT && metric != B200R_METRIC_L2)
+        return fail(B200R_E_INVALID, "b200r_merge_topk: bad metric");
+    if (nq < 0 || n_lists < 1 || k_in < 1 || k_out < 1 || stride_D < 0 || stride_I < 0)
+        return fail(B200R_E_INVALID, "b200r_merge_topk: bad shape");
+    if (k_out > kScanMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_merge_topk: k_out %d > %d", k_out, kScanMaxK);
+    if (nq == 0) return B200R_OK;
+    if (!cand_D || !cand_I || !D || !I) return fail(B200R_E_INVALID, "b200r_merge_topk: null buffer");
+    DeviceGuard g(device);
+    if (!g.ok) return fail(B200R_E_CUDA, "cudaSetDevice(%d) failed", device);
+    CU(launch_merge(metric == B200R_METRIC_L2, cand_D, cand_I, nq, n_lists, k_in, stride_D, stride_I, k_out, D, I,
+                    (cudaStream_t)stream));
+    return B200R_OK;
+}
+
+// ---------------------------------------------------------------------------
+// save / load: faiss flat-index file ("IxF2" / "IxFI"), fp32 payload
+//   u32 fourcc | i32 d | i64 ntotal | i64 dummy(1<<20) x2 | u8 is_trained | i32 metric |
+//   u64 n_floats | fp32 data          (faiss/impl/index_write.cpp write_index_header +
+//   WRITEXBVECTOR(codes))
+// ---------------------------------------------------------------------------
+static uint32_t fourcc(const char* s) {
+    return (uint32_t)(uint8_t)s[0] | ((uint32_t)(uint8_t)s[1] << 8) | ((uint32_t)(uint8_t)s[2] << 16) |
+           ((uint32_t)(uint8_t)s[3] << 24);
+}
+
+extern "C" int b200r_save(b200r_index* ix, const char* path) {
+    if (!ix || !path) return fail(B200R_E_INVALID, "b200r_save: null argument");
+    std::lock_guard<std::mutex> lk(ix->mu);
+    DeviceGuard g(ix->device);
+    FILE* f = fopen(path, "wb");
+    if (!f) return fail(B200R_E_IO, "b200r_save: cannot open %s", path);
+    const uint32_t h = fourcc(ix->l2 ? "IxF2" : "IxFI");
+    const int32_t d = ix->d;
+    const int64_t nt = ix->ntotal, dummy = 1 << 20;
+    const uint8_t trained = 1;
+    const int32_t metric = ix->cfg.metric;
+    const uint64_t nfloats = (uint64_t)nt * (uint64_t)d;
+    bool ok = fwrite(&h, 4, 1, f) == 1 && fwrite(&d, 4, 1, f) == 1 && fwrite(&nt, 8, 1, f) == 1 &&
+              fwrite(&dummy, 8, 1, f) == 1 && fwrite(&dummy, 8, 1, f) == 1 && fwrite(&trained, 1, 1, f) == 1 &&
+              fwrite(&metric, 4, 1, f) == 1 && fwrite(&nfloats, 8, 1, f) == 1;
+    // rows go out as fp32 without the padding columns, in bounded chunks
+    const int64_t chunk = std::max<int64_t>(1, (int64_t)((32u << 20) / ((size_t)d * 4)));
+    float* dev = nullptr;
+    float* host = nullptr;
+    cudaError_t e = cudaMalloc(&dev, (size_t)chunk * d * 4);
+    if (e == cudaSuccess) e = cudaMallocHost(&host, (size_t)chunk * d * 4);
+    for (int64_t r0 = 0; ok && e == cudaSuccess && r0 < nt; r0 += chunk) {
+        const int64_t m = std::min(chunk, nt - r0);
+        if (!ix->bf16 && ix->d_pad == ix->d) {
+            e = cudaMemcpyAsync(host, ix->rows + (size_t)r0 * ix->row_bytes, (size_t)m * d * 4, cudaMemcpyDeviceToHost,
+                                ix->stream);
+        } else {
+            for (int64_t r = 0; r < m && e == cudaSuccess; r++)
+                e = launch_row_to_f32(ix->rows + (size_t)(r0 + r) * ix->row_bytes, d, ix->bf16, dev + r * d, ix->stream);
+            if (e == cudaSuccess)
+                e = cudaMemcpyAsync(host, dev, (size_t)m * d * 4, cudaMemcpyDeviceToHost, ix->stream);
+        }
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ix->stream);
+        if (e == cudaSuccess) ok = fwrite(host, (size_t)d * 4, (size_t)m, f) == (size_t)m;
+    }
+    cudaFree(dev);
+    cudaFreeHost(host);
+    ok = (fclose(f) == 0) && ok;
+    if (e != cudaSuccess) return fail(B200R_E_CUDA, "b200r_save: %s", cudaGetErrorString(e));
+    if (!ok) return fail(B200R_E_IO, "b200r_save: write to %s failed", path);
+    return B200R_OK;
+}
+
+extern "C" int b200r_load(const char* path, const b200r_config* cfg, b200r_index** out) {
+    if (!path || !cfg || !out) return fail(B200R_E_INVALID, "b200r_load: null argument");
+    *out = nullptr;
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(B200R_E_IO, "b200r_load: cannot open %s", path);
+    uint32_t h = 0;
+    int32_t d = 0, metric = 0;
+    int64_t nt = 0, dummy = 0;
+    uint8_t trained = 0;
+    uint64_t nfloats = 0;
+    bool ok = fread(&h, 4, 1, f) == 1 && fread(&d, 4, 1, f) == 1 && fread(&nt, 8, 1, f) == 1 &&
+              fread(&dummy, 8, 1, f) == 1 && fread(&dummy, 8, 1, f) == 1 && fread(&trained, 1, 1, f) == 1 &&
+              fread(&metric, 4, 1, f) == 1;
+    if (ok && metric > 1) {
+        float metric_arg;
+        ok = fread(&metric_arg, 4, 1, f) == 1;
+    }
+    ok = ok && fread(&nfloats, 8, 1, f) == 1;
+    if (!ok || (h != fourcc("IxF2") && h != fourcc("IxFI") && h != fourcc("IxFl"))) {
+        fclose(f);
+        return fail(B200R_E_IO, "b200r_load: %s is not a faiss flat index file", path);
+    }
+    if (metric != B200R_METRIC_INNER_PRODUCT && metric != B200R_METRIC_L2) {
+        fclose(f);
+        return fail(B200R_E_UNSUPPORTED, "b200r_load: metric type %d is not supported", metric);
+    }
+    if (d <= 0 || nt < 0 || nfloats != (uint64_t)nt * (uint64_t)d) {
+        fclose(f);
+        return fail(B200R_E_IO, "b200r_load: inconsistent header in %s", path);
+    }
+    b200r_config c = *cfg;
+    c.dim = d;
+    c.metric = metric;
+    c.reserve_rows = std::max<int64_t>(c.reserve_rows, nt);
+    const int norm_on_add = c.normalize_on_add;
+    c.normalize_on_add = 0;  // stored rows are loaded verbatim
+    b200r_index* ix = nullptr;
+    int rc = b200r_create(&c, &ix);
+    if (rc != B200R_OK) {
+        fclose(f);
+        return rc;
+    }
+    const int64_t chunk = std::max<int64_t>(1, (int64_t)((32u << 20) / ((size_t)d * 4)));
+    std::vector<float> buf((size_t)std::min<int64_t>(chunk, std::max<int64_t>(nt, 1)) * d);
+    for (int64_t r0 = 0; r0 < nt; r0 += chunk) {
+        const int64_t m = std::min(chunk, nt - r0);
+        if (fread(buf.data(), (size_t)d * 4, (size_t)m, f) != (size_t)m) {
+            fclose(f);
+            free_index(ix);
+            return fail(B200R_E_IO, "b200r_load: %s is truncated", path);
+        }
+        rc = b200r_add(ix, buf.data(), m, B200R_F32, B200R_HOST, nullptr);
+        if (rc != B200R_OK) {
+            fclose(f);
+            free_index(ix);
+            return rc;
+        }
+    }
+    fclose(f);
+    ix->cfg.normalize_on_add = norm_on_add;
+    ix->st.n_rows_added = 0;
+    *out = ix;
+    return B200R_OK;
+}

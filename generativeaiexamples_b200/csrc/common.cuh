@@ -1,0 +1,249 @@
+// Shared device/host helpers for libb200r (sm_100a only).
+//
+// Nothing here has a counterpart in the reference: the reference's search step is
+// faiss-cpu's IndexFlat::search (see include/b200r.h for the call sites).  The
+// candidate lists below implement the same *selection* as faiss's binary heap
+// (faiss/utils/Heap.h) -- keep the k best, replace only on improvement -- but as
+// warp-distributed sorted lists so that the score matrix never leaves the SM.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <float.h>
+
+namespace b200r {
+
+constexpr uint32_t kEmptyId = 0xFFFFFFFFu;
+
+// ---------------------------------------------------------------------------
+// PTX wrappers: mbarrier + 1-D bulk async copy (TMA engine, SASS UBLKCP)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+
+__device__ __forceinline__ void fence_mbar_init() {
+    // make the inits visible to the async proxy (TMA) before first use
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void fence_proxy_async() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(
+                     smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+
+// global -> shared bulk copy; completes `bytes` on `bar`.  src, dst and bytes
+// must be multiples of 16.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// same, with an L2 eviction policy (streamed-once corpus: evict_first)
+__device__ __forceinline__ void bulk_g2s_hint(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar,
+                                              uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
+            "r"(smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+        : "memory");
+}
+
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    return v;
+}
+
+// ---------------------------------------------------------------------------
+// ordering: SMALL = keep the smallest (squared L2), else keep the largest (IP).
+// Ties on the score go to the lowest id, which makes every result deterministic
+// (faiss leaves the order of equal distances unspecified).
+// ---------------------------------------------------------------------------
+template <bool SMALL>
+__device__ __forceinline__ bool better_val(float a, float b) {
+    return SMALL ? (a < b) : (a > b);
+}
+
+template <bool SMALL>
+__device__ __forceinline__ bool better(float a, uint32_t ia, float b, uint32_t ib) {
+    return better_val<SMALL>(a, b) || (a == b && ia < ib);
+}
+
+template <bool SMALL>
+__device__ __forceinline__ float worst_val() {
+    return SMALL ? FLT_MAX : -FLT_MAX;  // faiss pads with +FLT_MAX (L2) / -FLT_MAX (IP)
+}
+
+struct __align__(8) Cand {
+    float v;
+    uint32_t id;
+};
+
+// ---------------------------------------------------------------------------
+// Warp-distributed sorted candidate list of capacity KPL*32, best first.
+// Entry e lives in slot e/32 of lane e%32.  All methods are warp-collective.
+// ---------------------------------------------------------------------------
+template <int KPL, bool SMALL>
+struct WarpTopK {
+    float v[KPL];
+    uint32_t id[KPL];
+    float thr;        // score of entry k-1 (uniform across the warp)
+    uint32_t thr_id;  // its id
+    int k;
+
+    __device__ __forceinline__ void init(int k_) {
+        k = k_;
+#pragma unroll
+        for (int j = 0; j < KPL; j++) {
+            v[j] = worst_val<SMALL>();
+            id[j] = kEmptyId;
+        }
+        thr = worst_val<SMALL>();
+        thr_id = kEmptyId;
+    }
+
+    __device__ __forceinline__ void refresh_thr() {
+        const int e = k - 1;
+        float tv = v[0];
+        uint32_t ti = id[0];
+#pragma unroll
+        for (int j = 1; j < KPL; j++)
+            if ((e >> 5) == j) {
+                tv = v[j];
+                ti = id[j];
+            }
+        thr = __shfl_sync(0xffffffffu, tv, e & 31);
+        thr_id = __shfl_sync(0xffffffffu, ti, e & 31);
+    }
+
+    // s/sid uniform across the warp.  Caller has checked that (s,sid) beats thr.
+    __device__ __forceinline__ void insert(float s, uint32_t sid) {
+        const int lane = threadIdx.x & 31;
+        int pos = 0;
+#pragma unroll
+        for (int j = 0; j < KPL; j++) pos += __popc(__ballot_sync(0xffffffffu, better<SMALL>(v[j], id[j], s, sid)));
+#pragma unroll
+        for (int j = KPL - 1; j >= 0; j--) {
+            float up_v = __shfl_up_sync(0xffffffffu, v[j], 1);
+            uint32_t up_i = __shfl_up_sync(0xffffffffu, id[j], 1);
+            if (j > 0) {
+                float cv = __shfl_sync(0xffffffffu, v[j - 1], 31);
+                uint32_t ci = __shfl_sync(0xffffffffu, id[j - 1], 31);
+                if (lane == 0) {
+                    up_v = cv;
+                    up_i = ci;
+                }
+            }
+            const int e = j * 32 + lane;
+            if (e > pos) {
+                v[j] = up_v;
+                id[j] = up_i;
+            } else if (e == pos) {
+                v[j] = s;
+                id[j] = sid;
+            }
+        }
+        refresh_thr();
+    }
+
+    // value-only test for the streaming loop, where ids only ever increase
+    __device__ __forceinline__ void offer_stream(float s, uint32_t sid) {
+        if (better_val<SMALL>(s, thr)) insert(s, sid);
+    }
+
+    // each lane brings one candidate; survivors are inserted one by one
+    __device__ __forceinline__ void offer_lanes(float cv, uint32_t cid) {
+        unsigned m = __ballot_sync(0xffffffffu, cid != kEmptyId && better<SMALL>(cv, cid, thr, thr_id));
+        while (m) {
+            const int src = __ffs(m) - 1;
+            m &= m - 1;
+            const float s = __shfl_sync(0xffffffffu, cv, src);
+            const uint32_t sid = __shfl_sync(0xffffffffu, cid, src);
+            if (better<SMALL>(s, sid, thr, thr_id)) insert(s, sid);
+        }
+    }
+
+    // merge `nlists` stored lists (each KPL*32 entries, `stride` entries apart)
+    template <bool GLOBAL>
+    __device__ __forceinline__ void merge_from(const Cand* lists, int first, int nlists, int step, size_t stride) {
+        const int lane = threadIdx.x & 31;
+        for (int l = first; l < nlists; l += step) {
+            const Cand* src = lists + (size_t)l * stride;
+#pragma unroll
+            for (int j = 0; j < KPL; j++) {
+                Cand c;
+                if (GLOBAL) {
+                    // written by other CTAs of this launch: read through L2
+                    const unsigned long long raw =
+                        __ldcg(reinterpret_cast<const unsigned long long*>(src + j * 32 + lane));
+                    c.v = __uint_as_float((uint32_t)(raw & 0xffffffffull));
+                    c.id = (uint32_t)(raw >> 32);
+                } else {
+                    c = src[j * 32 + lane];
+                }
+                // lists are sorted: once a whole slot fails, the rest of the list fails too
+                const bool any = __any_sync(0xffffffffu, c.id != kEmptyId && better<SMALL>(c.v, c.id, thr, thr_id));
+                if (!any) break;
+                offer_lanes(c.v, c.id);
+            }
+        }
+    }
+
+    __device__ __forceinline__ void store(Cand* dst) const {
+        const int lane = threadIdx.x & 31;
+#pragma unroll
+        for (int j = 0; j < KPL; j++) {
+            Cand c;
+            c.v = v[j];
+            c.id = id[j];
+            dst[j * 32 + lane] = c;
+        }
+    }
+};
+
+}  // namespace b200r

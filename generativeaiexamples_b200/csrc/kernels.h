@@ -1,0 +1,58 @@
+// Internal launch interfaces between the .cu files of libb200r.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200r {
+
+struct Cand;
+
+constexpr int kScanMaxNQ = 4;    // queries per scan launch
+constexpr int kScanMaxK = 128;   // k served by the register-list scan path
+
+struct ScanParams {
+    const void* corpus;   // [n_rows][d] fp32 or bf16, row-major, rows 16-byte multiples
+    int64_t n_rows;
+    int d;                // padded dimension (multiple of 4 fp32 / 8 bf16)
+    int row_bytes;
+    const float* q;       // [NQ][d] fp32 on the device, unused slots zero
+    int nq_active;
+    int k;
+    int nstages, stage_bytes, rows_per_tile;
+    int64_t n_tiles;
+    int evict_first;      // corpus larger than L2: stream it with evict_first
+    Cand* scratch;        // [grid][NQ][KCAP]
+    unsigned* counter;    // zero on entry, zero on exit
+    float* out_d;         // [nq][k]
+    int64_t* out_i;       // [nq][k]
+    int64_t id_base;      // added to every returned id (row-sharded multi-GPU)
+};
+
+size_t scan_scratch_bytes(int max_grid);
+cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st,
+                        int* grid_out);
+
+// K1 ingest: rows [n][d_in] fp32 -> corpus rows [n][d_pad] (fp32 or bf16), optional
+// L2 normalisation (faiss fvec_renorm_L2 semantics), squared norms of what was stored.
+cudaError_t launch_ingest(const float* src, int64_t n, int d_in, int d_pad, bool normalize, bool to_bf16, void* dst_rows,
+                          float* dst_norms, cudaStream_t st);
+// in-place faiss.normalize_L2 on device memory
+cudaError_t launch_normalize(float* x, int64_t n, int d, cudaStream_t st);
+// query prep: [nq][d_in] fp32 -> [nq_slots][d_pad] fp32, zero padded, optional normalise
+cudaError_t launch_prep_queries(const float* src, int64_t nq, int d_in, int d_pad, int64_t nq_slots, bool normalize,
+                                float* dst, cudaStream_t st);
+
+// K5 compaction gather: out row o (o0 <= o < o1) <- src row o + #{deleted ids before it}
+cudaError_t launch_gather_rows(const void* src, void* out, int64_t o0, int64_t o1, int row_bytes,
+                               const int64_t* del_adj, int64_t n_del, cudaStream_t st);
+
+// K4 merge: n_lists candidate blocks, block l at cand_x + l * stride_x holding [nq][k_in]
+// -> [nq][k_out]
+cudaError_t launch_merge(bool l2, const float* cand_d, const int64_t* cand_i, int64_t nq, int n_lists, int k_in,
+                         int64_t stride_d, int64_t stride_i, int k_out, float* out_d, int64_t* out_i,
+                         cudaStream_t st);
+
+// reconstruct helper: corpus row -> fp32
+cudaError_t launch_row_to_f32(const void* row, int d, bool bf16, float* out, cudaStream_t st);
+
+}  // namespace b200r

@@ -1,0 +1,74 @@
+// K4: final select over per-shard candidates (multi-GPU merge step).
+//
+// No counterpart in the reference (its FAISS index lives in one process on the CPU).
+// After each rank's local search, the (score, id) candidates are exchanged with an
+// NCCL allgather (torch.distributed, see generativeaiexamples_b200/sharded.py) into one
+// block per rank, each [nq][k_in]; this kernel keeps the k_out best per query -- the same
+// selection faiss's heap makes, because top-k of a union is top-k of the per-shard
+// top-k's.  Ties go to the earlier list position, which equals the lowest global id
+// for contiguous row-block sharding with rank-ordered lists.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200r {
+
+template <int KPL, bool L2>
+__global__ void __launch_bounds__(128) merge_topk_kernel(const float* __restrict__ cand_d,
+                                                         const int64_t* __restrict__ cand_i, int64_t nq, int n_lists,
+                                                         int k_in, int64_t stride_d, int64_t stride_i, int k_out,
+                                                         float* __restrict__ out_d, int64_t* __restrict__ out_i) {
+    const int lane = threadIdx.x & 31;
+    const int64_t q = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (q >= nq) return;
+    // candidate (list l, entry e) lives at cand_x[l * stride_x + q * k_in + e]; its
+    // identity inside the kernel is pos = l * k_in + e
+    const int64_t total = (int64_t)n_lists * k_in;
+    WarpTopK<KPL, L2> m;
+    m.init(k_out);
+    for (int64_t base = 0; base < total; base += 32) {
+        const int64_t pos = base + lane;
+        float v = worst_val<L2>();
+        uint32_t id = kEmptyId;
+        if (pos < total) {
+            const int64_t l = pos / k_in, e = pos - l * k_in;
+            if (cand_i[l * stride_i + q * k_in + e] >= 0) {
+                v = cand_d[l * stride_d + q * k_in + e];
+                id = (uint32_t)pos;
+            }
+        }
+        m.offer_lanes(v, id);
+    }
+#pragma unroll
+    for (int j = 0; j < KPL; j++) {
+        const int e = j * 32 + lane;
+        if (e < k_out) {
+            int64_t gid = -1;
+            if (m.id[j] != kEmptyId) {
+                const int64_t l = m.id[j] / k_in, ee = m.id[j] - l * k_in;
+                gid = cand_i[l * stride_i + q * k_in + ee];
+            }
+            out_d[q * k_out + e] = m.v[j];
+            out_i[q * k_out + e] = gid;
+        }
+    }
+}
+
+cudaError_t launch_merge(bool l2, const float* cand_d, const int64_t* cand_i, int64_t nq, int n_lists, int k_in,
+                         int64_t stride_d, int64_t stride_i, int k_out, float* out_d, int64_t* out_i,
+                         cudaStream_t st) {
+    if (nq <= 0) return cudaSuccess;
+    if (k_out < 1 || k_out > kScanMaxK || n_lists < 1 || k_in < 1) return cudaErrorInvalidValue;
+    if ((int64_t)n_lists * k_in >= 0xFFFFFFFFll) return cudaErrorInvalidValue;
+    const int wpb = 4;
+    const int g = (int)((nq + wpb - 1) / wpb);
+    if (k_out <= 32) {
+        if (l2) merge_topk_kernel<1, true><<<g, wpb * 32, 0, st>>>(cand_d, cand_i, nq, n_lists, k_in, stride_d, stride_i, k_out, out_d, out_i);
+        else merge_topk_kernel<1, false><<<g, wpb * 32, 0, st>>>(cand_d, cand_i, nq, n_lists, k_in, stride_d, stride_i, k_out, out_d, out_i);
+    } else {
+        if (l2) merge_topk_kernel<4, true><<<g, wpb * 32, 0, st>>>(cand_d, cand_i, nq, n_lists, k_in, stride_d, stride_i, k_out, out_d, out_i);
+        else merge_topk_kernel<4, false><<<g, wpb * 32, 0, st>>>(cand_d, cand_i, nq, n_lists, k_in, stride_d, stride_i, k_out, out_d, out_i);
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace b200r

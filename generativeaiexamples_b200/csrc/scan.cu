@@ -1,0 +1,296 @@
+// K2: small-batch exact scorer with fused top-k ("scan" path, nq <= 4 per launch).
+//
+// Replaces, on the GPU, what faiss 1.7.4 runs for nq < 20 in
+// IndexFlat::search -> knn_L2sqr / knn_inner_product -> exhaustive_*_seq
+// (faiss/utils/distances.cpp): one fvec_inner_product / fvec_L2sqr per corpus row and a
+// heap of the k best.  Reached in the reference from
+// RAG/examples/basic_rag/langchain/chains.py:163 (retriever) via
+// langchain FAISS.similarity_search_with_score_by_vector -> index.search(v, k).
+//
+// Design (HBM-bound; roofline = N * d * sizeof(elem) bytes per launch):
+//  * persistent grid, one CTA per SM; tile t -> CTA (t mod grid), a tile is
+//    `rows_per_tile` consecutive rows = one contiguous <= 32 KB block;
+//  * warp 0 is the producer: one lane issues cp.async.bulk (TMA engine, SASS UBLKCP)
+//    into an NSTAGES-deep shared-memory ring, completion on mbarriers;
+//  * 16 consumer warps: a warp owns whole rows, reads them with 128-bit LDS, keeps
+//    fp32 partial sums, butterfly-reduces, and offers the score to its register
+//    top-k list (WarpTopK).  Direct (q-x)^2 for L2, as faiss's nq<20 path does;
+//  * epilogue: lists -> shared memory -> per-CTA merge -> global scratch; the last
+//    CTA to finish (atomic ticket) merges all CTA lists and writes D/I.  The score
+//    vector is never written to HBM.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200r {
+
+constexpr int kScanConsumerWarps = 16;
+constexpr int kScanThreads = 32 * (1 + kScanConsumerWarps);
+
+template <int NQ, int KPL, bool L2, bool BF16>
+__global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int NCW = kScanConsumerWarps;
+    constexpr int KCAP = KPL * 32;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int nst = p.nstages;
+
+    uint8_t* stage_base = smem;
+    float* qs = reinterpret_cast<float*>(smem + (size_t)nst * p.stage_bytes);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(qs + (size_t)NQ * p.d);
+    uint64_t* empty_bar = full_bar + nst;
+    __shared__ int s_is_last;
+
+    // ---- set-up ---------------------------------------------------------
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < nst; s++) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], NCW);
+        }
+        fence_mbar_init();
+    }
+    // queries -> shared memory (fp32, zero padded to NQ rows by the host)
+    {
+        const float4* qg = reinterpret_cast<const float4*>(p.q);
+        float4* q4 = reinterpret_cast<float4*>(qs);
+        const int n4 = NQ * p.d / 4;
+        for (int i = threadIdx.x; i < n4; i += blockDim.x) q4[i] = qg[i];
+    }
+    __syncthreads();
+
+    const int64_t n_tiles = p.n_tiles;
+    const int R = p.rows_per_tile;
+
+    WarpTopK<KPL, L2> top[NQ];
+#pragma unroll
+    for (int qi = 0; qi < NQ; qi++) top[qi].init(p.k);
+
+    if (warp == 0) {
+        // ---- producer ---------------------------------------------------
+        if (lane == 0) {
+            const uint64_t pol = policy_evict_first();
+            const uint8_t* g = reinterpret_cast<const uint8_t*>(p.corpus);
+            int s = 0;
+            uint32_t ph = 0;
+            for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                const int64_t row0 = t * R;
+                const int64_t rem = p.n_rows - row0;
+                const uint32_t rows = (uint32_t)(rem < R ? rem : R);
+                const uint32_t bytes = rows * (uint32_t)p.row_bytes;
+                mbar_arrive_expect_tx(&full_bar[s], bytes);
+                if (p.evict_first)
+                    bulk_g2s_hint(stage_base + (size_t)s * p.stage_bytes, g + row0 * (int64_t)p.row_bytes, bytes,
+                                  &full_bar[s], pol);
+                else
+                    bulk_g2s(stage_base + (size_t)s * p.stage_bytes, g + row0 * (int64_t)p.row_bytes, bytes,
+                             &full_bar[s]);
+                if (++s == nst) {
+                    s = 0;
+                    ph ^= 1;
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ---- consumers --------------------------------------------------
+        const int cw = warp - 1;
+        int s = 0;
+        uint32_t ph = 0;
+        int64_t seq = 0;  // rows this CTA has streamed before the current tile
+        const int nvec = BF16 ? (p.d >> 3) : (p.d >> 2);  // 16-byte vectors per row
+        for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            const int64_t row0 = t * R;
+            const int64_t rem = p.n_rows - row0;
+            const int rows = (int)(rem < R ? rem : R);
+            mbar_wait(&full_bar[s], ph);
+            const uint8_t* tile = stage_base + (size_t)s * p.stage_bytes;
+            // round-robin row ownership across the CTA's row stream
+            int r = (int)(((int64_t)cw - seq) % NCW);
+            if (r < 0) r += NCW;
+            for (; r < rows; r += NCW) {
+                const uint4* xr = reinterpret_cast<const uint4*>(tile + (size_t)r * p.row_bytes);
+                float acc[NQ][4];
+#pragma unroll
+                for (int qi = 0; qi < NQ; qi++) acc[qi][0] = acc[qi][1] = acc[qi][2] = acc[qi][3] = 0.f;
+                for (int i0 = 0; i0 < nvec; i0 += 32 * 8) {
+                    uint4 xv[8];
+#pragma unroll
+                    for (int u = 0; u < 8; u++) {
+                        const int i = i0 + u * 32 + lane;
+                        xv[u] = (i < nvec) ? xr[i] : make_uint4(0, 0, 0, 0);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; u++) {
+                        const int i = i0 + u * 32 + lane;
+                        if (i < nvec) {
+                            if (!BF16) {
+                                const float x0 = __uint_as_float(xv[u].x), x1 = __uint_as_float(xv[u].y),
+                                            x2 = __uint_as_float(xv[u].z), x3 = __uint_as_float(xv[u].w);
+#pragma unroll
+                                for (int qi = 0; qi < NQ; qi++) {
+                                    const float4 qv = reinterpret_cast<const float4*>(qs + (size_t)qi * p.d)[i];
+                                    if (L2) {
+                                        const float t0 = qv.x - x0, t1 = qv.y - x1, t2 = qv.z - x2, t3 = qv.w - x3;
+                                        acc[qi][0] = fmaf(t0, t0, acc[qi][0]);
+                                        acc[qi][1] = fmaf(t1, t1, acc[qi][1]);
+                                        acc[qi][2] = fmaf(t2, t2, acc[qi][2]);
+                                        acc[qi][3] = fmaf(t3, t3, acc[qi][3]);
+                                    } else {
+                                        acc[qi][0] = fmaf(qv.x, x0, acc[qi][0]);
+                                        acc[qi][1] = fmaf(qv.y, x1, acc[qi][1]);
+                                        acc[qi][2] = fmaf(qv.z, x2, acc[qi][2]);
+                                        acc[qi][3] = fmaf(qv.w, x3, acc[qi][3]);
+                                    }
+                                }
+                            } else {
+                                // 8 bf16 -> fp32 (exact: bf16 is the top half of an fp32)
+                                float x[8];
+                                x[0] = __uint_as_float(xv[u].x << 16);
+                                x[1] = __uint_as_float(xv[u].x & 0xffff0000u);
+                                x[2] = __uint_as_float(xv[u].y << 16);
+                                x[3] = __uint_as_float(xv[u].y & 0xffff0000u);
+                                x[4] = __uint_as_float(xv[u].z << 16);
+                                x[5] = __uint_as_float(xv[u].z & 0xffff0000u);
+                                x[6] = __uint_as_float(xv[u].w << 16);
+                                x[7] = __uint_as_float(xv[u].w & 0xffff0000u);
+#pragma unroll
+                                for (int qi = 0; qi < NQ; qi++) {
+                                    const float4* qp = reinterpret_cast<const float4*>(qs + (size_t)qi * p.d) + 2 * i;
+                                    const float4 qa = qp[0], qb = qp[1];
+                                    const float qq[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+#pragma unroll
+                                    for (int e = 0; e < 8; e++) {
+                                        if (L2) {
+                                            const float tt = qq[e] - x[e];
+                                            acc[qi][e & 3] = fmaf(tt, tt, acc[qi][e & 3]);
+                                        } else {
+                                            acc[qi][e & 3] = fmaf(qq[e], x[e], acc[qi][e & 3]);
+                                        }
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+                const uint32_t row = (uint32_t)(row0 + r);
+#pragma unroll
+                for (int qi = 0; qi < NQ; qi++) {
+                    const float sc = warp_sum((acc[qi][0] + acc[qi][2]) + (acc[qi][1] + acc[qi][3]));
+                    top[qi].offer_stream(sc, row);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[s]);
+            seq += rows;
+            if (++s == nst) {
+                s = 0;
+                ph ^= 1;
+            }
+        }
+    }
+
+    // ---- epilogue: per-CTA merge, then last-CTA grid merge ----------------
+    __syncthreads();  // every stage consumed; the ring is free for reuse
+    Cand* sm_lists = reinterpret_cast<Cand*>(smem);  // [NQ][NCW][KCAP]
+    if (warp > 0) {
+#pragma unroll
+        for (int qi = 0; qi < NQ; qi++) top[qi].store(sm_lists + ((size_t)qi * NCW + (warp - 1)) * KCAP);
+    }
+    __syncthreads();
+    if (warp < NQ) {
+        WarpTopK<KPL, L2> m;
+        m.init(p.k);
+        m.template merge_from<false>(sm_lists + (size_t)warp * NCW * KCAP, 0, NCW, 1, KCAP);
+        m.store(p.scratch + ((size_t)blockIdx.x * NQ + warp) * KCAP);
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned ticket = atomicAdd(p.counter, 1u);
+        s_is_last = (ticket == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_is_last) return;
+    __threadfence();
+
+    // phase A: every warp folds a strided subset of the CTA lists, per query
+    constexpr int NW = kScanThreads / 32;
+    for (int qi = 0; qi < NQ; qi++) {
+        WarpTopK<KPL, L2> m;
+        m.init(p.k);
+        m.template merge_from<true>(p.scratch + (size_t)qi * KCAP, warp, (int)gridDim.x, NW, (size_t)NQ * KCAP);
+        m.store(sm_lists + ((size_t)qi * NW + warp) * KCAP);
+    }
+    __syncthreads();
+    // phase B: one warp per query folds the NW partial lists and writes the result
+    if (warp < NQ && warp < p.nq_active) {
+        WarpTopK<KPL, L2> m;
+        m.init(p.k);
+        m.template merge_from<false>(sm_lists + (size_t)warp * NW * KCAP, 0, NW, 1, KCAP);
+#pragma unroll
+        for (int j = 0; j < KPL; j++) {
+            const int e = j * 32 + lane;
+            if (e < p.k) {
+                p.out_d[(size_t)warp * p.k + e] = m.v[j];
+                p.out_i[(size_t)warp * p.k + e] = (m.id[j] == kEmptyId) ? -1 : (int64_t)m.id[j] + p.id_base;
+            }
+        }
+    }
+    if (threadIdx.x == 0) *p.counter = 0;  // ready for the next launch on this stream
+}
+
+// ---------------------------------------------------------------------------
+template <int NQ, int KPL, bool L2, bool BF16>
+static cudaError_t launch_one(const ScanParams& p, int grid, size_t smem, cudaStream_t st) {
+    auto kern = scan_topk_kernel<NQ, KPL, L2, BF16>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, kScanThreads, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+template <int NQ, int KPL>
+static cudaError_t launch_mk(const ScanParams& p, bool l2, bool bf16, int grid, size_t smem, cudaStream_t st) {
+    if (l2) return bf16 ? launch_one<NQ, KPL, true, true>(p, grid, smem, st)
+                        : launch_one<NQ, KPL, true, false>(p, grid, smem, st);
+    return bf16 ? launch_one<NQ, KPL, false, true>(p, grid, smem, st)
+                : launch_one<NQ, KPL, false, false>(p, grid, smem, st);
+}
+
+size_t scan_scratch_bytes(int max_grid) { return (size_t)max_grid * kScanMaxNQ * kScanMaxK * sizeof(Cand); }
+
+// Fills in the tiling fields of `p` and launches.  p.q must hold nq_slots(nq) rows.
+cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st,
+                        int* grid_out) {
+    const int NQ = nq <= 1 ? 1 : 4;
+    const int KPL = p.k <= 32 ? 1 : 4;
+    if (nq < 1 || nq > kScanMaxNQ || p.k < 1 || p.k > kScanMaxK) return cudaErrorInvalidValue;
+    smem_limit -= 1024;  // static shared + slack
+    const size_t q_bytes = (size_t)NQ * p.d * sizeof(float);
+    const size_t bar_bytes = 2 * 16 * sizeof(uint64_t);
+    const size_t merge_bytes = (size_t)NQ * (kScanThreads / 32) * KPL * 32 * sizeof(Cand);
+    // stage: as many whole rows as fit in 32 KB (at least one)
+    int stage_bytes = 32 * 1024;
+    if (p.row_bytes > stage_bytes) stage_bytes = (p.row_bytes + 127) / 128 * 128;
+    int R = stage_bytes / p.row_bytes;
+    if (smem_limit < q_bytes + bar_bytes + 2 * (size_t)stage_bytes) return cudaErrorInvalidValue;
+    int nst = (int)((smem_limit - q_bytes - bar_bytes) / stage_bytes);
+    if (nst > 16) nst = 16;
+    if (nst > 6) nst = 6;
+    if ((size_t)nst * stage_bytes < merge_bytes) return cudaErrorInvalidValue;
+    p.nstages = nst;
+    p.stage_bytes = stage_bytes;
+    p.rows_per_tile = R;
+    p.n_tiles = (p.n_rows + R - 1) / R;
+    p.nq_active = nq;
+    int grid = (int)(p.n_tiles < num_sms ? p.n_tiles : num_sms);
+    if (grid < 1) grid = 1;
+    if (grid_out) *grid_out = grid;
+    const size_t smem = (size_t)nst * stage_bytes + q_bytes + bar_bytes;
+    if (NQ == 1) return KPL == 1 ? launch_mk<1, 1>(p, l2, bf16, grid, smem, st) : launch_mk<1, 4>(p, l2, bf16, grid, smem, st);
+    return KPL == 1 ? launch_mk<4, 1>(p, l2, bf16, grid, smem, st) : launch_mk<4, 4>(p, l2, bf16, grid, smem, st);
+}
+
+}  // namespace b200r

@@ -1,0 +1,71 @@
+"""The factory branch a maintainer adds to the chain server.
+
+Mirrors ``create_vectorstore_langchain`` / ``get_vectorstore`` of
+/root/reference/RAG/src/chain_server/utils.py:288-347 for the one store this package
+provides.  Configuration follows the reference's ``APP_<SECTION>_<FIELD>`` environment
+convention (``RAG/src/chain_server/configuration_wizard.py:38``,
+``configuration.py:20-44,109-113``): ``APP_VECTORSTORE_NAME=b200flat`` selects the store,
+``APP_EMBEDDINGS_DIMENSIONS`` (default 1024) sizes it; ``faiss`` is accepted as an alias
+so an existing FAISS deployment switches over by installing this package.
+
+Engine options (no reference counterpart) use the ``B200R_`` prefix:
+``B200R_DEVICE`` (CUDA ordinal, default 0), ``B200R_STORAGE`` (``f32`` | ``bf16``),
+``B200R_RESERVE_ROWS`` (rows of HBM reserved up front).
+"""
+from __future__ import annotations
+
+import logging
+import os
+from typing import Optional
+
+from .flat_index import B200IndexFlatL2
+from .vectorstore import B200FlatVectorStore, InMemoryDocstore
+
+logger = logging.getLogger(__name__)
+
+SUPPORTED_NAMES = ("b200flat", "faiss")
+
+
+def create_vectorstore_langchain(document_embedder, collection_name: str = "", *, name: Optional[str] = None,
+                                 dimensions: Optional[int] = None) -> B200FlatVectorStore:
+    """utils.py:288-332, FAISS branch (:305-306): an empty squared-L2 flat store of
+    ``config.embeddings.dimensions`` columns with an in-memory docstore."""
+    name = name if name is not None else os.getenv("APP_VECTORSTORE_NAME", "b200flat")
+    if not collection_name:
+        collection_name = os.getenv("COLLECTION_NAME", "vector_db")
+    if name not in SUPPORTED_NAMES:
+        raise ValueError(f"{name} vector database is not supported")
+    d = int(dimensions if dimensions is not None else os.getenv("APP_EMBEDDINGS_DIMENSIONS", "1024"))
+    index = B200IndexFlatL2(d, device=int(os.getenv("B200R_DEVICE", "0")), storage=os.getenv("B200R_STORAGE", "f32"),
+                            reserve_rows=int(os.getenv("B200R_RESERVE_ROWS", "0")))
+    vectorstore = B200FlatVectorStore(document_embedder, index, InMemoryDocstore(), {})
+    logger.info("Vector store created and saved.")
+    return vectorstore
+
+
+def get_vectorstore(vectorstore: Optional[B200FlatVectorStore], document_embedder) -> B200FlatVectorStore:
+    """utils.py:335-347: hand back the module-global store, creating it on first use."""
+    if vectorstore is None:
+        return create_vectorstore_langchain(document_embedder)
+    return vectorstore
+
+
+def get_docs_vectorstore_langchain(vectorstore: B200FlatVectorStore):
+    """utils.py:492-529, FAISS branch (:506-510): file names of the ingested documents."""
+    in_memory_docstore = vectorstore.docstore._dict
+    filenames = [os.path.basename(doc.metadata["source"]) for doc in in_memory_docstore.values()]
+    return list(dict.fromkeys(filenames))  # the reference returns list(set(...)): same members
+
+
+def del_docs_vectorstore_langchain(vectorstore: B200FlatVectorStore, filenames) -> bool:
+    """utils.py:532-603, FAISS branch (:546-560): delete every chunk of the named files."""
+    in_memory_docstore = vectorstore.docstore._dict
+    for filename in filenames:
+        ids_list = [doc_id for doc_id, doc_data in in_memory_docstore.items()
+                    if os.path.basename(doc_data.metadata["source"]) == filename]
+        if not ids_list:
+            logger.info("File does not exist in the vectorstore")
+            return False
+        vectorstore.delete(ids_list)
+        logger.info(f"Deleted documents with filenames {filename}")
+    return True

@@ -1,0 +1,231 @@
+"""``B200IndexFlat``: the faiss ``IndexFlatL2`` / ``IndexFlatIP`` python surface on libb200r.
+
+Mirrors what ``faiss/python/class_wrappers.py`` (faiss 1.7.4) gives the reference:
+``replacement_add`` / ``replacement_search`` / ``replacement_remove_ids`` /
+``replacement_reconstruct`` plus ``faiss.normalize_L2`` -- same names, same argument
+meaning, same error behaviour (AssertionError on a dimension mismatch or ``k <= 0``,
+RuntimeError from the engine).  Reference call sites:
+``RAG/src/chain_server/utils.py:306`` (``IndexFlatL2(dim)``),
+``community/chat-llama-nemotron/backend-rag/src/rag_service.py:88,194,197,292,301,450``.
+
+numpy arrays and torch tensors (CPU or CUDA) are accepted; torch is used only to read
+``data_ptr()`` / the current stream and to allocate result tensors for device callers.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import numpy as np
+
+from . import _lib
+
+METRIC_INNER_PRODUCT = 0
+METRIC_L2 = 1
+
+try:  # torch is plumbing only; the index works without it for numpy callers
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+def _is_torch(x):
+    return torch is not None and isinstance(x, torch.Tensor)
+
+
+def _torch_stream(device_index):
+    return ctypes.c_void_p(torch.cuda.current_stream(device_index).cuda_stream)
+
+
+class B200IndexFlat:
+    """Exact (brute-force) index resident in one B200's HBM."""
+
+    def __init__(self, d: int, metric: int = METRIC_L2, *, storage: str = "f32", device: int = 0,
+                 normalize_on_add: bool = False, normalize_queries: bool = False, reserve_rows: int = 0,
+                 id_base: int = 0, search_path: int = _lib.PATH_AUTO):
+        if storage not in ("f32", "bf16"):
+            raise ValueError("storage must be 'f32' or 'bf16'")
+        self._h = None
+        self._L = _lib.load()
+        self.d = int(d)
+        self.metric_type = int(metric)
+        self.is_trained = True
+        self.storage = storage
+        self.device = int(device)
+        cfg = _lib.Config(dim=self.d, metric=self.metric_type, storage=_lib.BF16 if storage == "bf16" else _lib.F32,
+                          normalize_on_add=int(normalize_on_add), normalize_queries=int(normalize_queries),
+                          device=self.device, search_path=int(search_path), reserve_rows=int(reserve_rows),
+                          id_base=int(id_base))
+        h = ctypes.c_void_p()
+        _lib.check(self._L.b200r_create(ctypes.byref(cfg), ctypes.byref(h)))
+        self._h = h
+
+    # -- lifetime -----------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.b200r_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def ntotal(self) -> int:
+        out = ctypes.c_int64()
+        _lib.check(self._L.b200r_ntotal(self._h, ctypes.byref(out)))
+        return out.value
+
+    # -- add ------------------------------------------------------------------
+    def add(self, x) -> None:
+        """faiss ``replacement_add``: x is (n, d); converted to C-contiguous float32."""
+        if _is_torch(x) and x.is_cuda:
+            n, d = x.shape
+            assert d == self.d
+            assert x.device.index == self.device, "tensor and index live on different GPUs"
+            x = x.contiguous().to(torch.float32)
+            _lib.check(self._L.b200r_add(self._h, ctypes.c_void_p(x.data_ptr()), n, _lib.F32, _lib.DEVICE,
+                                         _torch_stream(self.device)))
+            # the ingest kernel reads x asynchronously on the caller's stream: keep it
+            # alive until that stream has passed this point
+            x.record_stream(torch.cuda.current_stream(self.device))
+            return
+        if _is_torch(x):
+            x = x.numpy()
+        n, d = x.shape
+        assert d == self.d
+        x = np.ascontiguousarray(x, dtype="float32")
+        _lib.check(self._L.b200r_add(self._h, x.ctypes.data_as(ctypes.c_void_p), n, _lib.F32, _lib.HOST, None))
+
+    # -- search ---------------------------------------------------------------
+    def search(self, x, k: int, D=None, I=None):
+        """faiss ``replacement_search``: returns (D (n,k) float32, I (n,k) int64).
+
+        numpy / CPU input -> numpy output.  CUDA tensor input -> CUDA tensors, filled
+        asynchronously on the current torch stream (no host round trip)."""
+        if _is_torch(x) and x.is_cuda:
+            n, d = x.shape
+            assert d == self.d
+            assert k > 0
+            assert x.device.index == self.device, "tensor and index live on different GPUs"
+            x = x.contiguous().to(torch.float32)
+            if D is None:
+                D = torch.empty((n, k), dtype=torch.float32, device=x.device)
+            if I is None:
+                I = torch.empty((n, k), dtype=torch.int64, device=x.device)
+            assert D.shape == (n, k) and I.shape == (n, k) and D.is_contiguous() and I.is_contiguous()
+            _lib.check(self._L.b200r_search(self._h, ctypes.c_void_p(x.data_ptr()), n, k, _lib.DEVICE,
+                                            ctypes.c_void_p(D.data_ptr()), ctypes.c_void_p(I.data_ptr()), _lib.DEVICE,
+                                            _torch_stream(self.device)))
+            x.record_stream(torch.cuda.current_stream(self.device))
+            return D, I
+        if _is_torch(x):
+            x = x.numpy()
+        n, d = x.shape
+        assert d == self.d
+        x = np.ascontiguousarray(x, dtype="float32")
+        assert k > 0
+        if D is None:
+            D = np.empty((n, k), dtype=np.float32)
+        else:
+            assert D.shape == (n, k)
+        if I is None:
+            I = np.empty((n, k), dtype=np.int64)
+        else:
+            assert I.shape == (n, k)
+        _lib.check(self._L.b200r_search(self._h, x.ctypes.data_as(ctypes.c_void_p), n, k, _lib.HOST,
+                                        D.ctypes.data_as(ctypes.c_void_p), I.ctypes.data_as(ctypes.c_void_p),
+                                        _lib.HOST, None))
+        return D, I
+
+    # -- remove / reconstruct / reset ----------------------------------------
+    def remove_ids(self, x) -> int:
+        """faiss ``replacement_remove_ids`` with an id array (IDSelectorBatch)."""
+        x = np.ascontiguousarray(x, dtype="int64")
+        assert x.ndim == 1
+        out = ctypes.c_int64()
+        _lib.check(self._L.b200r_remove_ids(self._h, x.ctypes.data_as(ctypes.c_void_p), x.size, ctypes.byref(out)))
+        return out.value
+
+    def reconstruct(self, key: int, x: Optional[np.ndarray] = None) -> np.ndarray:
+        if x is None:
+            x = np.empty(self.d, dtype=np.float32)
+        else:
+            assert x.shape == (self.d,)
+        _lib.check(self._L.b200r_reconstruct(self._h, int(key), x.ctypes.data_as(ctypes.c_void_p)))
+        return x
+
+    def reset(self) -> None:
+        _lib.check(self._L.b200r_reset(self._h))
+
+    # -- persistence (faiss.write_index / read_index) ---------------------------
+    def write(self, path: str) -> None:
+        _lib.check(self._L.b200r_save(self._h, str(path).encode()))
+
+    @classmethod
+    def read(cls, path: str, *, storage: str = "f32", device: int = 0, **kw) -> "B200IndexFlat":
+        L = _lib.load()
+        self = cls.__new__(cls)
+        self._L = L
+        self._h = None
+        cfg = _lib.Config(dim=1, metric=METRIC_L2, storage=_lib.BF16 if storage == "bf16" else _lib.F32,
+                          normalize_on_add=int(kw.get("normalize_on_add", False)),
+                          normalize_queries=int(kw.get("normalize_queries", False)), device=int(device),
+                          search_path=int(kw.get("search_path", _lib.PATH_AUTO)), reserve_rows=0,
+                          id_base=int(kw.get("id_base", 0)))
+        h = ctypes.c_void_p()
+        _lib.check(L.b200r_load(str(path).encode(), ctypes.byref(cfg), ctypes.byref(h)))
+        self._h = h
+        self.storage, self.device, self.is_trained = storage, int(device), True
+        # d and metric come from the file: recover them through a zero-row probe
+        st = self.stats()
+        self.d, self.metric_type = _read_header(path)
+        assert st["ntotal"] >= 0
+        return self
+
+    # -- engine extras --------------------------------------------------------
+    def set_id_base(self, base: int) -> None:
+        _lib.check(self._L.b200r_set_id_base(self._h, int(base)))
+
+    def set_timing(self, enabled: bool) -> None:
+        _lib.check(self._L.b200r_set_timing(self._h, int(enabled)))
+
+    def stats(self) -> dict:
+        st = _lib.Stats()
+        _lib.check(self._L.b200r_stats_get(self._h, ctypes.byref(st)))
+        return st.as_dict()
+
+
+def _read_header(path) -> Tuple[int, int]:
+    import struct
+
+    with open(path, "rb") as f:
+        head = f.read(4 + 4 + 8 + 8 + 8 + 1 + 4)
+    _, d, _, _, _, _, metric = struct.unpack("<IiqqqBi", head)
+    return d, metric
+
+
+def B200IndexFlatL2(d: int, **kw) -> B200IndexFlat:
+    """``faiss.IndexFlatL2(d)`` (utils.py:306)."""
+    return B200IndexFlat(d, METRIC_L2, **kw)
+
+
+def B200IndexFlatIP(d: int, **kw) -> B200IndexFlat:
+    """``faiss.IndexFlatIP(d)``."""
+    return B200IndexFlat(d, METRIC_INNER_PRODUCT, **kw)
+
+
+def normalize_L2(x, device: int = 0) -> None:
+    """``faiss.normalize_L2(x)``: in place; rows with zero norm are left untouched."""
+    L = _lib.load()
+    if _is_torch(x) and x.is_cuda:
+        assert x.dtype == torch.float32 and x.is_contiguous() and x.dim() == 2
+        _lib.check(L.b200r_normalize_l2(ctypes.c_void_p(x.data_ptr()), x.shape[0], x.shape[1], _lib.DEVICE,
+                                        x.device.index, _torch_stream(x.device.index)))
+        return
+    if _is_torch(x):
+        x = x.numpy()
+    assert x.dtype == np.float32 and x.flags.c_contiguous and x.ndim == 2
+    _lib.check(L.b200r_normalize_l2(x.ctypes.data_as(ctypes.c_void_p), x.shape[0], x.shape[1], _lib.HOST, device, None))

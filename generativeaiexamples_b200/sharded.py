@@ -1,0 +1,150 @@
+"""Row-sharded flat index: one process per GPU, NCCL allgather merge.
+
+The reference has no multi-GPU path (its FAISS index is one in-process CPU object,
+/root/reference/RAG/src/chain_server/utils.py:306); this module exists because the north
+star shards the corpus by rows over the GPUs of one box.  Top-k of a union equals top-k
+of the per-shard top-k's, so:
+
+1. rank r holds the contiguous global rows ``[base_r, base_r + n_r)`` in its own
+   ``B200IndexFlat`` (local id + ``id_base`` = faiss-style global position);
+2. every rank runs the same query batch against its shard (results stay on the device);
+3. one ``all_gather_into_tensor`` exchanges ``nq*k`` (score, id) pairs per rank --
+   12 bytes per candidate, a single packed buffer so the cost is one NCCL latency;
+4. every rank runs the K4 select (``b200r_merge_topk``) over the ``G*k`` candidates.
+
+``torch.distributed`` is plumbing only.  For CPU tests (gloo) the two device steps are
+injected as callables (``local_index`` / ``merge_fn``) so the host logic -- offsets,
+packing, gather layout -- runs without a GPU.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Callable, Optional
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .flat_index import METRIC_L2, B200IndexFlat
+
+
+def shard_bounds(n: int, world: int, rank: int):
+    """Contiguous row block of ``rank``: ceil-sized blocks, the last ones may be short/empty."""
+    per = (n + world - 1) // world
+    lo = min(n, rank * per)
+    return lo, min(n, lo + per)
+
+
+def _packed_layout(nq: int, k: int):
+    """Bytes of one rank's block: [scores fp32 nq*k | pad to 8 | ids int64 nq*k]."""
+    d_bytes = (nq * k * 4 + 7) // 8 * 8
+    return d_bytes, d_bytes + nq * k * 8
+
+
+def _merge_on_device(metric, packed_all, nq, world, k_in, k_out, device_index, D, I):
+    d_bytes, block = _packed_layout(nq, k_in)
+    base = packed_all.data_ptr()
+    L = _lib.load()
+    _lib.check(L.b200r_merge_topk(metric, ctypes.c_void_p(base), ctypes.c_void_p(base + d_bytes), nq, world, k_in,
+                                  block // 4, block // 8, k_out, ctypes.c_void_p(D.data_ptr()),
+                                  ctypes.c_void_p(I.data_ptr()), device_index,
+                                  ctypes.c_void_p(torch.cuda.current_stream(device_index).cuda_stream)))
+
+
+class ShardedFlatIndex:
+    """faiss-IndexFlat-shaped index whose rows are spread over the ranks of a process group."""
+
+    def __init__(self, d: int, metric: int = METRIC_L2, *, group=None, device: Optional[int] = None,
+                 local_index=None, merge_fn: Optional[Callable] = None, **index_kw):
+        self.d, self.metric_type = int(d), int(metric)
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        if local_index is None:
+            device = torch.cuda.current_device() if device is None else device
+            local_index = B200IndexFlat(d, metric, device=device, **index_kw)
+        self.local = local_index
+        self.device = device
+        self._merge_fn = merge_fn
+        self._on_gpu = merge_fn is None
+        self._counts = [0] * self.world  # rows per rank
+        self.id_base = 0
+
+    # -- bookkeeping ----------------------------------------------------------
+    @property
+    def ntotal(self) -> int:
+        return int(sum(self._counts))
+
+    def _buf_device(self):
+        return torch.device("cuda", self.device) if self._on_gpu else torch.device("cpu")
+
+    def _sync_counts(self):
+        mine = torch.tensor([self.local.ntotal], dtype=torch.int64, device=self._buf_device())
+        if self.world > 1:
+            allc = torch.empty(self.world, dtype=torch.int64, device=mine.device)
+            dist.all_gather_into_tensor(allc, mine, group=self.group)
+            self._counts = [int(c) for c in allc.cpu().tolist()]
+        else:
+            self._counts = [int(mine.item())]
+        self.id_base = int(sum(self._counts[: self.rank]))
+        self.local.set_id_base(self.id_base)
+
+    # -- add ------------------------------------------------------------------
+    def add_local(self, x) -> None:
+        """Append rows to THIS rank's shard (collective: every rank must call it, possibly with
+        zero rows).  Global ids are assigned rank-major: all of rank 0's rows, then rank 1's..."""
+        if x is not None and len(x):
+            self.local.add(x)
+        self._sync_counts()
+
+    def add(self, x) -> None:
+        """Every rank passes the same (n, d) matrix; rank r keeps its contiguous block.  Only
+        valid on an empty index or when appending would keep blocks contiguous per rank
+        (a growing corpus re-shards lazily: SURVEY.md section 7 "Mutable corpus")."""
+        if self.ntotal != 0:
+            raise NotImplementedError("add() after the first batch needs a re-shard; use add_local()")
+        lo, hi = shard_bounds(len(x), self.world, self.rank)
+        self.add_local(x[lo:hi])
+
+    # -- search ---------------------------------------------------------------
+    def search(self, q, k: int):
+        """All ranks pass the same queries; all ranks get the same (D, I)."""
+        nq = int(q.shape[0])
+        assert q.shape[1] == self.d
+        assert k > 0
+        as_numpy = not (isinstance(q, torch.Tensor) and q.is_cuda)
+        if self._on_gpu:
+            dev = self._buf_device()
+            qd = q if not as_numpy else torch.as_tensor(np.ascontiguousarray(q, dtype=np.float32)).to(dev, non_blocking=True)
+            d_bytes, block = _packed_layout(nq, k)
+            mine = torch.empty(block, dtype=torch.uint8, device=dev)
+            Dl = mine[: nq * k * 4].view(torch.float32).view(nq, k)
+            Il = mine[d_bytes:].view(torch.int64).view(nq, k)
+            self.local.search(qd, k, D=Dl, I=Il)  # ids already carry id_base
+            if self.world == 1:
+                D, I = Dl, Il
+            else:
+                allb = torch.empty(self.world * block, dtype=torch.uint8, device=dev)
+                dist.all_gather_into_tensor(allb, mine, group=self.group)
+                D = torch.empty((nq, k), dtype=torch.float32, device=dev)
+                I = torch.empty((nq, k), dtype=torch.int64, device=dev)
+                _merge_on_device(self.metric_type, allb, nq, self.world, k, k, self.device, D, I)
+            if as_numpy:
+                return D.cpu().numpy(), I.cpu().numpy()
+            return D, I
+        # host-logic path for CPU tests: same packing and layout, device steps injected
+        Dl, Il = self.local.search(np.ascontiguousarray(q, dtype=np.float32), k)
+        d_bytes, block = _packed_layout(nq, k)
+        mine = torch.zeros(block, dtype=torch.uint8)
+        mine[: nq * k * 4] = torch.from_numpy(np.ascontiguousarray(Dl, dtype=np.float32).view(np.uint8).reshape(-1))
+        mine[d_bytes:] = torch.from_numpy(np.ascontiguousarray(Il, dtype=np.int64).view(np.uint8).reshape(-1))
+        if self.world > 1:
+            allb = torch.empty(self.world * block, dtype=torch.uint8)
+            dist.all_gather_into_tensor(allb, mine, group=self.group)
+        else:
+            allb = mine
+        blocks = allb.numpy().reshape(self.world, block)
+        cand_d = np.stack([b[: nq * k * 4].view(np.float32).reshape(nq, k) for b in blocks])      # [G][nq][k]
+        cand_i = np.stack([b[d_bytes:].view(np.int64).reshape(nq, k) for b in blocks])
+        return self._merge_fn(self.metric_type, cand_d, cand_i, k)

@@ -1,0 +1,162 @@
+/*
+ * b200r.h -- C ABI of libb200r.so, the B200-native exact flat-search engine.
+ *
+ * This is the drop-in boundary for the vector-store search step of the reference's
+ * RAG chain server.  The reference reaches that step through faiss-cpu 1.7.4's SWIG
+ * wrapper (faiss/python/class_wrappers.py), from LangChain's FAISS vector store, which
+ * RAG/src/chain_server/utils.py:305-306 constructs:
+ *
+ *     FAISS(document_embedder, IndexFlatL2(config.embeddings.dimensions), InMemoryDocstore(), {})
+ *
+ * Every entry point below names the reference-side call it replaces.  All pointers are
+ * plain C; no torch types.  Every function returns 0 on success or a B200R_E_* code;
+ * b200r_last_error() then describes the failure (thread-local).  There is NO CPU
+ * fallback: creating an index without a usable CUDA device fails.
+ *
+ * Threading: searches on one index may be issued from many threads (they serialise on
+ * an internal lock, as the Morpheus service in
+ * community/event-driven-rag-cve-analysis/cyber_dev_day/faiss_vdb_service.py:169-174
+ * does with faiss); add/remove/reset must not overlap a search on the same index
+ * (faiss has the same rule).
+ */
+#ifndef B200R_H
+#define B200R_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200R_VERSION 100
+
+/* status codes */
+#define B200R_OK 0
+#define B200R_E_INVALID 1     /* bad argument (faiss wrapper: AssertionError) */
+#define B200R_E_CUDA 2        /* CUDA runtime/driver failure (faiss: RuntimeError) */
+#define B200R_E_UNSUPPORTED 3 /* valid request this build cannot serve */
+#define B200R_E_NOMEM 4       /* device or pinned allocation failed */
+#define B200R_E_IO 5          /* save/load */
+
+/* metric: numeric values equal faiss::MetricType */
+#define B200R_METRIC_INNER_PRODUCT 0 /* IndexFlatIP: larger is better, scores descending */
+#define B200R_METRIC_L2 1            /* IndexFlatL2: SQUARED distance, ascending */
+
+/* element type of the corpus in HBM / of vectors handed to add() */
+#define B200R_F32 0
+#define B200R_BF16 1
+
+/* where a caller-provided buffer lives */
+#define B200R_HOST 0
+#define B200R_DEVICE 1
+
+/* search path selection (b200r_config.search_path); AUTO mirrors faiss's own
+ * dispatch: small batches scan (faiss: exhaustive_*_seq for nq < 20), large batches
+ * go through the GEMM expansion (faiss: exhaustive_*_blas for nq >= 20). */
+#define B200R_PATH_AUTO 0
+#define B200R_PATH_SCAN 1
+#define B200R_PATH_GEMM 2
+
+typedef struct b200r_index b200r_index; /* opaque */
+
+typedef struct b200r_config {
+    int32_t dim;               /* IndexFlat(d) */
+    int32_t metric;            /* B200R_METRIC_* */
+    int32_t storage;           /* B200R_F32 (exact mode) or B200R_BF16 (recall mode) */
+    int32_t normalize_on_add;  /* fuse faiss.normalize_L2 into ingest (LangChain normalize_L2=True,
+                                  rag_service.py:194) */
+    int32_t normalize_queries; /* same for queries (rag_service.py:292) */
+    int32_t device;            /* CUDA device ordinal */
+    int32_t search_path;       /* B200R_PATH_* */
+    int32_t reserved0;
+    int64_t reserve_rows;      /* HBM reserved up front (0 = grow on demand) */
+    int64_t id_base;           /* added to every returned id: global position of local row 0
+                                  when the corpus is row-sharded over several GPUs */
+} b200r_config;
+
+typedef struct b200r_stats {
+    int64_t ntotal;
+    int64_t capacity_rows;
+    int64_t n_search_calls;
+    int64_t n_queries;
+    int64_t n_kernel_launches;   /* kernels of this library launched so far */
+    int64_t bytes_scanned;       /* algorithmic corpus bytes streamed by searches */
+    int64_t n_rows_added;
+    int64_t n_rows_removed;
+    int32_t last_grid;           /* CTAs of the last scoring launch */
+    int32_t last_path;           /* B200R_PATH_SCAN / B200R_PATH_GEMM */
+    int32_t num_sms;
+    int32_t reserved0;
+    double last_search_ms;       /* device time of the last search (events), 0 if timing is off */
+} b200r_stats;
+
+/* faiss.IndexFlatL2(d) / IndexFlatIP(d)   [utils.py:306; rag_service.py:88] */
+int b200r_create(const b200r_config* cfg, b200r_index** out);
+int b200r_destroy(b200r_index* idx); /* NULL is a no-op */
+
+/* IndexFlat.add(x)  -- faiss replacement_add: x is (n, d) C-contiguous; appended in
+ * order, row i of the call gets position ntotal+i.   [langchain FAISS.__add ->
+ * chains.py:83; rag_service.py:197,450].   dtype: element type of x (B200R_F32 only for
+ * host input).  stream: a cudaStream_t for DEVICE input (work is ordered on it), or
+ * NULL for the index's own stream.  HOST input may be pageable; the call returns when
+ * x has been consumed. */
+int b200r_add(b200r_index* idx, const void* x, int64_t n, int dtype, int mem_kind, void* stream);
+
+/* IndexFlat.search(x, k) -- faiss replacement_search: q is (nq, d) fp32; D is (nq, k)
+ * fp32, I is (nq, k) int64, both caller-allocated.  L2 returns squared distances
+ * ascending, IP dot products descending; when k > ntotal the tail is id -1 with
+ * +FLT_MAX (L2) / -FLT_MAX (IP).  Ties are broken by lowest id.
+ * [langchain FAISS.similarity_search_with_score_by_vector -> chains.py:163,211;
+ * rag_service.py:301].  q and D/I may independently live on the host or the device;
+ * with device outputs the call is asynchronous on `stream`. */
+int b200r_search(b200r_index* idx, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
+                 int out_mem_kind, void* stream);
+
+/* IndexFlat.remove_ids(ids) -- IDSelectorBatch semantics: positions in ids are
+ * removed, later rows shift down (stable), duplicates / out-of-range ignored.
+ * [langchain FAISS.delete -> utils.py:559].  ids is a host array. */
+int b200r_remove_ids(b200r_index* idx, const int64_t* ids, int64_t n, int64_t* n_removed);
+
+/* IndexFlat.ntotal */
+int b200r_ntotal(const b200r_index* idx, int64_t* out);
+
+/* IndexFlat.reconstruct(key): the stored row as fp32 into a host buffer of d floats */
+int b200r_reconstruct(b200r_index* idx, int64_t key, float* out);
+
+/* IndexFlat.reset() */
+int b200r_reset(b200r_index* idx);
+
+/* faiss.normalize_L2(x): in place on (n, d) fp32, host or device memory.
+ * [rag_service.py:194,292,439; langchain FAISS with normalize_L2=True] */
+int b200r_normalize_l2(float* x, int64_t n, int32_t d, int mem_kind, int32_t device, void* stream);
+
+/* faiss.write_index / faiss.read_index for flat indexes ("IxF2" / "IxFI" files, the
+ * index.faiss that LangChain FAISS.save_local/load_local writes).
+ * [community/llm-prompt-design-helper/vector_store/faiss_vector_store.py:124-133;
+ * rag_service.py:364-422].  cfg->dim/metric are taken from the file on load. */
+int b200r_save(b200r_index* idx, const char* path);
+int b200r_load(const char* path, const b200r_config* cfg, b200r_index** out);
+
+/* No faiss counterpart: the final select of the multi-GPU search.  The NCCL-allgathered
+ * per-shard results sit in DEVICE memory as n_lists blocks in rank order; block l holds
+ * scores [nq][k_in] at cand_D + l*stride_D (floats) and ids [nq][k_in] at
+ * cand_I + l*stride_I (int64s).  Writes the k_out best per query to DEVICE arrays D / I
+ * ([nq][k_out]); ids < 0 are padding and are skipped; ties go to the lower rank. */
+int b200r_merge_topk(int32_t metric, const float* cand_D, const int64_t* cand_I, int64_t nq, int32_t n_lists,
+                     int32_t k_in, int64_t stride_D, int64_t stride_I, int32_t k_out, float* D, int64_t* I,
+                     int32_t device, void* stream);
+
+/* row-sharding support: change the id offset after the shard layout moved */
+int b200r_set_id_base(b200r_index* idx, int64_t id_base);
+
+/* observability (no faiss counterpart) */
+int b200r_stats_get(b200r_index* idx, b200r_stats* out);
+int b200r_set_timing(b200r_index* idx, int32_t enabled);
+
+const char* b200r_last_error(void);
+int b200r_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200R_H */

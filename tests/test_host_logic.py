@@ -1,0 +1,173 @@
+"""CPU suite, part 3: the host-side mirror of the LangChain surface, with the CPU oracle
+injected as the index object (the product never does that itself).  The same call sequence
+runs through oracle.lc_faiss_shim.RefFAISS and B200FlatVectorStore and must agree."""
+import asyncio
+import os
+import warnings
+import zlib
+
+import numpy as np
+import pytest
+
+from generativeaiexamples_b200.factory import del_docs_vectorstore_langchain, get_docs_vectorstore_langchain
+from generativeaiexamples_b200.vectorstore import (B200FlatVectorStore, DistanceStrategy, Document, InMemoryDocstore,
+                                                   VectorStoreRetriever)
+from oracle.flat_ref import METRIC_INNER_PRODUCT, METRIC_L2, IndexFlatRef
+from oracle.lc_faiss_shim import RefDocstore, RefFAISS
+
+D = 64
+
+
+class Emb:
+    def _v(self, t):
+        rng = np.random.default_rng(zlib.crc32(t.encode()))
+        v = rng.standard_normal(D)
+        return (v / np.linalg.norm(v)).tolist()
+
+    def embed_documents(self, texts):
+        return [self._v(t) for t in texts]
+
+    def embed_query(self, t):
+        return self._v(t)
+
+
+def _pair(metric=METRIC_L2, strategy="EUCLIDEAN_DISTANCE", **kw):
+    ours = B200FlatVectorStore(Emb(), IndexFlatRef(D, metric), InMemoryDocstore(), {},
+                               distance_strategy=DistanceStrategy(strategy), **kw)
+    ref = RefFAISS(Emb(), IndexFlatRef(D, metric), RefDocstore(), {}, distance_strategy=strategy, **kw)
+    return ours, ref
+
+
+def _ingest(ours, ref, n=60):
+    texts = [f"chunk {i}" for i in range(n)]
+    metas = [{"source": f"/tmp-data/uploaded_files/doc{i % 4}.pdf"} for i in range(n)]
+    ids = [f"id-{i}" for i in range(n)]
+    assert ours.add_texts(texts, metadatas=metas, ids=list(ids)) == ids
+    assert ref.add_texts(texts, metadatas=metas, ids=list(ids)) == ids
+    return texts, ids
+
+
+def _same(a, b):
+    assert [(d.page_content, d.metadata) for d in a] == [(d.page_content, d.metadata) for d in b]
+
+
+def test_basic_rag_call_sequence():
+    """chains.py:83 (add_documents) then chains.py:156-163 (threshold retriever)."""
+    ours, ref = _pair()
+    docs = [Document(page_content=f"chunk {i}", metadata={"source": f"/x/doc{i % 3}.txt"}) for i in range(40)]
+    ours.add_documents(docs)
+    ref.add_texts([d.page_content for d in docs], [d.metadata for d in docs])
+    assert ours.index.ntotal == 40 and len(ours.docstore._dict) == 40
+    seen = []
+
+    class CB:
+        def on_retriever_start(self, serialized, query, **kw):
+            seen.append(("start", query))
+
+        def on_retriever_end(self, documents, **kw):
+            seen.append(("end", len(documents)))
+
+    retriever = ours.as_retriever(search_type="similarity_score_threshold",
+                                  search_kwargs={"score_threshold": 0.25, "k": 4})
+    assert isinstance(retriever, VectorStoreRetriever)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        got = retriever.get_relevant_documents("chunk 5", callbacks=[CB()])
+        want = ref.retrieve("chunk 5", "similarity_score_threshold", {"score_threshold": 0.25, "k": 4})
+    _same(got, want)
+    assert [d.page_content for d in got] == ["chunk 5"]
+    assert seen == [("start", "chunk 5"), ("end", 1)]
+    # fallback branch chains.py:166
+    _same(ours.as_retriever().get_relevant_documents("chunk 5"), ref.retrieve("chunk 5"))
+    _same(ours.as_retriever().invoke("chunk 9", config={"callbacks": []}), ref.retrieve("chunk 9"))
+
+
+@pytest.mark.parametrize("metric,strategy", [(METRIC_L2, "EUCLIDEAN_DISTANCE"),
+                                             (METRIC_INNER_PRODUCT, "MAX_INNER_PRODUCT")])
+def test_scores_filters_thresholds(metric, strategy):
+    ours, ref = _pair(metric, strategy)
+    _ingest(ours, ref)
+    for k in (1, 4, 25, 100):  # 100 > ntotal: -1 padding is skipped
+        a = ours.similarity_search_with_score("chunk 3", k=k)
+        b = ref.similarity_search_with_score("chunk 3", k=k)
+        _same([d for d, _ in a], [d for d, _ in b])
+        assert [float(s) for _, s in a] == [float(s) for _, s in b]
+        assert all(isinstance(s, np.float32) for _, s in a)
+    flt = {"source": "/tmp-data/uploaded_files/doc1.pdf"}
+    _same(ours.similarity_search("chunk 3", k=3, filter=flt, fetch_k=30),
+          ref.similarity_search("chunk 3", k=3, filter=flt, fetch_k=30))
+    thr = 1.0 if metric == METRIC_L2 else 0.2
+    a = ours.similarity_search_with_score_by_vector(Emb()._v("chunk 3"), k=10, score_threshold=thr)
+    b = ref.similarity_search_with_score_by_vector(Emb()._v("chunk 3"), k=10, score_threshold=thr)
+    _same([d for d, _ in a], [d for d, _ in b])
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        a = ours.similarity_search_with_relevance_scores("chunk 3", k=4, score_threshold=0.25)
+        b = ref.similarity_search_with_relevance_scores("chunk 3", k=4, score_threshold=0.25)
+    assert [(d.page_content, float(s)) for d, s in a] == [(d.page_content, float(s)) for d, s in b]
+    if metric == METRIC_L2:  # orthogonal-ish unit vectors: d ~ 2 -> relevance 1 - sqrt(2) < 0
+        assert any("Relevance scores must be between 0 and 1" in str(x.message) for x in w)
+
+
+def test_threshold_boundary_is_inclusive():
+    ours, _ = _pair(relevance_score_fn=lambda d: 0.25)
+    ours.add_texts(["a", "b"])
+    assert len(ours.similarity_search_with_relevance_scores("a", k=2, score_threshold=0.25)) == 2
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        assert ours.similarity_search_with_relevance_scores("a", k=2, score_threshold=0.2500001) == []
+    assert any("No relevant docs were retrieved" in str(x.message) for x in w)
+
+
+def test_retriever_validation():
+    ours, _ = _pair()
+    with pytest.raises(ValueError):
+        ours.as_retriever(search_type="similarity_score_threshold", search_kwargs={"k": 4})
+    with pytest.raises(ValueError):
+        ours.as_retriever(search_type="similarity_score_threshold", search_kwargs={"score_threshold": 1, "k": 4})
+    with pytest.raises(ValueError):
+        ours.as_retriever(search_type="nearest")
+
+
+def test_delete_and_docstore_helpers():
+    """utils.py:506-510 (list) and :546-560 (delete by file name)."""
+    ours, ref = _pair()
+    texts, ids = _ingest(ours, ref)
+    assert sorted(get_docs_vectorstore_langchain(ours)) == [f"doc{i}.pdf" for i in range(4)]
+    assert del_docs_vectorstore_langchain(ours, ["doc2.pdf"]) is True
+    ref.delete([i for n, i in enumerate(ids) if n % 4 == 2])
+    assert ours.index.ntotal == ref.index.ntotal == 45
+    assert ours.index_to_docstore_id == ref.index_to_docstore_id
+    assert del_docs_vectorstore_langchain(ours, ["missing.pdf"]) is False
+    _same(ours.similarity_search("chunk 7", k=5), ref.similarity_search("chunk 7", k=5))
+    with pytest.raises(ValueError):
+        ours.delete(["not-there"])
+    with pytest.raises(ValueError):
+        ours.delete(None)
+    with pytest.raises(ValueError):  # duplicate id on add
+        ours.add_texts(["again"], ids=[ids[0]])
+
+
+def test_add_embeddings_and_async():
+    ours, ref = _pair()
+    e = Emb()
+    pairs = [(f"t{i}", e._v(f"t{i}")) for i in range(20)]
+    ours.add_embeddings(pairs, ids=[f"i{i}" for i in range(20)])
+    ref.add_embeddings(pairs, ids=[f"i{i}" for i in range(20)])
+    v = e._v("t4")
+    _same(ours.similarity_search_by_vector(v, k=3), ref.similarity_search_by_vector(v, k=3))
+
+    async def go():  # faiss_vdb_service.py:169-174: gather of per-query async searches
+        return await asyncio.gather(*[ours.asimilarity_search_by_vector(e._v(f"t{i}"), k=2) for i in range(5)])
+
+    res = asyncio.run(go())
+    assert [r[0].page_content for r in res] == [f"t{i}" for i in range(5)]
+    Dm, Im = ours.search_by_vectors(np.array([e._v(f"t{i}") for i in range(5)], dtype=np.float32), k=2)
+    assert Im[:, 0].tolist() == list(range(5))
+
+
+def test_empty_store_and_bad_embedding_function(caplog):
+    vs = B200FlatVectorStore(lambda t: [0.0] * D, None)
+    assert vs.similarity_search_with_score_by_vector([0.0] * D) == []
+    with pytest.raises(NotImplementedError):
+        vs.max_marginal_relevance_search("q")

@@ -1,0 +1,119 @@
+"""CPU suite, part 4: the N>1 host logic over gloo, world_size 2 and 3 (row blocks, id
+offsets, packed allgather layout, merge ordering).  The two device steps are replaced by
+the CPU oracle, which is allowed in tests only."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from generativeaiexamples_b200.sharded import ShardedFlatIndex, _packed_layout, shard_bounds
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+class _LocalRef:
+    """IndexFlatRef + the id_base the device index applies in its epilogue."""
+
+    def __init__(self, d, metric):
+        from oracle.flat_ref import IndexFlatRef
+
+        self.ix, self.base = IndexFlatRef(d, metric), 0
+
+    ntotal = property(lambda self: self.ix.ntotal)
+
+    def add(self, x):
+        self.ix.add(np.asarray(x, dtype=np.float32))
+
+    def set_id_base(self, b):
+        self.base = b
+
+    def search(self, q, k):
+        D, I = self.ix.search(q, k)
+        return D, np.where(I >= 0, I + self.base, -1)
+
+
+def _merge_ref(metric, cand_d, cand_i, k):
+    """[G][nq][k] -> [nq][k]; same rule as the K4 kernel: skip id<0, ties to the lower rank."""
+    G, nq, kin = cand_d.shape
+    D = np.full((nq, k), np.finfo(np.float32).max if metric == 1 else -np.finfo(np.float32).max, dtype=np.float32)
+    I = np.full((nq, k), -1, dtype=np.int64)
+    for qi in range(nq):
+        d = cand_d[:, qi, :].reshape(-1)
+        i = cand_i[:, qi, :].reshape(-1)
+        pos = np.arange(d.size)
+        ok = i >= 0
+        d, i, pos = d[ok], i[ok], pos[ok]
+        order = np.lexsort((pos, d if metric == 1 else -d))[:k]
+        D[qi, : len(order)] = d[order]
+        I[qi, : len(order)] = i[order]
+    return D, I
+
+
+def _worker(rank, world, port, metric, n, nq, k, q_out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(5)
+        d = 32
+        x = rng.standard_normal((n, d), dtype=np.float32)
+        q = rng.standard_normal((nq, d), dtype=np.float32)
+        idx = ShardedFlatIndex(d, metric, local_index=_LocalRef(d, metric), merge_fn=_merge_ref)
+        idx.add(x)
+        lo, hi = shard_bounds(n, world, rank)
+        assert idx.local.ntotal == hi - lo and idx.id_base == lo and idx.ntotal == n
+        D, I = idx.search(q, k)
+        if rank == 0:
+            q_out.put((D, I))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("metric", [0, 1])
+def test_sharded_search_matches_single_index(world, metric):
+    from oracle import FlatRef
+
+    n, nq, k = 1001, 5, 10
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, metric, n, nq, k, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    D, I = out.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((n, 32), dtype=np.float32)
+    q = rng.standard_normal((nq, 32), dtype=np.float32)
+    Dr, Ir = FlatRef.knn(metric, q, x, k)
+    np.testing.assert_array_equal(I, Ir)
+    np.testing.assert_allclose(D, Dr, rtol=1e-6)
+
+
+def test_shard_bounds_and_layout():
+    assert [shard_bounds(10, 4, r) for r in range(4)] == [(0, 3), (3, 6), (6, 9), (9, 10)]
+    assert [shard_bounds(2, 4, r) for r in range(4)] == [(0, 1), (1, 2), (2, 2), (2, 2)]
+    assert shard_bounds(0, 2, 1) == (0, 0)
+    d_bytes, block = _packed_layout(1, 10)
+    assert d_bytes == 40 and block == 120
+    d_bytes, block = _packed_layout(3, 3)  # 36 -> padded to 40 so the ids stay 8-byte aligned
+    assert d_bytes == 40 and block == 40 + 72
+
+
+def test_single_process_world1():
+    idx = ShardedFlatIndex(8, 1, local_index=_LocalRef(8, 1), merge_fn=_merge_ref)
+    x = np.eye(8, dtype=np.float32)
+    idx.add(x)
+    D, I = idx.search(x[:2], 3)
+    assert I[:, 0].tolist() == [0, 1] and idx.ntotal == 8
