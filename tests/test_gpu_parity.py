@@ -1,0 +1,347 @@
+"""GPU suite: parity of the CUDA path (through the C ABI) with the oracle.
+
+Bar (BASELINE.json north_star): fp32 mode -- top-k ids identical to the reference's except
+ties within 1e-5 relative score, scores within 1e-5 (abs-or-rel, oracle/compare.py);
+integer outputs (ids, ntotal, remove_ids) bit-exact.  bf16 corpus mode: recall@k.
+"""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+FLT_MAX = np.finfo(np.float32).max
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(os.path.join(HERE, "golden", "seeded_topk.npz"))
+
+
+def _mk(metric, d, **kw):
+    from generativeaiexamples_b200 import B200IndexFlat
+
+    return B200IndexFlat(d, 1 if metric == "l2" else 0, **kw)
+
+
+def _check(metric, D, I, q, x, k, what):
+    from oracle import FlatRef, assert_topk_parity, truth_topk
+
+    Dt, It = truth_topk(metric, q, x, k + 8)
+    assert_topk_parity(D, I, Dt, It, what=what + " vs f64 truth")
+    Dr, Ir = FlatRef.knn(1 if metric == "l2" else 0, q, x, k)
+    assert_topk_parity(D, I, Dr, Ir, what=what + " vs faiss restatement")
+    # structural: sorted best-first
+    s = D if metric == "l2" else -D
+    assert (np.diff(s, axis=1) >= 0).all(), what + ": scores not sorted"
+
+
+def test_kat_through_abi(built_lib):
+    import json
+
+    kat = json.load(open(os.path.join(HERE, "golden", "kat_d4.json")))
+    for case in kat["cases"]:
+        ix = _mk(case["metric"], 4)
+        ix.add(np.array(case["corpus"], dtype=np.float32))
+        D, I = ix.search(np.array([case["query"]], dtype=np.float32), case["k"])
+        pad = FLT_MAX if case["metric"] == "l2" else -FLT_MAX
+        np.testing.assert_array_equal(I[0], np.array(case["ids"]), err_msg=case["name"])
+        np.testing.assert_array_equal(D[0], np.array([pad if s is None else s for s in case["scores"]],
+                                                     dtype=np.float32), err_msg=case["name"])
+        ix.close()
+    # normalize_L2 and remove_ids known answers
+    from generativeaiexamples_b200 import normalize_L2
+
+    x = np.array(kat["normalize"]["rows"], dtype=np.float32)
+    normalize_L2(x)
+    np.testing.assert_allclose(x, np.array(kat["normalize"]["expect"], dtype=np.float32), rtol=1e-6, atol=0)
+    r = kat["remove_ids"]
+    ix = _mk("l2", 4)
+    ix.add(np.array(r["rows"], dtype=np.float32))
+    assert ix.remove_ids(np.array(r["ids"], dtype=np.int64)) == r["n_removed"]
+    assert ix.ntotal == len(r["expect"])
+    for i, row in enumerate(r["expect"]):
+        np.testing.assert_array_equal(ix.reconstruct(i), np.array(row, dtype=np.float32))
+    ix.close()
+
+
+def test_golden_fixtures(built_lib, gold):
+    """Committed float64 results generated before any kernel existed."""
+    from oracle import assert_topk_parity
+    from tests.golden.make_fixtures import CASES, make_case
+
+    for name, (n, d, nq, k, metric, normalized, seed) in CASES.items():
+        x, q = make_case(*CASES[name])
+        ix = _mk(metric, d)
+        ix.add(x)
+        D, I = ix.search(q, k)
+        assert_topk_parity(D, I, gold[name + "__D"], gold[name + "__I"], what=name)
+        ix.close()
+
+
+@pytest.mark.parametrize("metric", ["ip", "l2"])
+@pytest.mark.parametrize("d", [1024, 384, 100, 4, 2048])
+def test_scan_parity_dims(built_lib, metric, d):
+    rng = np.random.default_rng(d)
+    n = 30011 if d <= 1024 else 9001  # ragged: not a multiple of the tile height
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    q = rng.standard_normal((6, d), dtype=np.float32)
+    q[::2] = x[rng.integers(0, n, 3)] + 0.05 * q[::2]
+    ix = _mk(metric, d)
+    ix.add(x)
+    assert ix.ntotal == n
+    for nq, k in ((1, 1), (1, 10), (3, 4), (4, 32), (6, 33), (2, 128)):
+        D, I = ix.search(q[:nq], k)
+        _check(metric, D, I, q[:nq], x, k, f"{metric} d={d} nq={nq} k={k}")
+    ix.close()
+
+
+@pytest.mark.parametrize("metric", ["ip", "l2"])
+def test_edge_cases(built_lib, metric):
+    d = 64
+    ix = _mk(metric, d)
+    pad = FLT_MAX if metric == "l2" else -FLT_MAX
+    # empty index: all padding (faiss: heap initial values)
+    D, I = ix.search(np.ones((2, d), dtype=np.float32), 5)
+    assert (I == -1).all() and (D == pad).all()
+    # fewer rows than k; incremental adds keep positions
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((7, d), dtype=np.float32)
+    ix.add(x[:3])
+    ix.add(x[3:])
+    D, I = ix.search(x[:1], 10)
+    assert (I[0, 7:] == -1).all() and (D[0, 7:] == pad).all() and sorted(I[0, :7].tolist()) == list(range(7))
+    _check(metric, D[:, :7], I[:, :7], x[:1], x, 7, f"{metric} k>ntotal")
+    # exact duplicates: ties resolved by lowest id
+    ix.reset()
+    assert ix.ntotal == 0
+    dup = np.repeat(x[:1], 50, axis=0)
+    ix.add(dup)
+    D, I = ix.search(x[:1], 10)
+    assert I[0].tolist() == list(range(10)) and len(set(D[0].tolist())) == 1
+    # argument errors mirror the faiss wrapper
+    with pytest.raises(AssertionError):
+        ix.search(np.ones((1, d + 1), dtype=np.float32), 3)
+    with pytest.raises(AssertionError):
+        ix.search(np.ones((1, d), dtype=np.float32), 0)
+    with pytest.raises(AssertionError):
+        ix.add(np.ones((1, d - 1), dtype=np.float32))
+    with pytest.raises(RuntimeError):
+        ix.reconstruct(10 ** 6)
+    ix.close()
+
+
+def test_remove_ids_parity(built_lib):
+    from oracle.flat_ref import IndexFlatRef
+
+    rng = np.random.default_rng(9)
+    n, d = 50000, 128
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    ix, ref = _mk("l2", d), IndexFlatRef(d, 1)
+    ix.add(x)
+    ref.add(x)
+    for ids in (np.array([0]), np.array([n - 2]), rng.integers(0, n, 5000), np.arange(100, 20000, 3),
+                np.array([-5, 10 ** 9])):
+        ids = ids.astype(np.int64)
+        assert ix.remove_ids(ids) == ref.remove_ids(ids)
+        assert ix.ntotal == ref.ntotal
+        for key in (0, 1, ref.ntotal // 2, ref.ntotal - 1):
+            np.testing.assert_array_equal(ix.reconstruct(key), ref.reconstruct(key))
+        q = x[rng.integers(0, n, 2)]
+        D, I = ix.search(q, 5)
+        Dr, Ir = ref.search(q, 5)
+        np.testing.assert_array_equal(I, Ir)
+    ix.close()
+
+
+def test_normalize_fused_and_standalone(built_lib):
+    """C5: ingest-time normalisation + normalised queries (rag_service.py:194,292)."""
+    from generativeaiexamples_b200 import B200IndexFlat, normalize_L2
+    from oracle import FlatRef
+
+    rng = np.random.default_rng(21)
+    n, d = 20000, 1024
+    x = (rng.standard_normal((n, d), dtype=np.float32) * rng.uniform(0.1, 10, (n, 1)).astype(np.float32))
+    x[17] = 0  # zero row stays zero
+    q = x[rng.integers(0, n, 3)] + 0.1 * rng.standard_normal((3, d), dtype=np.float32)
+    xn, qn = x.copy(), q.copy()
+    FlatRef.normalize_L2(xn)
+    FlatRef.normalize_L2(qn)
+    x2 = x.copy()
+    normalize_L2(x2)
+    np.testing.assert_allclose(x2, xn, rtol=2e-6, atol=1e-9)
+    ix = B200IndexFlat(d, 1, normalize_on_add=True, normalize_queries=True)
+    ix.add(x)
+    np.testing.assert_allclose(ix.reconstruct(5), xn[5], rtol=2e-6, atol=1e-9)
+    assert not ix.reconstruct(17).any()
+    D, I = ix.search(q, 10)
+    _check("l2", D, I, qn, xn, 10, "fused normalise")
+    ix.close()
+
+
+def test_device_tensors_roundtrip(built_lib):
+    """torch hand-off: CUDA tensors in, CUDA tensors out, on the current stream."""
+    import torch
+
+    rng = np.random.default_rng(33)
+    n, d = 40000, 1024
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    q = x[:4] + 0.01
+    ix = _mk("ip", d)
+    ix.add(torch.from_numpy(x).cuda())
+    D, I = ix.search(torch.from_numpy(q).cuda(), 10)
+    assert D.is_cuda and I.is_cuda and I.dtype == torch.int64
+    _check("ip", D.cpu().numpy(), I.cpu().numpy(), q, x, 10, "device tensors")
+    Dh, Ih = ix.search(q, 10)
+    np.testing.assert_array_equal(Ih, I.cpu().numpy())
+    np.testing.assert_array_equal(Dh, D.cpu().numpy())
+    ix.close()
+
+
+def test_bf16_recall(built_lib):
+    """Optional bf16 corpus mode: reported as recall@k against the fp32 truth."""
+    from oracle import recall_at_k, truth_topk
+
+    rng = np.random.default_rng(44)
+    n, d, k = 50000, 1024, 100
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    q = x[rng.integers(0, n, 4)] + 0.3 * rng.standard_normal((4, d), dtype=np.float32) / np.sqrt(d)
+    ix = _mk("ip", d, storage="bf16")
+    ix.add(x)
+    D, I = ix.search(q, k)
+    _, It = truth_topk("ip", q, x, k)
+    r = recall_at_k(I, It)
+    assert r >= 0.95, r
+    # and exact w.r.t. the bf16-rounded corpus it actually stores
+    import torch
+
+    xb = torch.from_numpy(x).to(torch.bfloat16).to(torch.float32).numpy()
+    np.testing.assert_array_equal(ix.reconstruct(123), xb[123])
+    _check("ip", D, I, q, xb, k, "bf16 storage vs rounded corpus")
+    ix.close()
+
+
+def test_save_load_faiss_file(built_lib, tmp_path):
+    import struct
+
+    from generativeaiexamples_b200 import B200IndexFlat
+
+    rng = np.random.default_rng(55)
+    x = rng.standard_normal((3000, 100), dtype=np.float32)
+    ix = _mk("l2", 100)
+    ix.add(x)
+    p = str(tmp_path / "index.faiss")
+    ix.write(p)
+    raw = open(p, "rb").read()
+    assert raw[:4] == b"IxF2"
+    d, nt, _, _, trained, metric, nfl = struct.unpack("<iqqqBiQ", raw[4:4 + 4 + 8 + 8 + 8 + 1 + 4 + 8])
+    assert (d, nt, trained, metric, nfl) == (100, 3000, 1, 1, 300000)
+    np.testing.assert_array_equal(np.frombuffer(raw[45:], dtype=np.float32).reshape(3000, 100), x)
+    ix2 = B200IndexFlat.read(p)
+    assert ix2.ntotal == 3000 and ix2.d == 100 and ix2.metric_type == 1
+    D1, I1 = ix.search(x[:3], 5)
+    D2, I2 = ix2.search(x[:3], 5)
+    np.testing.assert_array_equal(I1, I2)
+    np.testing.assert_array_equal(D1, D2)
+    ix.close()
+    ix2.close()
+
+
+def test_concurrent_searches(built_lib):
+    """faiss_vdb_service.py:169-174: B threads each running an nq=1 search."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    rng = np.random.default_rng(66)
+    n, d = 30000, 256
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    ix = _mk("l2", d)
+    ix.add(x)
+    rows = rng.integers(0, n, 32)
+    with ThreadPoolExecutor(8) as ex:
+        res = list(ex.map(lambda r: ix.search(x[r:r + 1], 3)[1][0, 0], rows))
+    assert res == rows.tolist()
+    ix.close()
+
+
+def test_vectorstore_end_to_end(built_lib):
+    """basic_rag call sequence on the real engine against the LangChain restatement."""
+    import warnings
+    import zlib
+
+    from generativeaiexamples_b200 import B200FlatVectorStore, create_vectorstore_langchain
+    from oracle.flat_ref import IndexFlatRef
+    from oracle.lc_faiss_shim import RefDocstore, RefFAISS
+
+    d = 1024
+
+    class Emb:
+        def _v(self, t):
+            r = np.random.default_rng(zlib.crc32(t.encode()))
+            base = r.standard_normal(d)
+            if t.startswith("about "):  # a query near its document: cos ~ 0.8
+                base = np.asarray(Emb()._v(t[6:])) + 0.75 * base / np.linalg.norm(base)
+            return (base / np.linalg.norm(base)).astype(np.float32).tolist()
+
+        def embed_documents(self, texts):
+            return [self._v(t) for t in texts]
+
+        def embed_query(self, t):
+            return self._v(t)
+
+    vs = create_vectorstore_langchain(Emb(), name="b200flat", dimensions=d)
+    assert isinstance(vs, B200FlatVectorStore)
+    ref = RefFAISS(Emb(), IndexFlatRef(d, 1), RefDocstore(), {})
+    texts = [f"chunk {i}" for i in range(300)]
+    metas = [{"source": f"/tmp-data/uploaded_files/f{i % 6}.pdf"} for i in range(300)]
+    ids = [f"id{i}" for i in range(300)]
+    vs.add_texts(texts, metas, ids=list(ids))
+    ref.add_texts(texts, metas, ids=list(ids))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        for query in ("chunk 5", "about chunk 17", "nothing like it"):
+            r = vs.as_retriever(search_type="similarity_score_threshold", search_kwargs={"score_threshold": 0.25, "k": 4})
+            got = r.get_relevant_documents(query)
+            want = ref.retrieve(query, "similarity_score_threshold", {"score_threshold": 0.25, "k": 4})
+            assert [g.page_content for g in got] == [w.page_content for w in want], query
+            a = vs.similarity_search_with_score(query, k=25)
+            b = ref.similarity_search_with_score(query, k=25)
+            assert [x.page_content for x, _ in a] == [x.page_content for x, _ in b]
+            np.testing.assert_allclose([s for _, s in a], [s for _, s in b], rtol=1e-5, atol=1e-5)
+    assert [g.page_content for g in vs.as_retriever().get_relevant_documents("about chunk 17")][0] == "chunk 17"
+    vs.delete([ids[17], ids[5]])
+    ref.delete([ids[17], ids[5]])
+    assert vs.index.ntotal == 298 and vs.index_to_docstore_id == ref.index_to_docstore_id
+    a = vs.similarity_search("about chunk 18", k=3)
+    b = ref.similarity_search("about chunk 18", k=3)
+    assert [x.page_content for x in a] == [x.page_content for x in b]
+
+
+def test_merge_kernel(built_lib):
+    """K4 against a numpy merge with the same tie rule."""
+    import torch
+
+    from generativeaiexamples_b200 import _lib
+    from tests.test_sharded_gloo import _merge_ref
+
+    rng = np.random.default_rng(77)
+    for metric, G, nq, k in ((0, 8, 1, 10), (1, 4, 5, 33), (0, 2, 256, 10), (1, 8, 3, 128)):
+        cd = rng.standard_normal((G, nq, k)).astype(np.float32)
+        cd = np.sort(cd, axis=2) if metric == 1 else -np.sort(-cd, axis=2)
+        cd[:, :, 1] = cd[:, :, 0]  # force ties
+        ci = rng.permutation(G * nq * k).reshape(G, nq, k).astype(np.int64)
+        ci[-1, :, k - 2:] = -1  # padding in the last shard
+        De, Ie = _merge_ref(metric, cd, ci, k)
+        tcd, tci = torch.from_numpy(cd).cuda(), torch.from_numpy(ci).cuda()
+        D = torch.empty((nq, k), dtype=torch.float32, device="cuda")
+        I = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+        _lib.check(built_lib.b200r_merge_topk(metric, ctypes.c_void_p(tcd.data_ptr()), ctypes.c_void_p(tci.data_ptr()),
+                                              nq, G, k, nq * k, nq * k, k, ctypes.c_void_p(D.data_ptr()),
+                                              ctypes.c_void_p(I.data_ptr()), 0,
+                                              ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        torch.cuda.synchronize()
+        np.testing.assert_array_equal(I.cpu().numpy(), Ie)
+        np.testing.assert_array_equal(D.cpu().numpy(), De)
