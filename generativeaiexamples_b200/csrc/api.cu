@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -279,7 +280,9 @@ extern "C" int b200r_add(b200r_index* ix, const void* x, int64_t n, int dtype, i
     if (mem_kind != B200R_HOST && mem_kind != B200R_DEVICE) return fail(B200R_E_INVALID, "b200r_add: bad mem_kind");
     std::lock_guard<std::mutex> lk(ix->mu);
     DeviceGuard g(ix->device);
-    cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
+    // device input: ordered on the caller's stream exactly as given (NULL is CUDA's default
+    // stream, e.g. torch's); host input: the index's own non-blocking stream unless told otherwise
+    cudaStream_t st = (mem_kind == B200R_DEVICE || stream) ? (cudaStream_t)stream : ix->stream;
     int rc = ensure_capacity(ix, ix->ntotal + n, st);
     if (rc != B200R_OK) return rc;
     const bool norm = ix->cfg.normalize_on_add != 0;
@@ -367,7 +370,8 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
 
     std::lock_guard<std::mutex> lk(ix->mu);
     DeviceGuard g(ix->device);
-    cudaStream_t st = stream ? (cudaStream_t)stream : ix->stream;
+    const bool any_dev = q_mem_kind == B200R_DEVICE || out_mem_kind == B200R_DEVICE;
+    cudaStream_t st = (any_dev || stream) ? (cudaStream_t)stream : ix->stream;
     const int64_t nq_slots = round_up(nq, kScanMaxNQ);
     int rc = ensure_search_ws(ix, nq_slots, nq, k);
     if (rc != B200R_OK) return rc;
@@ -392,6 +396,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     p.row_bytes = ix->row_bytes;
     p.k = k;
     p.evict_first = ((size_t)ix->ntotal * ix->row_bytes > (size_t)96 << 20) ? 1 : 0;
+    if (const char* ev = getenv("B200R_EVICT_FIRST")) p.evict_first = atoi(ev);  // tuning knob
     p.scratch = ix->scratch;
     p.counter = ix->counter;
     p.id_base = ix->cfg.id_base;

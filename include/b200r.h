@@ -97,9 +97,10 @@ int b200r_destroy(b200r_index* idx); /* NULL is a no-op */
 /* IndexFlat.add(x)  -- faiss replacement_add: x is (n, d) C-contiguous; appended in
  * order, row i of the call gets position ntotal+i.   [langchain FAISS.__add ->
  * chains.py:83; rag_service.py:197,450].   dtype: element type of x (B200R_F32 only for
- * host input).  stream: a cudaStream_t for DEVICE input (work is ordered on it), or
- * NULL for the index's own stream.  HOST input may be pageable; the call returns when
- * x has been consumed. */
+ * host input).  stream: with DEVICE input the work is ordered on this cudaStream_t exactly
+ * as given (NULL = CUDA's default stream, which is also torch's default); with HOST input
+ * NULL selects the index's own non-blocking stream.  HOST input may be pageable; the call
+ * returns when x has been consumed. */
 int b200r_add(b200r_index* idx, const void* x, int64_t n, int dtype, int mem_kind, void* stream);
 
 /* IndexFlat.search(x, k) -- faiss replacement_search: q is (nq, d) fp32; D is (nq, k)
@@ -108,7 +109,8 @@ int b200r_add(b200r_index* idx, const void* x, int64_t n, int dtype, int mem_kin
  * +FLT_MAX (L2) / -FLT_MAX (IP).  Ties are broken by lowest id.
  * [langchain FAISS.similarity_search_with_score_by_vector -> chains.py:163,211;
  * rag_service.py:301].  q and D/I may independently live on the host or the device;
- * with device outputs the call is asynchronous on `stream`. */
+ * with device outputs the call is asynchronous on `stream`.  Stream rule as for add():
+ * if any buffer is DEVICE memory the given stream is used as is (NULL = default stream). */
 int b200r_search(b200r_index* idx, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
                  int out_mem_kind, void* stream);
 
