@@ -31,6 +31,10 @@ static int fail(int code, const char* fmt, ...) {
     return code;
 }
 
+namespace b200r {
+void set_last_error(const char* msg) { g_err = msg ? msg : ""; }
+}  // namespace b200r
+
 #define CU(call)                                                                                     \
     do {                                                                                             \
         cudaError_t e__ = (call);                                                                    \

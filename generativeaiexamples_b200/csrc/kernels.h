@@ -52,6 +52,9 @@ cudaError_t launch_merge(bool l2, const float* cand_d, const int64_t* cand_i, in
                          int64_t stride_d, int64_t stride_i, int k_out, float* out_d, int64_t* out_i,
                          cudaStream_t st);
 
+// lets entry points outside api.cu fill b200r_last_error()
+void set_last_error(const char* msg);
+
 // reconstruct helper: corpus row -> fp32
 cudaError_t launch_row_to_f32(const void* row, int d, bool bf16, float* out, cudaStream_t st);
 

@@ -294,3 +294,160 @@ cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, s
 }
 
 }  // namespace b200r
+
+// ===========================================================================
+// b200r_search_noalloc -- the scan search for callers that must not allocate.
+//
+// Who needs this: a caller whose device memory is already spoken for -- an inference
+// server that handed the whole HBM to its own pool at start-up, so a cudaMalloc from a
+// plug-in either fails or eats into someone else's budget -- and a caller inside a
+// latency-critical serving loop, where cudaMalloc / cudaFree stall every stream of the
+// device while they run.  b200r_search needs an index object, and that object owns
+// cudaMalloc'ed workspace.  This entry point owns nothing: the corpus, the queries and
+// the result arrays are the caller's device buffers, and the only extra global memory the
+// kernel touches (the per-CTA candidate lists, the finish ticket and the zero-padded query
+// slots) lives in the file-scope array below, which is part of the loaded module.
+//
+// Cost and limits of that choice: every GPU that loads libb200r.so carries the array
+// (672,000 bytes) until the process exits; sizes are capped at what it was laid out for
+// (dim <= 4096, nq <= 4, k <= 128, at most 148 CTAs); and there is exactly one array per
+// device, so two calls whose kernels overlap on the same GPU (different streams or
+// threads) race on it -- callers must serialise them.  The array keeps whatever the last
+// call left; the ticket and the query slots are cleared on the stream before each launch,
+// the candidate lists are fully rewritten by every launch before they are read.
+//
+// The first call on a device looks up the array's device address (cudaGetSymbolAddress
+// with that device current; in host code the symbol's name is only a stand-in, not an
+// address the GPU can use) and reads two device attributes.  Make that first call before
+// any stream capture begins.
+// ===========================================================================
+#include "../../include/b200r.h"
+#include <cstdio>
+#include <mutex>
+
+namespace b200r {
+
+constexpr int kNoAllocMaxDim = 4096;
+constexpr int kNoAllocMaxGrid = 148;
+constexpr size_t kNoAllocTicketBytes = 256;
+constexpr size_t kNoAllocCandBytes = (size_t)kNoAllocMaxGrid * kScanMaxNQ * kScanMaxK * sizeof(Cand);  // 606,208
+constexpr size_t kNoAllocQueryBytes = (size_t)kScanMaxNQ * kNoAllocMaxDim * sizeof(float);             //  65,536
+static_assert(kNoAllocCandBytes % 256 == 0, "sections of the scratch array stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocTicketBytes + kNoAllocCandBytes +
+                                                                 kNoAllocQueryBytes];
+
+struct NoAllocDevice {
+    bool ready = false;
+    unsigned char* base = nullptr;  // DEVICE address of g_noalloc_scratch on this GPU
+    int num_sms = 0;
+    size_t smem_optin = 0;
+};
+constexpr int kNoAllocMaxDevices = 64;
+static NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+static std::mutex g_noalloc_mu;
+
+// Once per device, with that device current.
+static cudaError_t noalloc_setup(int device, NoAllocDevice** out) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    NoAllocDevice& nd = g_noalloc_dev[device];
+    if (!nd.ready) {
+        unsigned char* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        int sms = 0, smem = 0;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        if (e != cudaSuccess) return e;
+        e = cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+        if (e != cudaSuccess) return e;
+        nd.base = ptr;
+        nd.num_sms = sms < kNoAllocMaxGrid ? sms : kNoAllocMaxGrid;
+        nd.smem_optin = (size_t)smem;
+        nd.ready = true;
+    }
+    *out = &nd;
+    return cudaSuccess;
+}
+
+static int noalloc_fail(int code, const char* fmt, long long a = 0, long long b = 0) {
+    char buf[512];
+    snprintf(buf, sizeof buf, fmt, a, b);
+    set_last_error(buf);
+    return code;
+}
+
+}  // namespace b200r
+
+extern "C" int b200r_search_noalloc(const void* corpus, int64_t n_rows, int32_t dim, int32_t storage, int32_t metric,
+                                    const float* q, int32_t nq, int32_t k, float* D, int64_t* I, int64_t id_base,
+                                    int32_t device, void* stream) {
+    using namespace b200r;
+    if (storage != B200R_F32 && storage != B200R_BF16)
+        return noalloc_fail(B200R_E_INVALID, "b200r_search_noalloc: storage must be B200R_F32 or B200R_BF16");
+    if (metric != B200R_METRIC_INNER_PRODUCT && metric != B200R_METRIC_L2)
+        return noalloc_fail(B200R_E_INVALID, "b200r_search_noalloc: bad metric");
+    const bool bf16 = storage == B200R_BF16;
+    if (dim <= 0 || n_rows < 0 || !q || !D || !I || (n_rows > 0 && !corpus))
+        return noalloc_fail(B200R_E_INVALID, "b200r_search_noalloc: null buffer or negative size");
+    if (dim > kNoAllocMaxDim)
+        return noalloc_fail(B200R_E_UNSUPPORTED,
+                            "b200r_search_noalloc: dim %lld exceeds the built-in scratch (max %lld); use b200r_search",
+                            dim, kNoAllocMaxDim);
+    if (nq < 1 || nq > kScanMaxNQ)
+        return noalloc_fail(B200R_E_UNSUPPORTED,
+                            "b200r_search_noalloc: nq %lld outside 1..%lld, the built-in scratch holds no more", nq,
+                            kScanMaxNQ);
+    if (k < 1 || k > kScanMaxK)
+        return noalloc_fail(B200R_E_UNSUPPORTED,
+                            "b200r_search_noalloc: k %lld outside 1..%lld, the built-in scratch holds no more", k,
+                            kScanMaxK);
+    if (dim % (bf16 ? 8 : 4) != 0 || (reinterpret_cast<uintptr_t>(corpus) & 15) != 0)
+        return noalloc_fail(B200R_E_UNSUPPORTED,
+                            "b200r_search_noalloc: rows must be 16-byte multiples at a 16-byte aligned address "
+                            "(dim %lld); there is no room to re-pack them without allocating", dim);
+    if (n_rows > 0xFFFFFFFEll) return noalloc_fail(B200R_E_UNSUPPORTED, "b200r_search_noalloc: too many rows");
+    if (device < 0 || device >= kNoAllocMaxDevices)
+        return noalloc_fail(B200R_E_INVALID, "b200r_search_noalloc: device %lld out of range", device);
+
+    int prev = -1;
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != device && cudaSetDevice(device) != cudaSuccess)
+        return noalloc_fail(B200R_E_CUDA, "b200r_search_noalloc: cudaSetDevice(%lld) failed", device);
+    cudaStream_t st = (cudaStream_t)stream;
+    NoAllocDevice* nd = nullptr;
+    cudaError_t e = noalloc_setup(device, &nd);
+    if (e == cudaSuccess) {
+        unsigned* ticket = reinterpret_cast<unsigned*>(nd->base);
+        Cand* cand = reinterpret_cast<Cand*>(nd->base + kNoAllocTicketBytes);
+        float* qslots = reinterpret_cast<float*>(nd->base + kNoAllocTicketBytes + kNoAllocCandBytes);
+        const int slots = nq <= 1 ? 1 : kScanMaxNQ;
+        // what must start at zero: the ticket (a failed earlier launch may have left it
+        // mid-count) and the query slots beyond nq
+        e = cudaMemsetAsync(ticket, 0, kNoAllocTicketBytes, st);
+        if (e == cudaSuccess) e = cudaMemsetAsync(qslots, 0, (size_t)slots * dim * sizeof(float), st);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(qslots, q, (size_t)nq * dim * sizeof(float), cudaMemcpyDeviceToDevice, st);
+        if (e == cudaSuccess) {
+            ScanParams p{};
+            p.corpus = corpus;
+            p.n_rows = n_rows;
+            p.d = dim;
+            p.row_bytes = dim * (bf16 ? 2 : 4);
+            p.q = qslots;
+            p.k = k;
+            p.evict_first = ((size_t)n_rows * p.row_bytes > (size_t)96 << 20) ? 1 : 0;
+            p.scratch = cand;
+            p.counter = ticket;
+            p.out_d = D;
+            p.out_i = I;
+            p.id_base = id_base;
+            e = launch_scan(p, nq, metric == B200R_METRIC_L2, bf16, nd->num_sms, nd->smem_optin, st, nullptr);
+        }
+    }
+    if (prev >= 0 && prev != device) cudaSetDevice(prev);
+    if (e != cudaSuccess) {
+        set_last_error(cudaGetErrorString(e));
+        return B200R_E_CUDA;
+    }
+    return B200R_OK;
+}

@@ -148,6 +148,25 @@ int b200r_merge_topk(int32_t metric, const float* cand_D, const int64_t* cand_I,
                      int32_t k_in, int64_t stride_D, int64_t stride_I, int32_t k_out, float* D, int64_t* I,
                      int32_t device, void* stream);
 
+/* Has no counterpart in the reference.  The same small-batch scan search as b200r_search,
+ * for callers that cannot allocate device memory: a plug-in inside a server that gave all
+ * of the HBM to its own pool at start-up (a cudaMalloc there fails or takes someone else's
+ * budget), or a serving loop that cannot afford the device-wide stall of cudaMalloc /
+ * cudaFree.  It takes no index object.  corpus ([n_rows][dim], fp32 or bf16, row-major),
+ * q ([nq][dim] fp32), D ([nq][k] fp32) and I ([nq][k] int64) are all the caller's DEVICE
+ * buffers; results follow b200r_search exactly (no normalisation is applied).  The kernel's
+ * scratch is a fixed 672,000-byte array built into the library -- every GPU that loads the
+ * library holds it until exit -- hence the limits, rejected with B200R_E_UNSUPPORTED and a
+ * message: dim <= 4096 and a multiple of 4 (fp32) / 8 (bf16), corpus 16-byte aligned,
+ * 1 <= nq <= 4, 1 <= k <= 128.  It calls no cudaMalloc / cudaFree or allocating routine.
+ * All calls on one GPU share that array: calls whose kernels may overlap on the GPU
+ * (different streams or threads) race and must be serialised by the caller.  The first
+ * call on each device also performs a one-time address look-up; issue it before any
+ * stream capture starts.  The work is ordered on `stream` (NULL = default stream). */
+int b200r_search_noalloc(const void* corpus, int64_t n_rows, int32_t dim, int32_t storage, int32_t metric,
+                         const float* q, int32_t nq, int32_t k, float* D, int64_t* I, int64_t id_base,
+                         int32_t device, void* stream);
+
 /* row-sharding support: change the id offset after the shard layout moved */
 int b200r_set_id_base(b200r_index* idx, int64_t id_base);
 
