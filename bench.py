@@ -313,8 +313,8 @@ def main_gpu(args):
         per = ms256 / args.batch256_steps
         flops = 2.0 * 256 * n_total * DIM
         b256 = {"value": 256 * 1000.0 / per, "unit": "queries/s", "ms_per_batch": per, "steps": args.batch256_steps,
-                "path": "scan x64 passes (tcgen05 GEMM path not built yet)" if index.local.stats()["last_path"] == 1
-                else "gemm", "achieved_tflops": flops / (per * 1e-3) / 1e12,
+                "path": "scan x64 passes" if index.local.stats()["last_path"] == 1
+                else "tcgen05 tf32 GEMM filter + exact fp32 re-score", "gemm_fallbacks": index.local.stats()["n_gemm_fallbacks"], "achieved_tflops": flops / (per * 1e-3) / 1e12,
                 "hbm_fraction_single_pass": (max_rows * DIM * 4 / (per * 1e-3) / 1e9) / peak}
 
     if rank == 0:

@@ -34,7 +34,7 @@ class Stats(ctypes.Structure):
         ("n_queries", ctypes.c_int64), ("n_kernel_launches", ctypes.c_int64), ("bytes_scanned", ctypes.c_int64),
         ("n_rows_added", ctypes.c_int64), ("n_rows_removed", ctypes.c_int64), ("last_grid", ctypes.c_int32),
         ("last_path", ctypes.c_int32), ("num_sms", ctypes.c_int32), ("reserved0", ctypes.c_int32),
-        ("last_search_ms", ctypes.c_double),
+        ("last_search_ms", ctypes.c_double), ("n_gemm_fallbacks", ctypes.c_int64),
     ]
 
     def as_dict(self):

@@ -90,6 +90,15 @@ struct b200r_index {
     int64_t out_cap = 0;  // nq*k entries allocated
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     bool timing = false;
+    // GEMM path workspace
+    void* q_bf16 = nullptr;        // bf16 copy of q_dev (bf16 corpus only), q_cap rows
+    Cand* gemm_cand = nullptr;
+    size_t gemm_cand_bytes = 0;
+    unsigned* max_norm_bits = nullptr;
+    bool max_norm_dirty = true;
+    int* fail_dev = nullptr;       // [fail_cap] flags + 1 counter at the end
+    int* fail_pin = nullptr;
+    int64_t fail_cap = 0;
 
     std::mutex mu;
     b200r_stats st{};
@@ -150,6 +159,11 @@ static void free_index(b200r_index* ix) {
     cudaFree(ix->out_d);
     cudaFree(ix->out_i);
     cudaFreeHost(ix->out_pin);
+    cudaFree(ix->q_bf16);
+    cudaFree(ix->gemm_cand);
+    cudaFree(ix->max_norm_bits);
+    cudaFree(ix->fail_dev);
+    cudaFreeHost(ix->fail_pin);
     for (auto& e : ix->add_ev)
         if (e) cudaEventDestroy(e);
     if (ix->t0) cudaEventDestroy(ix->t0);
@@ -269,6 +283,7 @@ extern "C" int b200r_reset(b200r_index* ix) {
     if (!ix) return fail(B200R_E_INVALID, "b200r_reset: null index");
     std::lock_guard<std::mutex> lk(ix->mu);
     ix->ntotal = 0;
+    ix->max_norm_dirty = true;
     return B200R_OK;
 }
 
@@ -320,6 +335,7 @@ extern "C" int b200r_add(b200r_index* ix, const void* x, int64_t n, int dtype, i
         CU(cudaStreamSynchronize(st));
     }
     ix->ntotal += n;
+    ix->max_norm_dirty = true;
     ix->st.n_rows_added += n;
     return B200R_OK;
 }
@@ -332,12 +348,15 @@ static int ensure_search_ws(b200r_index* ix, int64_t nq_slots, int64_t nq, int k
         cudaFreeHost(ix->q_pin);
         cudaFree(ix->q_raw);
         cudaFree(ix->q_dev);
+        cudaFree(ix->q_bf16);
         ix->q_pin = ix->q_raw = ix->q_dev = nullptr;
+        ix->q_bf16 = nullptr;
         ix->q_cap = 0;
-        const int64_t cap = std::max<int64_t>(nq_slots, 64);
+        const int64_t cap = std::max<int64_t>(nq_slots, 256);
         CU(cudaMallocHost(&ix->q_pin, (size_t)cap * ix->d * sizeof(float)));
         CU(cudaMalloc(&ix->q_raw, (size_t)cap * ix->d * sizeof(float)));
         CU(cudaMalloc(&ix->q_dev, (size_t)cap * ix->d_pad * sizeof(float)));
+        if (ix->bf16) CU(cudaMalloc(&ix->q_bf16, (size_t)cap * ix->d_pad * 2));
         ix->q_cap = cap;
     }
     const int64_t need = nq * k;
@@ -358,6 +377,38 @@ static int ensure_search_ws(b200r_index* ix, int64_t nq_slots, int64_t nq, int k
     return B200R_OK;
 }
 
+static int ensure_gemm_ws(b200r_index* ix, int64_t nq, int k, cudaStream_t st) {
+    const size_t need = gemm_cand_bytes(ix->num_sms, kGemmMaxBlock, gemm_kp_cap(k));
+    if (need > ix->gemm_cand_bytes) {
+        cudaFree(ix->gemm_cand);
+        ix->gemm_cand = nullptr;
+        ix->gemm_cand_bytes = 0;
+        CU(cudaMalloc(&ix->gemm_cand, need));
+        ix->gemm_cand_bytes = need;
+    }
+    if (!ix->max_norm_bits) {
+        CU(cudaMalloc(&ix->max_norm_bits, 2048));  // [0]: max norm bits; [16..272): GEMM thresholds
+        ix->max_norm_dirty = true;
+    }
+    if (ix->max_norm_dirty) {
+        CU(launch_max_norm(ix->norms, ix->ntotal, ix->max_norm_bits, st));
+        ix->st.n_kernel_launches++;
+        ix->max_norm_dirty = false;
+    }
+    if (nq > ix->fail_cap) {
+        cudaFree(ix->fail_dev);
+        cudaFreeHost(ix->fail_pin);
+        ix->fail_dev = nullptr;
+        ix->fail_pin = nullptr;
+        ix->fail_cap = 0;
+        const int64_t cap = std::max<int64_t>(nq, 1024);
+        CU(cudaMalloc(&ix->fail_dev, (size_t)(cap + 1) * sizeof(int)));
+        CU(cudaMallocHost(&ix->fail_pin, (size_t)(cap + 1) * sizeof(int)));
+        ix->fail_cap = cap;
+    }
+    return B200R_OK;
+}
+
 extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
                             int out_mem_kind, void* stream) {
     if (!ix) return fail(B200R_E_INVALID, "b200r_search: null index");
@@ -369,16 +420,24 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
         (out_mem_kind != B200R_HOST && out_mem_kind != B200R_DEVICE))
         return fail(B200R_E_INVALID, "b200r_search: bad mem_kind");
     if (k > kScanMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_search: k = %d exceeds the supported maximum %d", k, kScanMaxK);
-    if (ix->cfg.search_path == B200R_PATH_GEMM)
-        return fail(B200R_E_UNSUPPORTED, "b200r_search: the GEMM path is not built in this version");
 
     std::lock_guard<std::mutex> lk(ix->mu);
     DeviceGuard g(ix->device);
     const bool any_dev = q_mem_kind == B200R_DEVICE || out_mem_kind == B200R_DEVICE;
     cudaStream_t st = (any_dev || stream) ? (cudaStream_t)stream : ix->stream;
-    const int64_t nq_slots = round_up(nq, kScanMaxNQ);
+    // dispatch mirrors faiss (distance_compute_blas_threshold = 20): small batches scan,
+    // large batches go through the tensor-core GEMM filter + exact re-score
+    const char* env_thr = getenv("B200R_GEMM_MIN_NQ");
+    const int64_t gemm_min = env_thr ? atoll(env_thr) : 20;
+    const bool use_gemm = ix->ntotal > 0 && (ix->cfg.search_path == B200R_PATH_GEMM ||
+                                             (ix->cfg.search_path == B200R_PATH_AUTO && nq >= gemm_min));
+    const int64_t nq_slots = use_gemm ? round_up(nq, 128) : round_up(nq, kScanMaxNQ);
     int rc = ensure_search_ws(ix, nq_slots, nq, k);
     if (rc != B200R_OK) return rc;
+    if (use_gemm) {
+        rc = ensure_gemm_ws(ix, nq, k, st);
+        if (rc != B200R_OK) return rc;
+    }
 
     if (ix->timing) CU(cudaEventRecord(ix->t0, st));
     const float* q_src = (const float*)q;
@@ -393,6 +452,48 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     float* od = out_mem_kind == B200R_DEVICE ? D : ix->out_d;
     int64_t* oi = out_mem_kind == B200R_DEVICE ? I : ix->out_i;
 
+    if (use_gemm) {
+        if (ix->bf16) {
+            CU(launch_f32_to_bf16(ix->q_dev, ix->q_bf16, nq_slots * ix->d_pad, st));
+            ix->st.n_kernel_launches++;
+        }
+        int* fail_count = ix->fail_dev + ix->fail_cap;
+        CU(cudaMemsetAsync(fail_count, 0, sizeof(int), st));
+        for (int64_t q0 = 0; q0 < nq; q0 += kGemmMaxBlock) {
+            GemmSearchArgs a{};
+            a.corpus = ix->rows;
+            a.norms = ix->norms;
+            a.n_rows = ix->ntotal;
+            a.d_pad = ix->d_pad;
+            a.bf16 = ix->bf16;
+            a.l2 = ix->l2;
+            a.q_f32 = ix->q_dev + (size_t)q0 * ix->d_pad;
+            a.q_mma = ix->bf16 ? (const void*)((const uint8_t*)ix->q_bf16 + (size_t)q0 * ix->d_pad * 2)
+                               : (const void*)a.q_f32;
+            a.nq = (int)std::min<int64_t>(kGemmMaxBlock, nq - q0);
+            a.k = k;
+            a.cand = ix->gemm_cand;
+            a.max_norm_bits = ix->max_norm_bits;
+            a.gthr = reinterpret_cast<int*>(ix->max_norm_bits) + 16;  // same 2 KB allocation
+            a.out_d = od + (size_t)q0 * k;
+            a.out_i = oi + (size_t)q0 * k;
+            a.id_base = ix->cfg.id_base;
+            a.fail_flags = ix->fail_dev + q0;
+            a.fail_count = fail_count;
+            a.num_sms = ix->num_sms;
+            CU(launch_gemm_search(a, st));
+            ix->st.n_kernel_launches += 3;
+            ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
+        }
+        ix->st.last_path = B200R_PATH_GEMM;
+        ix->st.last_grid = ix->num_sms;
+        // the containment check is read back: one small D2H + sync per search
+        CU(cudaMemcpyAsync(ix->fail_pin, ix->fail_dev, (size_t)(ix->fail_cap + 1) * sizeof(int), cudaMemcpyDeviceToHost,
+                           st));
+        CU(cudaStreamSynchronize(st));
+        ix->st.n_gemm_fallbacks += ix->fail_pin[ix->fail_cap];
+    }
+
     ScanParams p{};
     p.corpus = ix->rows;
     p.n_rows = ix->ntotal;
@@ -404,8 +505,9 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     p.scratch = ix->scratch;
     p.counter = ix->counter;
     p.id_base = ix->cfg.id_base;
-    for (int64_t q0 = 0; q0 < nq; q0 += kScanMaxNQ) {
-        const int nqg = (int)std::min<int64_t>(kScanMaxNQ, nq - q0);
+    for (int64_t q0 = 0; q0 < nq; q0 += (use_gemm ? 1 : kScanMaxNQ)) {
+        if (use_gemm && !ix->fail_pin[q0]) continue;  // only the queries whose check failed
+        const int nqg = use_gemm ? 1 : (int)std::min<int64_t>(kScanMaxNQ, nq - q0);
         p.q = ix->q_dev + (size_t)q0 * ix->d_pad;
         p.out_d = od + (size_t)q0 * k;
         p.out_i = oi + (size_t)q0 * k;
@@ -415,7 +517,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
         ix->st.last_grid = grid;
         ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
     }
-    ix->st.last_path = B200R_PATH_SCAN;
+    if (!use_gemm) ix->st.last_path = B200R_PATH_SCAN;
     if (ix->timing) CU(cudaEventRecord(ix->t1, st));
 
     if (out_mem_kind == B200R_HOST) {
@@ -494,6 +596,7 @@ extern "C" int b200r_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, 
     cudaFree(bounce);
     if (rc != B200R_OK) return rc;
     ix->ntotal = new_total;
+    ix->max_norm_dirty = true;
     ix->st.n_rows_removed += m;
     if (n_removed) *n_removed = m;
     return B200R_OK;

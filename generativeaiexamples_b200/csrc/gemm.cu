@@ -1,0 +1,766 @@
+// K3: large-batch search = tcgen05/TMEM inner-product GEMM with a fused top-K' filter,
+// followed by an exact fp32 re-score of the survivors ("gemm" path).
+//
+// Replaces what faiss 1.7.4 runs for nq >= 20: IndexFlat::search -> knn_* ->
+// exhaustive_inner_product_blas / exhaustive_L2sqr_blas (faiss/utils/distances.cpp): sgemm
+// over 4096 x 1024 blocks, L2 through ||q||^2 + ||x||^2 - 2 q.x, heap top-k.  In the
+// reference it is reached by batched callers of index.search (the only in-tree one is
+// community/event-driven-rag-cve-analysis/cyber_dev_day/faiss_vdb_service.py:147-174).
+//
+// Why two kernels.  The tensor cores have no fp32 inputs: kind::tf32 keeps 10 mantissa
+// bits of each operand, kind::f16 (bf16) keeps 8.  The north star wants fp32 results
+// (scores within 1e-5), so the GEMM is used as a FILTER with a proven error bound, and the
+// few survivors are re-scored exactly on the CUDA cores:
+//   1. gemm_filter_kernel: approx scores s~ for every (query, row); per query keep the
+//      K' = k + slack best approx scores (never written to HBM beyond those lists);
+//   2. rescore_kernel: exact fp32 score of each survivor (same arithmetic and summation
+//      order as the scan path), exact top-k among them, and the check
+//            exact_kth  >  approx_K'th + eps,      eps = c * ||q|| * max_row ||x||
+//      (|s~ - s| <= eps for every row, by Cauchy-Schwarz on the per-product rounding
+//      error).  If it holds, no row outside the survivors can belong to the exact top-k.
+//      A query that fails the check is flagged and the host re-runs it on the scan path.
+//
+// gemm_filter_kernel layout (one CTA per SM, persistent over 256-row corpus tiles):
+//   D[128 queries x 256 rows] (+ a second 128-query M tile when nq > 128) in TMEM;
+//   A = queries, B = corpus rows, both K-major, 128-byte swizzled K blocks staged by TMA
+//   (cp.async.bulk.tensor.2d, SASS UTMALDG) into a 3/4-stage mbarrier ring;
+//   warp 0 = TMA producer, warp 1 = MMA issuer (one lane, tcgen05.mma cta_group::1),
+//   warp 2 = TMEM allocator, warps 4.. = epilogue: tcgen05.ld 32 columns at a time, each
+//   THREAD owns one query (TMEM lane), keeps its running K'-th best in a register and its
+//   sorted survivor list in local memory (touched only on the rare insert).
+#include "common.cuh"
+#include "kernels.h"
+
+#include <cuda.h>
+
+namespace b200r {
+
+// ---------------------------------------------------------------------------
+// tcgen05 / TMA PTX wrappers
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void tma_load_2d(void* dst_smem, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+
+__device__ __forceinline__ void tma_load_2d_hint(void* dst_smem, const CUtensorMap* map, int c0, int c1, uint64_t* bar,
+                                                 uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, "
+        "%4}], [%2], %5;" ::"r"(smem_u32(dst_smem)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
+        : "memory");
+}
+
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+                 "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
+// mbarrier arrives once all tcgen05.mma issued so far by this thread have completed
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+
+template <bool BF16>
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                     uint32_t accumulate) {
+    if (BF16) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+            "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+            "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+            : "memory");
+    }
+}
+
+// 32 lanes x 32 consecutive columns: thread t of the warp gets row (lane) t
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128-byte-swizzled operand tile (rows of 128 B, 8-row groups 1024 B apart):
+// start>>4 | LBO=1 (unused for swizzled K-major) | SBO=1024>>4 | version=1 | SWIZZLE_128B
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(const void* smem_tile) {
+    const uint64_t addr = (uint64_t)((smem_u32(smem_tile) & 0x3FFFFu) >> 4);
+    return addr | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// ---------------------------------------------------------------------------
+constexpr int kGemmTileN = 256;        // corpus rows per tile (UMMA N)
+constexpr int kGemmTileM = 128;        // queries per M tile (UMMA M)
+constexpr int kGemmKBytes = 128;       // one swizzle atom of K per stage
+constexpr int kGemmBBytes = kGemmTileN * kGemmKBytes;   // 32 KB
+constexpr int kGemmABytes = kGemmTileM * kGemmKBytes;   // 16 KB per M tile
+
+struct GemmParams {
+    int64_t n_rows;
+    int nq;            // active queries (<= 128 * MT)
+    int d_pad;         // elements per row
+    int kprime;        // survivors kept per query (<= KP)
+    int num_kb;        // K blocks of 128 bytes
+    int64_t n_tiles;
+    const float* norms;   // [n_rows] squared norms (L2 only)
+    Cand* cand;           // [grid][128*MT][KP]
+    int* gthr;            // [128*MT] grid-wide thresholds, ordered-int encoded, pre-set to the worst value
+    int evict_first;
+};
+
+// monotone float <-> int encoding, so that atomicMax / atomicMin order floats correctly
+__device__ __forceinline__ int enc_ordered(float f) {
+    const int i = __float_as_int(f);
+    return i >= 0 ? i : i ^ 0x7FFFFFFF;
+}
+__device__ __forceinline__ float dec_ordered(int o) { return __int_as_float(o >= 0 ? o : o ^ 0x7FFFFFFF); }
+
+template <bool SMALL>
+__device__ __forceinline__ float better_of(float a, float b) {
+    return SMALL ? fminf(a, b) : fmaxf(a, b);
+}
+
+// Per-thread survivor list in local memory: UNSORTED, with the position and value of its
+// worst entry cached.  Filling is an append; once full, a new survivor overwrites the worst
+// entry and one independent-load scan finds the new worst.  `lthr` is the value a score must
+// beat to enter (worst_val until the list is full).
+template <int KP, bool SMALL>
+__device__ __noinline__ void list_offer(float* lv, uint32_t* li, int kp, int& count, int& widx, float& lthr, float v,
+                                        uint32_t id) {
+    if (count < kp) {
+        lv[count] = v;
+        li[count] = id;
+        if (++count < kp) return;
+    } else {
+        lv[widx] = v;
+        li[widx] = id;
+    }
+    float w = lv[0];
+    int wi = 0;
+    for (int j = 1; j < kp; j++) {
+        const float c = lv[j];
+        if (better_val<SMALL>(w, c)) {  // c is worse than the worst seen so far
+            w = c;
+            wi = j;
+        }
+    }
+    widx = wi;
+    lthr = w;
+}
+
+template <bool BF16, int MT, int KP, bool L2>
+__global__ void __launch_bounds__(128 + 128 * MT, 1)
+gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
+                   const GemmParams p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    constexpr int STAGES = MT == 1 ? 4 : 3;
+    constexpr int STAGE_BYTES = kGemmBBytes + MT * kGemmABytes;
+    constexpr int ACC_STAGES = MT == 1 ? 2 : 1;      // 512 TMEM columns in total
+    constexpr int ACC_COLS = MT * kGemmTileN;        // columns per accumulator stage
+    constexpr int UMMA_K_BYTES = 32;                 // 8 tf32 / 16 bf16
+    constexpr int N_EPI_WARPS = 4 * MT;
+
+    // carve-up (1024-byte aligned stages for the 128B swizzle)
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* stages = smem;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tfull_bar = empty_bar + STAGES;
+    uint64_t* tempty_bar = tfull_bar + ACC_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + ACC_STAGES);
+    float* s_norms = reinterpret_cast<float*>(tmem_slot + 4);  // [N_EPI_WARPS][256] (L2 only)
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int a = 0; a < ACC_STAGES; a++) {
+            mbar_init(&tfull_bar[a], 1);
+            mbar_init(&tempty_bar[a], N_EPI_WARPS);
+        }
+        fence_mbar_init();
+        prefetch_tmap(&map_q);
+        prefetch_tmap(&map_x);
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    const int64_t n_tiles = p.n_tiles;
+
+    if (warp == 0) {
+        // ---------------- TMA producer ----------------
+        if (lane == 0) {
+            const uint64_t pol = policy_evict_first();
+            int s = 0;
+            uint32_t ph = 0;
+            const int kstep = BF16 ? 64 : 32;  // elements per 128-byte K block
+            for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                const int row0 = (int)(t * kGemmTileN);
+                for (int kb = 0; kb < p.num_kb; kb++) {
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    uint8_t* st = stages + (size_t)s * STAGE_BYTES;
+                    mbar_arrive_expect_tx(&full_bar[s], STAGE_BYTES);
+                    if (p.evict_first)
+                        tma_load_2d_hint(st, &map_x, kb * kstep, row0, &full_bar[s], pol);
+                    else
+                        tma_load_2d(st, &map_x, kb * kstep, row0, &full_bar[s]);
+#pragma unroll
+                    for (int mt = 0; mt < MT; mt++)
+                        tma_load_2d(st + kGemmBBytes + mt * kGemmABytes, &map_q, kb * kstep, mt * kGemmTileM,
+                                    &full_bar[s]);
+                    if (++s == STAGES) {
+                        s = 0;
+                        ph ^= 1;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ---------------- MMA issuer ----------------
+        if (lane == 0) {
+            // idesc: D=f32 (1<<4) | A,B format (tf32=2 / bf16=1) | K-major both | N>>3 | M>>4
+            const uint32_t fmt = BF16 ? 1u : 2u;
+            const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(kGemmTileN >> 3) << 17) |
+                                   ((uint32_t)(kGemmTileM >> 4) << 24);
+            int s = 0;
+            uint32_t ph = 0;
+            int64_t it = 0;
+            for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+                const int as = (int)(it % ACC_STAGES);
+                const uint32_t aph = (uint32_t)((it / ACC_STAGES) & 1);
+                mbar_wait(&tempty_bar[as], aph ^ 1);
+                tc_fence_after();
+                for (int kb = 0; kb < p.num_kb; kb++) {
+                    mbar_wait(&full_bar[s], ph);
+                    tc_fence_after();
+                    const uint8_t* st = stages + (size_t)s * STAGE_BYTES;
+                    const uint64_t db = make_kmajor_sw128_desc(st);
+#pragma unroll
+                    for (int mt = 0; mt < MT; mt++) {
+                        const uint64_t da = make_kmajor_sw128_desc(st + kGemmBBytes + mt * kGemmABytes);
+                        const uint32_t td = tmem_base + (uint32_t)(as * ACC_COLS + mt * kGemmTileN);
+#pragma unroll
+                        for (int k4 = 0; k4 < kGemmKBytes / UMMA_K_BYTES; k4++) {
+                            const uint64_t adv = (uint64_t)((k4 * UMMA_K_BYTES) >> 4);
+                            umma<BF16>(td, da + adv, db + adv, idesc, (uint32_t)((kb | k4) != 0));
+                        }
+                    }
+                    tc_commit(&empty_bar[s]);  // frees the smem stage when these MMAs are done
+                    if (kb == p.num_kb - 1) tc_commit(&tfull_bar[as]);
+                    if (++s == STAGES) {
+                        s = 0;
+                        ph ^= 1;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp >= 4) {
+        // ---------------- epilogue: one query per thread ----------------
+        const int ew = warp - 4;
+        const int mt = ew >> 2;
+        const int quad = warp & 3;  // TMEM lane quadrant this warp may read
+        const int qidx = mt * kGemmTileM + quad * 32 + lane;
+        const bool active = qidx < p.nq;
+        float lv[KP];
+        uint32_t li[KP];
+        const int kp = p.kprime;
+        int count = 0, widx = 0;
+        float lthr = worst_val<L2>();   // what a score must beat to enter THIS thread's list
+        float thr = worst_val<L2>();    // effective filter: better of lthr and the grid-wide threshold
+        int* gthr = p.gthr + qidx;      // grid-wide K'-th best so far for this query (ordered-int encoded)
+        float* my_norms = s_norms + ew * kGemmTileN;
+        int64_t it = 0;
+        for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+            const int as = (int)(it % ACC_STAGES);
+            const uint32_t aph = (uint32_t)((it / ACC_STAGES) & 1);
+            const int64_t row0 = t * kGemmTileN;
+            // Any CTA's full-list worst is a lower bound of the final K'-th best, so filtering with
+            // the best such bound published by any CTA never drops a row of the global top-K'.
+            float g = worst_val<L2>();
+            if (active) g = dec_ordered(*reinterpret_cast<volatile int*>(gthr));
+            if (L2) {
+                // stage ||x||^2 of the tile's rows; rows past the end never win
+                __syncwarp();
+#pragma unroll
+                for (int u = 0; u < kGemmTileN / 32; u++) {
+                    const int64_t r = row0 + u * 32 + lane;
+                    my_norms[u * 32 + lane] = r < p.n_rows ? p.norms[r] : FLT_MAX;
+                }
+                __syncwarp();
+            }
+            thr = better_of<L2>(lthr, g);
+            mbar_wait(&tfull_bar[as], aph);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * ACC_COLS + mt * kGemmTileN);
+            bool improved = false;
+#pragma unroll 1
+            for (int c = 0; c < kGemmTileN / 32; c++) {
+                uint32_t r[32];
+                tmem_ld32(taddr + c * 32, r);
+                if (active) {
+                    float v[32];
+                    float best;
+                    if (L2) {
+                        // ||x||^2 - 2 q.x   (+ ||q||^2 is added at re-score time; order is unaffected)
+#pragma unroll
+                        for (int j = 0; j < 32; j++) v[j] = fmaf(-2.f, __uint_as_float(r[j]), my_norms[c * 32 + j]);
+                        best = v[0];
+#pragma unroll
+                        for (int j = 1; j < 32; j++) best = fminf(best, v[j]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; j++) v[j] = __uint_as_float(r[j]);
+                        best = v[0];
+#pragma unroll
+                        for (int j = 1; j < 32; j++) best = fmaxf(best, v[j]);
+                    }
+                    if (better_val<L2>(best, thr)) {
+                        const int64_t rbase = row0 + c * 32;
+#pragma unroll
+                        for (int j = 0; j < 32; j++)
+                            if (better_val<L2>(v[j], thr) && rbase + j < p.n_rows) {
+                                list_offer<KP, L2>(lv, li, kp, count, widx, lthr, v[j], (uint32_t)(rbase + j));
+                                thr = better_of<L2>(lthr, g);
+                                improved = true;
+                            }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[as]);
+            // publish: only a FULL list's worst is a valid bound
+            if (active && improved && count >= kp && better_val<L2>(lthr, g)) {
+                if (L2)
+                    atomicMin(gthr, enc_ordered(lthr));
+                else
+                    atomicMax(gthr, enc_ordered(lthr));
+            }
+        }
+        // survivors -> global, [cta][query][KP] (unsorted; unused slots empty)
+        if (active) {
+            Cand* dst = p.cand + ((size_t)blockIdx.x * (kGemmTileM * MT) + qidx) * KP;
+            for (int j = 0; j < kp; j++) {
+                Cand cnd;
+                cnd.v = j < count ? lv[j] : worst_val<L2>();
+                cnd.id = j < count ? li[j] : kEmptyId;
+                dst[j] = cnd;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// rescore_kernel: one CTA per query.
+// ---------------------------------------------------------------------------
+constexpr int kRescoreWarps = 8;
+
+struct RescoreParams {
+    const void* corpus;
+    int64_t n_rows;
+    int d_pad, row_bytes;
+    const float* q;        // [nq][d_pad] fp32 (prepared)
+    const Cand* cand;      // [grid][q_stride][KP] approx survivors
+    int grid, q_stride, kp_stride, kprime, k;
+    const unsigned* max_norm_bits;  // max_i ||x_i||^2 as float bits
+    float err_coeff;       // c in eps = c * ||q|| * max||x||
+    float* out_d;
+    int64_t* out_i;
+    int64_t id_base;
+    int* fail_flags;       // [nq]
+    int* fail_count;
+};
+
+template <int KPL, bool L2, bool BF16>
+__global__ void __launch_bounds__(kRescoreWarps * 32) rescore_kernel(const RescoreParams p) {
+    extern __shared__ __align__(16) uint8_t rs_smem[];
+    float* qs = reinterpret_cast<float*>(rs_smem);                   // [d_pad]
+    Cand* surv = reinterpret_cast<Cand*>(qs + p.d_pad);              // [KPL*32] approx survivors
+    float* exact = reinterpret_cast<float*>(surv + KPL * 32);        // [KPL*32]
+    __shared__ float s_red[kRescoreWarps];
+    __shared__ float s_qnorm2;
+
+    const int qi = blockIdx.x;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float* qg = p.q + (size_t)qi * p.d_pad;
+    float part = 0.f;
+    for (int i = threadIdx.x; i < p.d_pad; i += blockDim.x) {
+        const float v = qg[i];
+        qs[i] = v;
+        part = fmaf(v, v, part);
+    }
+    part = warp_sum(part);
+    if (lane == 0) s_red[warp] = part;
+
+    // warp 0: merge the per-CTA survivor lists into the K' best approx scores
+    if (warp == 0) {
+        WarpTopK<KPL, L2> m;
+        m.init(p.kprime);
+        for (int g = 0; g < p.grid; g++) {
+            const Cand* src = p.cand + ((size_t)g * p.q_stride + qi) * p.kp_stride;
+#pragma unroll
+            for (int j = 0; j < KPL; j++) {
+                const int e = j * 32 + lane;
+                Cand c;
+                c.v = worst_val<L2>();
+                c.id = kEmptyId;
+                if (e < p.kprime) c = src[e];
+                m.offer_lanes(c.v, c.id);  // per-CTA lists are unsorted
+            }
+        }
+        m.store(surv);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float s = 0.f;
+        for (int w = 0; w < kRescoreWarps; w++) s += s_red[w];
+        s_qnorm2 = s;
+    }
+
+    // all warps: exact fp32 score of every survivor, same lane mapping / summation order as
+    // the scan kernel (4 partial sums per lane, butterfly)
+    const int nvec = BF16 ? (p.d_pad >> 3) : (p.d_pad >> 2);
+    for (int c = warp; c < p.kprime; c += kRescoreWarps) {
+        const uint32_t id = surv[c].id;
+        float sc = worst_val<L2>();
+        if (id != kEmptyId) {
+            const uint4* xr = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(p.corpus) +
+                                                             (size_t)id * p.row_bytes);
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            for (int i = lane; i < nvec; i += 32) {
+                const uint4 xv = __ldg(xr + i);
+                if (!BF16) {
+                    const float4 qv = reinterpret_cast<const float4*>(qs)[i];
+                    const float x0 = __uint_as_float(xv.x), x1 = __uint_as_float(xv.y), x2 = __uint_as_float(xv.z),
+                                x3 = __uint_as_float(xv.w);
+                    if (L2) {
+                        const float t0 = qv.x - x0, t1 = qv.y - x1, t2 = qv.z - x2, t3 = qv.w - x3;
+                        a0 = fmaf(t0, t0, a0);
+                        a1 = fmaf(t1, t1, a1);
+                        a2 = fmaf(t2, t2, a2);
+                        a3 = fmaf(t3, t3, a3);
+                    } else {
+                        a0 = fmaf(qv.x, x0, a0);
+                        a1 = fmaf(qv.y, x1, a1);
+                        a2 = fmaf(qv.z, x2, a2);
+                        a3 = fmaf(qv.w, x3, a3);
+                    }
+                } else {
+                    const float4 qa = reinterpret_cast<const float4*>(qs)[2 * i];
+                    const float4 qb = reinterpret_cast<const float4*>(qs)[2 * i + 1];
+                    const float qq[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+                    const float x[8] = {__uint_as_float(xv.x << 16), __uint_as_float(xv.x & 0xffff0000u),
+                                        __uint_as_float(xv.y << 16), __uint_as_float(xv.y & 0xffff0000u),
+                                        __uint_as_float(xv.z << 16), __uint_as_float(xv.z & 0xffff0000u),
+                                        __uint_as_float(xv.w << 16), __uint_as_float(xv.w & 0xffff0000u)};
+                    float acc[4] = {a0, a1, a2, a3};
+#pragma unroll
+                    for (int e = 0; e < 8; e++) {
+                        if (L2) {
+                            const float tt = qq[e] - x[e];
+                            acc[e & 3] = fmaf(tt, tt, acc[e & 3]);
+                        } else {
+                            acc[e & 3] = fmaf(qq[e], x[e], acc[e & 3]);
+                        }
+                    }
+                    a0 = acc[0];
+                    a1 = acc[1];
+                    a2 = acc[2];
+                    a3 = acc[3];
+                }
+            }
+            sc = warp_sum((a0 + a2) + (a1 + a3));
+        }
+        if (lane == 0) exact[c] = sc;
+    }
+    __syncthreads();
+
+    // warp 0: exact top-k among the survivors + the containment check
+    if (warp == 0) {
+        WarpTopK<KPL, L2> m;
+        m.init(p.k);
+        int n_valid = 0;
+        float approx_worst = worst_val<L2>();  // approx score of the K'-th survivor
+#pragma unroll
+        for (int j = 0; j < KPL; j++) {
+            const int e = j * 32 + lane;
+            float v = worst_val<L2>();
+            uint32_t id = kEmptyId;
+            if (e < p.kprime) {
+                id = surv[e].id;
+                if (id != kEmptyId) v = exact[e];
+            }
+            n_valid += __popc(__ballot_sync(0xffffffffu, id != kEmptyId));
+            m.offer_lanes(v, id);
+        }
+        if (n_valid > 0) approx_worst = surv[n_valid - 1].v;
+        // every row outside the survivors has approx score no better than approx_worst
+        // (only meaningful when the list is full; otherwise every row IS a survivor)
+        bool ok = true;
+        if (n_valid >= p.kprime && (int64_t)n_valid < p.n_rows) {
+            const float qn = sqrtf(s_qnorm2);
+            const float xn = sqrtf(__uint_as_float(*p.max_norm_bits));
+            float eps = p.err_coeff * qn * xn;
+            if (L2) {
+                // approx value is ||x||^2 - 2 q.x~ ; exact is sum (q-x)^2 = ||q||^2 + ||x||^2 - 2 q.x
+                eps = 2.f * eps + 1e-6f * (s_qnorm2 + xn * xn);
+                const float kth = m.thr;  // exact k-th smallest (FLT_MAX if fewer than k)
+                ok = (kth - s_qnorm2) < approx_worst - eps;
+            } else {
+                const float kth = m.thr;
+                ok = kth > approx_worst + eps;
+            }
+            if (m.thr_id == kEmptyId) ok = false;  // fewer than k finite survivors: be safe
+        }
+#pragma unroll
+        for (int j = 0; j < KPL; j++) {
+            const int e = j * 32 + lane;
+            if (e < p.k) {
+                p.out_d[(size_t)qi * p.k + e] = m.v[j];
+                p.out_i[(size_t)qi * p.k + e] = (m.id[j] == kEmptyId) ? -1 : (int64_t)m.id[j] + p.id_base;
+            }
+        }
+        if (lane == 0) {
+            p.fail_flags[qi] = ok ? 0 : 1;
+            if (!ok) atomicAdd(p.fail_count, 1);
+        }
+    }
+}
+
+__global__ void fill_i32_kernel(int* dst, int n, int value) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = value;
+}
+
+// max over rows of the squared norm, as float bits (non-negative floats order like uints)
+__global__ void max_norm_kernel(const float* __restrict__ norms, int64_t n, unsigned* __restrict__ out_bits) {
+    float m = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        m = fmaxf(m, norms[i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));
+}
+
+cudaError_t launch_max_norm(const float* norms, int64_t n, unsigned* out_bits, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(out_bits, 0, sizeof(unsigned), st);
+    if (e != cudaSuccess || n <= 0) return e;
+    int g = (int)((n + 1023) / 1024);
+    if (g > 148 * 4) g = 148 * 4;
+    max_norm_kernel<<<g, 256, 0, st>>>(norms, n, out_bits);
+    return cudaGetLastError();
+}
+
+// fp32 [nq_slots][d_pad] -> bf16 (queries for the bf16-corpus GEMM); RNE
+__global__ void f32_to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+cudaError_t launch_f32_to_bf16(const float* src, void* dst, int64_t n, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    int g = (int)((n + 255) / 256);
+    if (g > 148 * 8) g = 148 * 8;
+    f32_to_bf16_kernel<<<g, 256, 0, st>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), n);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    }
+    return fn;
+}
+
+// [rows][d_pad] row-major matrix, box = 128 bytes of K x box_rows rows, 128B swizzle
+static bool make_map(CUtensorMap* map, const void* base, int64_t rows, int d_pad, bool bf16, int box_rows) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)d_pad, (cuuint64_t)(rows > 0 ? rows : 1)};
+    const cuuint64_t strides[1] = {(cuuint64_t)d_pad * (bf16 ? 2 : 4)};
+    const cuuint32_t box[2] = {(cuuint32_t)(bf16 ? 64 : 32), (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                           const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS;
+}
+
+size_t gemm_cand_bytes(int grid, int nq_pad, int kp_cap) { return (size_t)grid * nq_pad * kp_cap * sizeof(Cand); }
+
+// survivors kept per query: the slack beyond k must cover the rows whose approx score lies
+// within 2*eps of the k-th best; their number grows with k (and with N), so it scales with k
+int gemm_kp_cap(int k) { return (k + kGemmSlack <= 32) ? 32 : 256; }
+int gemm_kprime(int k) {
+    if (k + kGemmSlack <= 32) return k + kGemmSlack;
+    const int kp = 2 * k + 24;
+    return kp < 256 ? kp : 256;
+}
+
+template <bool BF16, int MT, int KP, bool L2>
+static cudaError_t launch_filter_one(const CUtensorMap& mq, const CUtensorMap& mx, const GemmParams& p, int grid,
+                                     cudaStream_t st) {
+    constexpr int STAGES = MT == 1 ? 4 : 3;
+    constexpr int STAGE_BYTES = kGemmBBytes + MT * kGemmABytes;
+    const size_t smem = 1024 + (size_t)STAGES * STAGE_BYTES + 256 + (L2 ? (size_t)4 * MT * kGemmTileN * sizeof(float) : 0);
+    auto kern = gemm_filter_kernel<BF16, MT, KP, L2>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    kern<<<grid, 128 + 128 * MT, smem, st>>>(mq, mx, p);
+    return cudaGetLastError();
+}
+
+template <bool BF16, int MT, int KP>
+static cudaError_t launch_filter_l2(bool l2, const CUtensorMap& mq, const CUtensorMap& mx, const GemmParams& p, int grid,
+                                    cudaStream_t st) {
+    return l2 ? launch_filter_one<BF16, MT, KP, true>(mq, mx, p, grid, st)
+              : launch_filter_one<BF16, MT, KP, false>(mq, mx, p, grid, st);
+}
+
+template <int KPL, bool L2>
+static cudaError_t launch_rescore_bf(bool bf16, const RescoreParams& rp, int nq, size_t smem, cudaStream_t st) {
+    if (bf16)
+        rescore_kernel<KPL, L2, true><<<nq, kRescoreWarps * 32, smem, st>>>(rp);
+    else
+        rescore_kernel<KPL, L2, false><<<nq, kRescoreWarps * 32, smem, st>>>(rp);
+    return cudaGetLastError();
+}
+
+// One block of up to 256 queries against the whole shard.
+//   q_f32:   [nq_pad][d_pad] prepared fp32 queries (nq_pad = 128 or 256 rows, unused rows zero)
+//   q_mma:   the same matrix in the MMA input type (== q_f32 for an fp32 corpus, bf16 copy otherwise)
+cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
+    if (a.nq < 1 || a.nq > 2 * kGemmTileM || a.k < 1 || a.k > kScanMaxK) return cudaErrorInvalidValue;
+    const int MT = a.nq <= kGemmTileM ? 1 : 2;
+    const int kp_cap = gemm_kp_cap(a.k);
+    const int kprime = gemm_kprime(a.k);
+    CUtensorMap mq, mx;
+    if (!make_map(&mq, a.q_mma, (int64_t)MT * kGemmTileM, a.d_pad, a.bf16, kGemmTileM)) return cudaErrorNotSupported;
+    if (!make_map(&mx, a.corpus, a.n_rows, a.d_pad, a.bf16, kGemmTileN)) return cudaErrorNotSupported;
+    GemmParams p{};
+    p.n_rows = a.n_rows;
+    p.nq = a.nq;
+    p.d_pad = a.d_pad;
+    p.kprime = kprime;
+    p.num_kb = (a.d_pad * (a.bf16 ? 2 : 4) + kGemmKBytes - 1) / kGemmKBytes;
+    p.n_tiles = (a.n_rows + kGemmTileN - 1) / kGemmTileN;
+    p.norms = a.norms;
+    p.cand = a.cand;
+    p.gthr = a.gthr;
+    {
+        // grid-wide thresholds start at the worst value: enc(-FLT_MAX) for IP, enc(+FLT_MAX) for L2
+        const int worst_enc = a.l2 ? 0x7F7FFFFF : (int)(0xFF7FFFFFu ^ 0x7FFFFFFFu);
+        fill_i32_kernel<<<1, 256, 0, st>>>(a.gthr, 2 * kGemmTileM, worst_enc);
+    }
+    p.evict_first = ((size_t)a.n_rows * a.d_pad * (a.bf16 ? 2 : 4) > ((size_t)96 << 20)) ? 1 : 0;
+    int grid = (int)(p.n_tiles < a.num_sms ? p.n_tiles : a.num_sms);
+    if (grid < 1) grid = 1;
+    cudaError_t e;
+    if (a.bf16) {
+        if (MT == 1)
+            e = kp_cap == 32 ? launch_filter_l2<true, 1, 32>(a.l2, mq, mx, p, grid, st)
+                             : launch_filter_l2<true, 1, 256>(a.l2, mq, mx, p, grid, st);
+        else
+            e = kp_cap == 32 ? launch_filter_l2<true, 2, 32>(a.l2, mq, mx, p, grid, st)
+                             : launch_filter_l2<true, 2, 256>(a.l2, mq, mx, p, grid, st);
+    } else {
+        if (MT == 1)
+            e = kp_cap == 32 ? launch_filter_l2<false, 1, 32>(a.l2, mq, mx, p, grid, st)
+                             : launch_filter_l2<false, 1, 256>(a.l2, mq, mx, p, grid, st);
+        else
+            e = kp_cap == 32 ? launch_filter_l2<false, 2, 32>(a.l2, mq, mx, p, grid, st)
+                             : launch_filter_l2<false, 2, 256>(a.l2, mq, mx, p, grid, st);
+    }
+    if (e != cudaSuccess) return e;
+
+    RescoreParams rp{};
+    rp.corpus = a.corpus;
+    rp.n_rows = a.n_rows;
+    rp.d_pad = a.d_pad;
+    rp.row_bytes = a.d_pad * (a.bf16 ? 2 : 4);
+    rp.q = a.q_f32;
+    rp.cand = a.cand;
+    rp.grid = grid;
+    rp.q_stride = MT * kGemmTileM;
+    rp.kp_stride = kp_cap;
+    rp.kprime = kprime;
+    rp.k = a.k;
+    rp.max_norm_bits = a.max_norm_bits;
+    rp.err_coeff = 2.5e-3f;  // 2^-9 per product (two truncated tf32 / one bf16-rounded operand) + accumulation slack
+    rp.out_d = a.out_d;
+    rp.out_i = a.out_i;
+    rp.id_base = a.id_base;
+    rp.fail_flags = a.fail_flags;
+    rp.fail_count = a.fail_count;
+    const int kpl = kp_cap == 32 ? 1 : 8;
+    const size_t rs_smem = (size_t)a.d_pad * sizeof(float) + (size_t)kpl * 32 * (sizeof(Cand) + sizeof(float));
+    if (kpl == 1)
+        e = a.l2 ? launch_rescore_bf<1, true>(a.bf16, rp, a.nq, rs_smem, st)
+                 : launch_rescore_bf<1, false>(a.bf16, rp, a.nq, rs_smem, st);
+    else
+        e = a.l2 ? launch_rescore_bf<8, true>(a.bf16, rp, a.nq, rs_smem, st)
+                 : launch_rescore_bf<8, false>(a.bf16, rp, a.nq, rs_smem, st);
+    return e;
+}
+
+}  // namespace b200r

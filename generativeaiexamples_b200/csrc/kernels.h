@@ -52,6 +52,34 @@ cudaError_t launch_merge(bool l2, const float* cand_d, const int64_t* cand_i, in
                          int64_t stride_d, int64_t stride_i, int k_out, float* out_d, int64_t* out_i,
                          cudaStream_t st);
 
+// K3 (gemm.cu): tcgen05 GEMM filter + exact re-score for one block of <= 256 queries
+constexpr int kGemmSlack = 22;       // survivors kept beyond k when k + slack <= 32
+constexpr int kGemmMaxBlock = 256;   // queries per GEMM launch (two 128-row M tiles)
+struct GemmSearchArgs {
+    const void* corpus;
+    const float* norms;
+    int64_t n_rows;
+    int d_pad;
+    bool bf16, l2;
+    const float* q_f32;   // [128 or 256][d_pad] prepared queries, unused rows zero
+    const void* q_mma;    // same rows in the MMA input type (fp32 corpus: == q_f32; bf16 corpus: bf16 copy)
+    int nq, k;
+    Cand* cand;           // >= gemm_cand_bytes(num_sms, 256, gemm_kp_cap(k))
+    int* gthr;            // [256] scratch: grid-wide per-query thresholds
+    const unsigned* max_norm_bits;
+    float* out_d;
+    int64_t* out_i;
+    int64_t id_base;
+    int* fail_flags;      // [nq]: 1 = containment check failed, re-run on the scan path
+    int* fail_count;
+    int num_sms;
+};
+cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st);
+cudaError_t launch_max_norm(const float* norms, int64_t n, unsigned* out_bits, cudaStream_t st);
+cudaError_t launch_f32_to_bf16(const float* src, void* dst, int64_t n, cudaStream_t st);
+size_t gemm_cand_bytes(int grid, int nq_pad, int kp_cap);
+int gemm_kp_cap(int k);
+
 // lets entry points outside api.cu fill b200r_last_error()
 void set_last_error(const char* msg);
 

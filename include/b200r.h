@@ -88,6 +88,8 @@ typedef struct b200r_stats {
     int32_t num_sms;
     int32_t reserved0;
     double last_search_ms;       /* device time of the last search (events), 0 if timing is off */
+    int64_t n_gemm_fallbacks;    /* queries of the GEMM path whose containment check failed and
+                                    were re-run on the scan path (results are exact either way) */
 } b200r_stats;
 
 /* faiss.IndexFlatL2(d) / IndexFlatIP(d)   [utils.py:306; rag_service.py:88] */

@@ -27,9 +27,9 @@ def test_header_symbols_exported(built_lib):
 
 
 def test_struct_layout_matches_header():
-    # b200r_config: 8 x int32 + 2 x int64; b200r_stats: 8 x int64 + 4 x int32 + double
+    # b200r_config: 8 x int32 + 2 x int64; b200r_stats: 8 x int64 + 4 x int32 + double + int64
     assert ctypes.sizeof(_lib.Config) == 8 * 4 + 2 * 8
-    assert ctypes.sizeof(_lib.Stats) == 8 * 8 + 4 * 4 + 8
+    assert ctypes.sizeof(_lib.Stats) == 8 * 8 + 4 * 4 + 8 + 8
 
 
 def test_version(built_lib):
