@@ -95,6 +95,7 @@ struct b200r_index {
     Cand* gemm_cand = nullptr;
     size_t gemm_cand_bytes = 0;
     unsigned* max_norm_bits = nullptr;
+    void* gemm_aux = nullptr;      // histograms, bucket maps, grid-wide thresholds
     bool max_norm_dirty = true;
     int* fail_dev = nullptr;       // [fail_cap] flags + 1 counter at the end
     int* fail_pin = nullptr;
@@ -162,6 +163,7 @@ static void free_index(b200r_index* ix) {
     cudaFree(ix->q_bf16);
     cudaFree(ix->gemm_cand);
     cudaFree(ix->max_norm_bits);
+    cudaFree(ix->gemm_aux);
     cudaFree(ix->fail_dev);
     cudaFreeHost(ix->fail_pin);
     for (auto& e : ix->add_ev)
@@ -387,7 +389,8 @@ static int ensure_gemm_ws(b200r_index* ix, int64_t nq, int k, cudaStream_t st) {
         ix->gemm_cand_bytes = need;
     }
     if (!ix->max_norm_bits) {
-        CU(cudaMalloc(&ix->max_norm_bits, 2048));  // [0]: max norm bits; [16..272): GEMM thresholds
+        CU(cudaMalloc(&ix->max_norm_bits, 256));
+        CU(cudaMalloc(&ix->gemm_aux, gemm_aux_bytes()));
         ix->max_norm_dirty = true;
     }
     if (ix->max_norm_dirty) {
@@ -474,7 +477,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
             a.k = k;
             a.cand = ix->gemm_cand;
             a.max_norm_bits = ix->max_norm_bits;
-            a.gthr = reinterpret_cast<int*>(ix->max_norm_bits) + 16;  // same 2 KB allocation
+            gemm_aux_layout(ix->gemm_aux, &a.hist, &a.qscale, &a.gthr);
             a.out_d = od + (size_t)q0 * k;
             a.out_i = oi + (size_t)q0 * k;
             a.id_base = ix->cfg.id_base;

@@ -32,6 +32,7 @@
 #include "kernels.h"
 
 #include <cuda.h>
+#include <cstdlib>
 
 namespace b200r {
 
@@ -53,6 +54,11 @@ __device__ __forceinline__ void tma_load_2d_hint(void* dst_smem, const CUtensorM
         "%4}], [%2], %5;" ::"r"(smem_u32(dst_smem)),
         "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy)
         : "memory");
+}
+
+// contiguous global -> L2 prefetch (no shared-memory destination)
+__device__ __forceinline__ void bulk_prefetch_l2(const void* gmem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem), "r"(bytes) : "memory");
 }
 
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
@@ -125,6 +131,7 @@ constexpr int kGemmTileM = 128;        // queries per M tile (UMMA M)
 constexpr int kGemmKBytes = 128;       // one swizzle atom of K per stage
 constexpr int kGemmBBytes = kGemmTileN * kGemmKBytes;   // 32 KB
 constexpr int kGemmABytes = kGemmTileM * kGemmKBytes;   // 16 KB per M tile
+constexpr int kGemmBuckets = 512;      // score histogram resolution for the grid-wide threshold
 
 struct GemmParams {
     int64_t n_rows;
@@ -136,6 +143,11 @@ struct GemmParams {
     const float* norms;   // [n_rows] squared norms (L2 only)
     Cand* cand;           // [grid][128*MT][KP]
     int* gthr;            // [128*MT] grid-wide thresholds, ordered-int encoded, pre-set to the worst value
+    const void* corpus;   // base of the row-major corpus (for the L2 prefetch stream)
+    int prefetch_tiles;   // tiles of look-ahead for that stream (0 = off)
+    unsigned* hist;       // [128*MT][kGemmBuckets] rows inserted so far per goodness bucket (zeroed per launch)
+    const float* qscale;  // [128*MT][2] bucket map per query: goodness lo, buckets per unit
+    int debug_no_select;  // timing experiments only: 1 = skip the selection, 2 = also skip the TMEM loads
     int evict_first;
 };
 
@@ -151,32 +163,51 @@ __device__ __forceinline__ float better_of(float a, float b) {
     return SMALL ? fminf(a, b) : fmaxf(a, b);
 }
 
-// Per-thread survivor list in local memory: UNSORTED, with the position and value of its
-// worst entry cached.  Filling is an append; once full, a new survivor overwrites the worst
-// entry and one independent-load scan finds the new worst.  `lthr` is the value a score must
-// beat to enter (worst_val until the list is full).
+// Per-thread survivor list in local memory, kept as a binary heap whose ROOT is the WORST
+// kept entry (the same structure faiss uses, faiss/utils/Heap.h).  Filling sifts up; once full
+// a better score replaces the root and sifts down: log2(K') dependent steps instead of a scan.
+// `lthr` is what a score must beat to enter (worst_val until the heap is full).
 template <int KP, bool SMALL>
-__device__ __noinline__ void list_offer(float* lv, uint32_t* li, int kp, int& count, int& widx, float& lthr, float v,
+__device__ __noinline__ void list_offer(float* lv, uint32_t* li, int kp, int& count, float& lthr, float v,
                                         uint32_t id) {
+    int i;
     if (count < kp) {
-        lv[count] = v;
-        li[count] = id;
-        if (++count < kp) return;
-    } else {
-        lv[widx] = v;
-        li[widx] = id;
-    }
-    float w = lv[0];
-    int wi = 0;
-    for (int j = 1; j < kp; j++) {
-        const float c = lv[j];
-        if (better_val<SMALL>(w, c)) {  // c is worse than the worst seen so far
-            w = c;
-            wi = j;
+        i = count++;
+        while (i > 0) {
+            const int par = (i - 1) >> 1;
+            const float pv = lv[par];
+            if (!better_val<SMALL>(pv, v)) break;  // parent already at least as bad as v
+            lv[i] = pv;
+            li[i] = li[par];
+            i = par;
         }
+        lv[i] = v;
+        li[i] = id;
+        if (count == kp) lthr = lv[0];
+        return;
     }
-    widx = wi;
-    lthr = w;
+    i = 0;
+    for (;;) {
+        const int l = 2 * i + 1;
+        if (l >= kp) break;
+        const int r = l + 1;
+        float cv = lv[l];
+        int c = l;
+        if (r < kp) {
+            const float rv = lv[r];
+            if (better_val<SMALL>(cv, rv)) {  // right child is the worse one
+                cv = rv;
+                c = r;
+            }
+        }
+        if (!better_val<SMALL>(v, cv)) break;  // v is at least as bad as the worse child
+        lv[i] = cv;
+        li[i] = li[c];
+        i = c;
+    }
+    lv[i] = v;
+    li[i] = id;
+    lthr = lv[0];
 }
 
 template <bool BF16, int MT, int KP, bool L2>
@@ -199,6 +230,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
     uint64_t* tfull_bar = empty_bar + STAGES;
     uint64_t* tempty_bar = tfull_bar + ACC_STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + ACC_STAGES);
+    volatile int* s_done = reinterpret_cast<volatile int*>(tmem_slot + 1);  // epilogue warps that have finished
     float* s_norms = reinterpret_cast<float*>(tmem_slot + 4);  // [N_EPI_WARPS][256] (L2 only)
 
     const int warp = threadIdx.x >> 5;
@@ -213,6 +245,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             mbar_init(&tfull_bar[a], 1);
             mbar_init(&tempty_bar[a], N_EPI_WARPS);
         }
+        *s_done = 0;
         fence_mbar_init();
         prefetch_tmap(&map_q);
         prefetch_tmap(&map_x);
@@ -232,8 +265,26 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             int s = 0;
             uint32_t ph = 0;
             const int kstep = BF16 ? 64 : 32;  // elements per 128-byte K block
+            // The K-blocked tile loads touch 256 rows x 128 B each: scattered for DRAM.  Stream the
+            // tile's rows (one contiguous block) into L2 a few tiles ahead with bulk prefetches, so
+            // that DRAM sees long sequential reads and the TMA tile loads hit L2.
+            const int row_bytes = p.d_pad * (BF16 ? 2 : 4);
+            const uint8_t* xg = reinterpret_cast<const uint8_t*>(p.corpus);
+            auto prefetch_tile = [&](int64_t tt) {
+                if (tt >= n_tiles) return;
+                const int64_t r0 = tt * kGemmTileN;
+                const int64_t rows = (p.n_rows - r0) < kGemmTileN ? (p.n_rows - r0) : kGemmTileN;
+                const int64_t bytes = rows * row_bytes;
+                const uint8_t* base = xg + r0 * row_bytes;
+                for (int64_t o = 0; o < bytes; o += 32768) {
+                    const int64_t len = (bytes - o) < 32768 ? (bytes - o) : 32768;
+                    bulk_prefetch_l2(base + o, (uint32_t)len);
+                }
+            };
+            for (int pf = 0; pf < p.prefetch_tiles; pf++) prefetch_tile((int64_t)blockIdx.x + (int64_t)pf * gridDim.x);
             for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
                 const int row0 = (int)(t * kGemmTileN);
+                if (p.prefetch_tiles > 0) prefetch_tile(t + (int64_t)p.prefetch_tiles * gridDim.x);
                 for (int kb = 0; kb < p.num_kb; kb++) {
                     mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t* st = stages + (size_t)s * STAGE_BYTES;
@@ -294,6 +345,70 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             }
         }
         __syncwarp();
+    } else if (warp == 3) {
+        // ---------------- grid-wide threshold refresher ----------------
+        // hist[q][b] counts the rows that entered some CTA's list for query q with goodness in
+        // bucket b (goodness = score for IP, -value for L2).  The lower edge of the highest bucket
+        // whose suffix count reaches K' is a valid lower bound of the final K'-th best, and a far
+        // tighter one than any single CTA's own K'-th best.  This warp keeps publishing it.
+        const float sgn = L2 ? -1.f : 1.f;
+        int round = 0;
+        while (*s_done < N_EPI_WARPS) {
+            const int q = (int)(((int64_t)blockIdx.x + (int64_t)round * gridDim.x) % p.nq);
+            ++round;
+            const uint4* h4 = reinterpret_cast<const uint4*>(p.hist + (size_t)q * kGemmBuckets) + lane * 4;
+            unsigned c[16];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const uint4 t4 = __ldcg(h4 + u);
+                c[4 * u] = t4.x;
+                c[4 * u + 1] = t4.y;
+                c[4 * u + 2] = t4.z;
+                c[4 * u + 3] = t4.w;
+            }
+            unsigned tot = 0;
+#pragma unroll
+            for (int u = 0; u < 16; u++) tot += c[u];
+            // suffix sums across lanes: above = rows in the buckets of all higher lanes
+            unsigned incl = tot;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned up = __shfl_down_sync(0xffffffffu, incl, o);
+                if (lane + o < 32) incl += up;
+            }
+            const unsigned above = incl - tot;
+            const unsigned need = (unsigned)p.kprime;
+            const unsigned reach = __ballot_sync(0xffffffffu, incl >= need);
+            if (reach != 0) {
+                const int lstar = 31 - __clz(reach);  // highest lane whose suffix count reaches K'
+                if (lane == lstar) {
+                    unsigned run = above;
+                    int bstar = lane * 16;
+#pragma unroll
+                    for (int u = 15; u >= 0; u--) {
+                        run += c[u];
+                        if (run >= need) {
+                            bstar = lane * 16 + u;
+                            break;
+                        }
+                    }
+                    // one bucket of safety margin against rounding in the edge computation
+                    const float lo = p.qscale[2 * q], per_unit = p.qscale[2 * q + 1];
+                    if (bstar >= 1 && per_unit > 0.f) {
+                        const float edge = lo + (float)(bstar - 1) / per_unit;
+                        const float tval = sgn * edge;
+                        const float cur = dec_ordered(*reinterpret_cast<volatile int*>(p.gthr + q));
+                        if (better_val<L2>(tval, cur)) {
+                            if (L2)
+                                atomicMin(p.gthr + q, enc_ordered(tval));
+                            else
+                                atomicMax(p.gthr + q, enc_ordered(tval));
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+        }
     } else if (warp >= 4) {
         // ---------------- epilogue: one query per thread ----------------
         const int ew = warp - 4;
@@ -301,13 +416,26 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         const int quad = warp & 3;  // TMEM lane quadrant this warp may read
         const int qidx = mt * kGemmTileM + quad * 32 + lane;
         const bool active = qidx < p.nq;
+        // KP == 32: sorted list held entirely in registers (no memory traffic on insert: the
+        // L1 left over beside ~200 KB of pipeline smem is too small for local-memory lists).
+        // KP > 32: binary heap in local memory (list_offer).
         float lv[KP];
         uint32_t li[KP];
         const int kp = p.kprime;
-        int count = 0, widx = 0;
+        int count = 0;
+        if (KP == 32) {
+#pragma unroll
+            for (int j = 0; j < KP; j++) {
+                lv[j] = worst_val<L2>();
+                li[j] = kEmptyId;
+            }
+        }
         float lthr = worst_val<L2>();   // what a score must beat to enter THIS thread's list
         float thr = worst_val<L2>();    // effective filter: better of lthr and the grid-wide threshold
         int* gthr = p.gthr + qidx;      // grid-wide K'-th best so far for this query (ordered-int encoded)
+        unsigned* my_hist = p.hist + (size_t)qidx * kGemmBuckets;
+        const float h_lo = active ? p.qscale[2 * qidx] : 0.f;
+        const float h_per_unit = active ? p.qscale[2 * qidx + 1] : 0.f;
         float* my_norms = s_norms + ew * kGemmTileN;
         int64_t it = 0;
         for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
@@ -336,8 +464,9 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
 #pragma unroll 1
             for (int c = 0; c < kGemmTileN / 32; c++) {
                 uint32_t r[32];
+                if (p.debug_no_select == 2) continue;
                 tmem_ld32(taddr + c * 32, r);
-                if (active) {
+                if (active && p.debug_no_select == 0) {
                     float v[32];
                     float best;
                     if (L2) {
@@ -359,9 +488,33 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
 #pragma unroll
                         for (int j = 0; j < 32; j++)
                             if (better_val<L2>(v[j], thr) && rbase + j < p.n_rows) {
-                                list_offer<KP, L2>(lv, li, kp, count, widx, lthr, v[j], (uint32_t)(rbase + j));
+                                if (KP == 32) {
+                                    // compare-exchange chain over the 32 register slots (static indices)
+                                    float cv = v[j];
+                                    uint32_t ci = (uint32_t)(rbase + j);
+#pragma unroll
+                                    for (int e = 0; e < 32; e++) {
+                                        const bool sw = better_val<L2>(cv, lv[e]);
+                                        const float tv = lv[e];
+                                        const uint32_t ti = li[e];
+                                        lv[e] = sw ? cv : tv;
+                                        li[e] = sw ? ci : ti;
+                                        cv = sw ? tv : cv;
+                                        ci = sw ? ti : ci;
+                                    }
+                                    lthr = lv[31];
+                                    count = 32;  // sentinel slots make the list "full" from the start
+                                } else {
+                                    list_offer<KP, L2>(lv, li, kp, count, lthr, v[j], (uint32_t)(rbase + j));
+                                }
                                 thr = better_of<L2>(lthr, g);
                                 improved = true;
+                                {
+                                    const float good = L2 ? -v[j] : v[j];
+                                    int b = (int)((good - h_lo) * h_per_unit);
+                                    b = b < 0 ? 0 : (b > kGemmBuckets - 1 ? kGemmBuckets - 1 : b);
+                                    atomicAdd(my_hist + b, 1u);
+                                }
                             }
                     }
                 }
@@ -370,21 +523,33 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty_bar[as]);
             // publish: only a FULL list's worst is a valid bound
-            if (active && improved && count >= kp && better_val<L2>(lthr, g)) {
+            if (active && improved && count >= kp && lthr != worst_val<L2>() && better_val<L2>(lthr, g)) {
                 if (L2)
                     atomicMin(gthr, enc_ordered(lthr));
                 else
                     atomicMax(gthr, enc_ordered(lthr));
             }
         }
+        __syncwarp();
+        if (lane == 0) atomicAdd(const_cast<int*>(s_done), 1);
         // survivors -> global, [cta][query][KP] (unsorted; unused slots empty)
         if (active) {
             Cand* dst = p.cand + ((size_t)blockIdx.x * (kGemmTileM * MT) + qidx) * KP;
-            for (int j = 0; j < kp; j++) {
-                Cand cnd;
-                cnd.v = j < count ? lv[j] : worst_val<L2>();
-                cnd.id = j < count ? li[j] : kEmptyId;
-                dst[j] = cnd;
+            if (KP == 32) {
+#pragma unroll
+                for (int j = 0; j < 32; j++) {
+                    Cand cnd;
+                    cnd.v = lv[j];
+                    cnd.id = li[j];
+                    dst[j] = cnd;
+                }
+            } else {
+                for (int j = 0; j < kp; j++) {
+                    Cand cnd;
+                    cnd.v = j < count ? lv[j] : worst_val<L2>();
+                    cnd.id = j < count ? li[j] : kEmptyId;
+                    dst[j] = cnd;
+                }
             }
         }
     }
@@ -574,9 +739,31 @@ __global__ void __launch_bounds__(kRescoreWarps * 32) rescore_kernel(const Resco
     }
 }
 
-__global__ void fill_i32_kernel(int* dst, int n, int value) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) dst[i] = value;
+// One warp per query slot: bucket map for the score histogram, zeroed histogram row, and the
+// grid-wide threshold preset to the worst value.
+//   IP : goodness = score      in [-B, B],               B = ||q|| * max||x||
+//   L2 : goodness = -(||x||^2 - 2 q.x) in [-(maxn + 2B), 2B]
+__global__ void gemm_prepare_kernel(const float* __restrict__ q, int d_pad, int nq, const unsigned* max_norm_bits,
+                                    int l2, unsigned* hist, float* qscale, int* gthr) {
+    const int qi = blockIdx.x;
+    const int lane = threadIdx.x;
+    float s = 0.f;
+    if (qi < nq)
+        for (int i = lane; i < d_pad; i += 32) {
+            const float v = q[(size_t)qi * d_pad + i];
+            s = fmaf(v, v, s);
+        }
+    s = warp_sum(s);
+    for (int b = lane; b < kGemmBuckets; b += 32) hist[(size_t)qi * kGemmBuckets + b] = 0u;
+    if (lane == 0) {
+        const float maxn = __uint_as_float(*max_norm_bits);
+        const float B = sqrtf(s) * sqrtf(maxn) * 1.001f + 1e-30f;
+        const float lo = l2 ? -(maxn + 2.f * B) : -B;
+        const float hi = l2 ? 2.f * B : B;
+        qscale[2 * qi] = lo;
+        qscale[2 * qi + 1] = (hi > lo) ? (float)kGemmBuckets / (hi - lo) : 0.f;
+        gthr[qi] = l2 ? 0x7F7FFFFF : (int)(0xFF7FFFFFu ^ 0x7FFFFFFFu);  // enc(+FLT_MAX) / enc(-FLT_MAX)
+    }
 }
 
 // max over rows of the squared norm, as float bits (non-negative floats order like uints)
@@ -647,12 +834,19 @@ static bool make_map(CUtensorMap* map, const void* base, int64_t rows, int d_pad
 }
 
 size_t gemm_cand_bytes(int grid, int nq_pad, int kp_cap) { return (size_t)grid * nq_pad * kp_cap * sizeof(Cand); }
+size_t gemm_aux_bytes() { return (size_t)kGemmMaxBlock * (kGemmBuckets * sizeof(unsigned) + 2 * sizeof(float) + sizeof(int)) + 1024; }
+void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr) {
+    uint8_t* b = reinterpret_cast<uint8_t*>(aux);
+    *hist = reinterpret_cast<unsigned*>(b);
+    *qscale = reinterpret_cast<float*>(b + (size_t)kGemmMaxBlock * kGemmBuckets * sizeof(unsigned));
+    *gthr = reinterpret_cast<int*>(b + (size_t)kGemmMaxBlock * (kGemmBuckets * sizeof(unsigned) + 2 * sizeof(float)));
+}
 
 // survivors kept per query: the slack beyond k must cover the rows whose approx score lies
 // within 2*eps of the k-th best; their number grows with k (and with N), so it scales with k
 int gemm_kp_cap(int k) { return (k + kGemmSlack <= 32) ? 32 : 256; }
 int gemm_kprime(int k) {
-    if (k + kGemmSlack <= 32) return k + kGemmSlack;
+    if (k + kGemmSlack <= 32) return 32;  // the register list below always holds 32
     const int kp = 2 * k + 24;
     return kp < 256 ? kp : 256;
 }
@@ -707,11 +901,17 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     p.norms = a.norms;
     p.cand = a.cand;
     p.gthr = a.gthr;
+    p.corpus = a.corpus;
     {
-        // grid-wide thresholds start at the worst value: enc(-FLT_MAX) for IP, enc(+FLT_MAX) for L2
-        const int worst_enc = a.l2 ? 0x7F7FFFFF : (int)(0xFF7FFFFFu ^ 0x7FFFFFFFu);
-        fill_i32_kernel<<<1, 256, 0, st>>>(a.gthr, 2 * kGemmTileM, worst_enc);
+        const char* ev = getenv("B200R_GEMM_PREFETCH");  // tuning knob
+        p.prefetch_tiles = ev ? atoi(ev) : 0;
+        const char* dv = getenv("B200R_GEMM_DEBUG_NOSELECT");
+        p.debug_no_select = dv ? atoi(dv) : 0;  // measured: the extra L2 fill stream hurts (r01 notes)
     }
+    p.hist = a.hist;
+    p.qscale = a.qscale;
+    gemm_prepare_kernel<<<MT * kGemmTileM, 32, 0, st>>>(a.q_f32, a.d_pad, a.nq, a.max_norm_bits, a.l2 ? 1 : 0, a.hist,
+                                                        a.qscale, a.gthr);
     p.evict_first = ((size_t)a.n_rows * a.d_pad * (a.bf16 ? 2 : 4) > ((size_t)96 << 20)) ? 1 : 0;
     int grid = (int)(p.n_tiles < a.num_sms ? p.n_tiles : a.num_sms);
     if (grid < 1) grid = 1;

@@ -66,6 +66,8 @@ struct GemmSearchArgs {
     int nq, k;
     Cand* cand;           // >= gemm_cand_bytes(num_sms, 256, gemm_kp_cap(k))
     int* gthr;            // [256] scratch: grid-wide per-query thresholds
+    unsigned* hist;       // [256][512] scratch: score histograms
+    float* qscale;        // [256][2] scratch: bucket maps
     const unsigned* max_norm_bits;
     float* out_d;
     int64_t* out_i;
@@ -78,6 +80,8 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st);
 cudaError_t launch_max_norm(const float* norms, int64_t n, unsigned* out_bits, cudaStream_t st);
 cudaError_t launch_f32_to_bf16(const float* src, void* dst, int64_t n, cudaStream_t st);
 size_t gemm_cand_bytes(int grid, int nq_pad, int kp_cap);
+size_t gemm_aux_bytes();
+void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr);
 int gemm_kp_cap(int k);
 
 // lets entry points outside api.cu fill b200r_last_error()

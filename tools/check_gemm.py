@@ -1,3 +1,6 @@
+"""Developer scratch tool (GPU box): see DESIGN.md section 4 for the numbers it produced."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, numpy as np, os, sys, time
 from generativeaiexamples_b200 import B200IndexFlat, _lib
 dev = torch.device("cuda",0)
