@@ -54,6 +54,22 @@ def _peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def _tensor_peaks():
+    """(tf32, bf16) dense TFLOP/s denominators: bf16 from MEASURED_PEAKS.json (sustained), tf32 from
+    profiles/tf32_peak.json (tools/measure_tf32_peak.py on this pool), else nominal 1.1 PF."""
+    bf16, tf32, src = 1400.0, 1100.0, "nominal"
+    try:
+        bf16 = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+    except Exception:
+        pass
+    try:
+        tf32 = float(json.load(open(os.path.join(ROOT, "profiles", "tf32_peak.json")))["tf32_tflops_sustained"])
+        src = "measured (profiles/tf32_peak.json, cuBLAS tf32 8192^3 sustained)"
+    except Exception:
+        pass
+    return tf32, bf16, src
+
+
 def _traffic():
     """dram bytes per launch of the scan kernel from the committed ncu capture, if any."""
     p = os.path.join(ROOT, "profiles", "scan_traffic.json")
@@ -312,10 +328,15 @@ def main_gpu(args):
         ms256, _ = timed(b256_step, args.batch256_steps, 1)
         per = ms256 / args.batch256_steps
         flops = 2.0 * 256 * n_total * DIM
+        tf32_peak, _, tf32_src = _tensor_peaks()
+        per_gpu_tflops = flops / world / (per * 1e-3) / 1e12
         b256 = {"value": 256 * 1000.0 / per, "unit": "queries/s", "ms_per_batch": per, "steps": args.batch256_steps,
+                "tensor_frac_tf32": per_gpu_tflops / tf32_peak, "tensor_peak_tflops": tf32_peak,
+                "tensor_peak_source": tf32_src,
                 "path": "scan x64 passes" if index.local.stats()["last_path"] == 1
                 else "tcgen05 tf32 GEMM filter + exact fp32 re-score", "gemm_fallbacks": index.local.stats()["n_gemm_fallbacks"], "achieved_tflops": flops / (per * 1e-3) / 1e12,
-                "hbm_fraction_single_pass": (max_rows * DIM * 4 / (per * 1e-3) / 1e9) / peak}
+                "hbm_frac": (max_rows * DIM * 4 / (per * 1e-3) / 1e9) / peak,
+                "note": "crossover config (128 flop/B): both fractions reported; flops = 2*nq*N*d, bytes = N*d*4"}
 
     if rank == 0:
         qps = args.steps * 1000.0 / ms_dev
@@ -355,7 +376,7 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=N_TOTAL, help="total corpus rows (default: the 10M headline config)")
-    ap.add_argument("--batch256-steps", type=int, default=2)
+    ap.add_argument("--batch256-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup

@@ -428,10 +428,12 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     DeviceGuard g(ix->device);
     const bool any_dev = q_mem_kind == B200R_DEVICE || out_mem_kind == B200R_DEVICE;
     cudaStream_t st = (any_dev || stream) ? (cudaStream_t)stream : ix->stream;
-    // dispatch mirrors faiss (distance_compute_blas_threshold = 20): small batches scan,
-    // large batches go through the tensor-core GEMM filter + exact re-score
+    // Two-way dispatch like faiss (scan for small batches, GEMM for large ones).  faiss switches
+    // at nq = 20 (distance_compute_blas_threshold); here the scan serves 4 queries per corpus pass
+    // and one GEMM pass costs about one scan pass, so the GEMM path wins from nq = 5.  Both paths
+    // end in the same fp32 scoring code, so the choice never changes a result.
     const char* env_thr = getenv("B200R_GEMM_MIN_NQ");
-    const int64_t gemm_min = env_thr ? atoll(env_thr) : 20;
+    const int64_t gemm_min = env_thr ? atoll(env_thr) : 5;
     const bool use_gemm = ix->ntotal > 0 && (ix->cfg.search_path == B200R_PATH_GEMM ||
                                              (ix->cfg.search_path == B200R_PATH_AUTO && nq >= gemm_min));
     const int64_t nq_slots = use_gemm ? round_up(nq, 128) : round_up(nq, kScanMaxNQ);
@@ -449,8 +451,17 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
         CU(cudaMemcpyAsync(ix->q_raw, ix->q_pin, (size_t)nq * ix->d * sizeof(float), cudaMemcpyHostToDevice, st));
         q_src = ix->q_raw;
     }
-    CU(launch_prep_queries(q_src, nq, ix->d, ix->d_pad, nq_slots, ix->cfg.normalize_queries != 0, ix->q_dev, st));
-    ix->st.n_kernel_launches++;
+    // device queries that need no padding, normalisation or zero-filled spare slots are used in place
+    const bool q_in_place = !use_gemm && q_mem_kind == B200R_DEVICE && ix->d == ix->d_pad &&
+                            !ix->cfg.normalize_queries && (nq == 1 || nq % kScanMaxNQ == 0) &&
+                            (reinterpret_cast<uintptr_t>(q) & 15) == 0;
+    const float* q_ready = ix->q_dev;
+    if (q_in_place) {
+        q_ready = (const float*)q;
+    } else {
+        CU(launch_prep_queries(q_src, nq, ix->d, ix->d_pad, nq_slots, ix->cfg.normalize_queries != 0, ix->q_dev, st));
+        ix->st.n_kernel_launches++;
+    }
 
     float* od = out_mem_kind == B200R_DEVICE ? D : ix->out_d;
     int64_t* oi = out_mem_kind == B200R_DEVICE ? I : ix->out_i;
@@ -511,7 +522,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     for (int64_t q0 = 0; q0 < nq; q0 += (use_gemm ? 1 : kScanMaxNQ)) {
         if (use_gemm && !ix->fail_pin[q0]) continue;  // only the queries whose check failed
         const int nqg = use_gemm ? 1 : (int)std::min<int64_t>(kScanMaxNQ, nq - q0);
-        p.q = ix->q_dev + (size_t)q0 * ix->d_pad;
+        p.q = q_ready + (size_t)q0 * ix->d_pad;
         p.out_d = od + (size_t)q0 * k;
         p.out_i = oi + (size_t)q0 * k;
         int grid = 0;
