@@ -355,7 +355,11 @@ def main_gpu(args):
                     "d2h_bytes_per_step": TOPK * 12, "api": "ShardedFlatIndex.search(numpy) -> b200r_search(HOST,HOST)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": (traffic or {}).get("dram_bytes_per_launch"), "peak_source": peak_src,
+                         "traffic": (algo_bytes * traffic["traffic_over_algorithmic"]) if traffic else None,
+                         "traffic_source": ("ncu dram__bytes_read+write per launch = %.4f x algorithmic bytes, measured on a "
+                                            "2M-row shard (%s), scaled to this shard" %
+                                            (traffic["traffic_over_algorithmic"], traffic["source"])) if traffic else None,
+                         "peak_source": peak_src,
                          "kernel": "scan_topk_kernel<1,1,IP,f32>", "kernel_ms": kernel_ms,
                          "algorithmic_bytes_per_launch": algo_bytes,
                          "note": "kernel_ms = prep_queries + scan launch, CUDA events on the launching stream"},

@@ -1,0 +1,76 @@
+"""GPU suite, multi-GPU part: ShardedFlatIndex over NCCL with 2 ranks (skipped on a 1-GPU box;
+the gloo tests in test_sharded_gloo.py cover the host logic everywhere)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, out):
+    import torch
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from generativeaiexamples_b200.sharded import ShardedFlatIndex
+
+        rng = np.random.default_rng(11)
+        n, d = 50001, 256
+        x = rng.standard_normal((n, d), dtype=np.float32)
+        q = rng.standard_normal((40, d), dtype=np.float32)
+        res = {}
+        for metric in (0, 1):
+            idx = ShardedFlatIndex(d, metric, device=rank)
+            idx.add(x)
+            assert idx.ntotal == n
+            for nq, k in ((1, 10), (3, 4), (40, 10)):   # scan path and GEMM path under the merge
+                D, I = idx.search(q[:nq], k)
+                res[(metric, nq, k)] = (D, I)
+            Dd, Id = idx.search(torch.from_numpy(q[:2]).cuda(), 5)  # device in -> device out
+            res[(metric, "dev")] = (Dd.cpu().numpy(), Id.cpu().numpy())
+        if rank == 0:
+            out.put(res)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_nccl_two_ranks(built_lib):
+    import torch
+    import torch.multiprocessing as mp
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from oracle import assert_topk_parity, truth_topk
+
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = out.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    rng = np.random.default_rng(11)
+    x = rng.standard_normal((50001, 256), dtype=np.float32)
+    q = rng.standard_normal((40, 256), dtype=np.float32)
+    for (metric, nq, k), (D, I) in ((kk, v) for kk, v in res.items() if kk[1] != "dev"):
+        Dt, It = truth_topk("l2" if metric else "ip", q[:nq], x, k + 8)
+        assert_topk_parity(D, I, Dt, It, what=f"sharded nccl metric={metric} nq={nq} k={k}")
+    for metric in (0, 1):
+        D, I = res[(metric, "dev")]
+        Dt, It = truth_topk("l2" if metric else "ip", q[:2], x, 13)
+        assert_topk_parity(D, I, Dt, It, what="sharded nccl device tensors")
