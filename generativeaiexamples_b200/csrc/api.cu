@@ -488,13 +488,13 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
             a.k = k;
             a.cand = ix->gemm_cand;
             a.max_norm_bits = ix->max_norm_bits;
-            gemm_aux_layout(ix->gemm_aux, &a.hist, &a.qscale, &a.gthr);
+            gemm_aux_layout(ix->gemm_aux, &a.hist, &a.qscale, &a.gthr, &a.list_counts);
             a.out_d = od + (size_t)q0 * k;
             a.out_i = oi + (size_t)q0 * k;
             a.id_base = ix->cfg.id_base;
             a.fail_flags = ix->fail_dev + q0;
             a.fail_count = fail_count;
-            a.num_sms = ix->num_sms;
+            a.num_sms = std::min(ix->num_sms, kGemmMaxGrid);
             CU(launch_gemm_search(a, st));
             ix->st.n_kernel_launches += 3;
             ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;

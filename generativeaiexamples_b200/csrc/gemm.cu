@@ -147,6 +147,8 @@ struct GemmParams {
     int prefetch_tiles;   // tiles of look-ahead for that stream (0 = off)
     unsigned* hist;       // [128*MT][kGemmBuckets] rows inserted so far per goodness bucket (zeroed per launch)
     const float* qscale;  // [128*MT][2] bucket map per query: goodness lo, buckets per unit
+    int warmup;           // 1: first tile of each CTA only feeds the histogram and is replayed at the end
+    int* list_counts;     // [grid][128*MT] valid entries in each survivor list
     int debug_no_select;  // timing experiments only: 1 = skip the selection, 2 = also skip the TMEM loads
     int evict_first;
 };
@@ -257,6 +259,10 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
     const uint32_t tmem_base = *tmem_slot;
 
     const int64_t n_tiles = p.n_tiles;
+    // tiles of this CTA: blockIdx.x, +grid, ...; with warm-up the first one is visited once more at the end
+    const int64_t n_my = (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    const int64_t n_iter = n_my + (p.warmup ? 1 : 0);
+    auto tile_of = [&](int64_t i) -> int64_t { return (int64_t)blockIdx.x + (i < n_my ? i : 0) * (int64_t)gridDim.x; };
 
     if (warp == 0) {
         // ---------------- TMA producer ----------------
@@ -282,7 +288,8 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                 }
             };
             for (int pf = 0; pf < p.prefetch_tiles; pf++) prefetch_tile((int64_t)blockIdx.x + (int64_t)pf * gridDim.x);
-            for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            for (int64_t i = 0; i < n_iter; i++) {
+                const int64_t t = tile_of(i);
                 const int row0 = (int)(t * kGemmTileN);
                 if (p.prefetch_tiles > 0) prefetch_tile(t + (int64_t)p.prefetch_tiles * gridDim.x);
                 for (int kb = 0; kb < p.num_kb; kb++) {
@@ -314,8 +321,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                                    ((uint32_t)(kGemmTileM >> 4) << 24);
             int s = 0;
             uint32_t ph = 0;
-            int64_t it = 0;
-            for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+            for (int64_t it = 0; it < n_iter; ++it) {
                 const int as = (int)(it % ACC_STAGES);
                 const uint32_t aph = (uint32_t)((it / ACC_STAGES) & 1);
                 mbar_wait(&tempty_bar[as], aph ^ 1);
@@ -354,7 +360,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         const float sgn = L2 ? -1.f : 1.f;
         int round = 0;
         while (*s_done < N_EPI_WARPS) {
-            const int q = (int)(((int64_t)blockIdx.x + (int64_t)round * gridDim.x) % p.nq);
+            const int q = (int)(((int64_t)blockIdx.x + (int64_t)round) % p.nq);  // every CTA walks all queries
             ++round;
             const uint4* h4 = reinterpret_cast<const uint4*>(p.hist + (size_t)q * kGemmBuckets) + lane * 4;
             unsigned c[16];
@@ -437,8 +443,10 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         const float h_lo = active ? p.qscale[2 * qidx] : 0.f;
         const float h_per_unit = active ? p.qscale[2 * qidx + 1] : 0.f;
         float* my_norms = s_norms + ew * kGemmTileN;
-        int64_t it = 0;
-        for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++it) {
+        for (int64_t it = 0; it < n_iter; ++it) {
+            const int64_t t = tile_of(it);
+            const bool hist_only = p.warmup && it == 0;     // feed the histogram, keep nothing
+            const bool replay = p.warmup && it == n_my;     // second visit: rows are already counted
             const int as = (int)(it % ACC_STAGES);
             const uint32_t aph = (uint32_t)((it / ACC_STAGES) & 1);
             const int64_t row0 = t * kGemmTileN;
@@ -483,7 +491,17 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
 #pragma unroll
                         for (int j = 1; j < 32; j++) best = fmaxf(best, v[j]);
                     }
-                    if (better_val<L2>(best, thr)) {
+                    if (hist_only) {
+                        const int64_t rbase = row0 + c * 32;
+#pragma unroll
+                        for (int j = 0; j < 32; j++)
+                            if (rbase + j < p.n_rows) {
+                                const float good = L2 ? -v[j] : v[j];
+                                int b = (int)((good - h_lo) * h_per_unit);
+                                b = b < 0 ? 0 : (b > kGemmBuckets - 1 ? kGemmBuckets - 1 : b);
+                                atomicAdd(my_hist + b, 1u);
+                            }
+                    } else if (better_val<L2>(best, thr)) {
                         const int64_t rbase = row0 + c * 32;
 #pragma unroll
                         for (int j = 0; j < 32; j++)
@@ -509,7 +527,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                                 }
                                 thr = better_of<L2>(lthr, g);
                                 improved = true;
-                                {
+                                if (!replay) {
                                     const float good = L2 ? -v[j] : v[j];
                                     int b = (int)((good - h_lo) * h_per_unit);
                                     b = b < 0 ? 0 : (b > kGemmBuckets - 1 ? kGemmBuckets - 1 : b);
@@ -522,6 +540,13 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty_bar[as]);
+            if (hist_only && active) {
+                // give the refresher warps (any CTA's) a moment to turn the first counts into a
+                // threshold; bounded wait, the result is correct with or without it
+                const long long t_end = clock64() + 40000;
+                while (dec_ordered(*reinterpret_cast<volatile int*>(gthr)) == worst_val<L2>() && clock64() < t_end) {
+                }
+            }
             // publish: only a FULL list's worst is a valid bound
             if (active && improved && count >= kp && lthr != worst_val<L2>() && better_val<L2>(lthr, g)) {
                 if (L2)
@@ -536,18 +561,24 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         if (active) {
             Cand* dst = p.cand + ((size_t)blockIdx.x * (kGemmTileM * MT) + qidx) * KP;
             if (KP == 32) {
+                int nv = 0;
 #pragma unroll
                 for (int j = 0; j < 32; j++) {
                     Cand cnd;
                     cnd.v = lv[j];
                     cnd.id = li[j];
-                    dst[j] = cnd;
+                    if (li[j] != kEmptyId) {  // sorted: the valid entries come first
+                        dst[j] = cnd;
+                        nv++;
+                    }
                 }
+                p.list_counts[(size_t)blockIdx.x * (kGemmTileM * MT) + qidx] = nv;
             } else {
-                for (int j = 0; j < kp; j++) {
+                p.list_counts[(size_t)blockIdx.x * (kGemmTileM * MT) + qidx] = count;
+                for (int j = 0; j < count; j++) {
                     Cand cnd;
-                    cnd.v = j < count ? lv[j] : worst_val<L2>();
-                    cnd.id = j < count ? li[j] : kEmptyId;
+                    cnd.v = lv[j];
+                    cnd.id = li[j];
                     dst[j] = cnd;
                 }
             }
@@ -573,6 +604,8 @@ struct RescoreParams {
     int d_pad, row_bytes;
     const float* q;        // [nq][d_pad] fp32 (prepared)
     const Cand* cand;      // [grid][q_stride][KP] approx survivors
+    const int* list_counts; // [grid][q_stride]
+    const float* qscale;    // [q_stride][2] the filter's bucket map
     int grid, q_stride, kp_stride, kprime, k;
     const unsigned* max_norm_bits;  // max_i ||x_i||^2 as float bits
     float err_coeff;       // c in eps = c * ||q|| * max||x||
@@ -583,14 +616,49 @@ struct RescoreParams {
     int* fail_count;
 };
 
-template <int KPL, bool L2, bool BF16>
+// block-wide bitonic sort of n (a power of two) candidates in shared memory, best first;
+// ties on the score go to the lower id, as everywhere else
+template <bool L2>
+__device__ void block_sort_best_first(Cand* a, int n) {
+    for (int k = 2; k <= n; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < n; i += blockDim.x) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const Cand x = a[i], y = a[ixj];
+                    const bool first_half = (i & k) == 0;  // this sub-sequence is sorted best-first
+                    const bool swap = first_half ? better<L2>(y.v, y.id, x.v, x.id) : better<L2>(x.v, x.id, y.v, y.id);
+                    if (swap) {
+                        a[i] = y;
+                        a[ixj] = x;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__device__ __forceinline__ int next_pow2(int v, int lo) {
+    int p2 = lo;
+    while (p2 < v) p2 <<= 1;
+    return p2;
+}
+
+constexpr int kRescoreCap = 2048;    // selected candidates (K' + one boundary bucket) that fit the sort buffer
+constexpr int kRescoreMaxKp = 256;
+
+template <bool L2, bool BF16>
 __global__ void __launch_bounds__(kRescoreWarps * 32) rescore_kernel(const RescoreParams p) {
     extern __shared__ __align__(16) uint8_t rs_smem[];
-    float* qs = reinterpret_cast<float*>(rs_smem);                   // [d_pad]
-    Cand* surv = reinterpret_cast<Cand*>(qs + p.d_pad);              // [KPL*32] approx survivors
-    float* exact = reinterpret_cast<float*>(surv + KPL * 32);        // [KPL*32]
+    float* qs = reinterpret_cast<float*>(rs_smem);              // [d_pad]
+    Cand* buf = reinterpret_cast<Cand*>(qs + p.d_pad);          // [kRescoreCap] approx survivors, then sorted
+    Cand* ex = buf + kRescoreCap;                               // [kRescoreMaxKp] exact scores of the K' best
     __shared__ float s_red[kRescoreWarps];
     __shared__ float s_qnorm2;
+    __shared__ int s_off[kGemmMaxGrid + 1];
+    __shared__ unsigned s_hist[kGemmBuckets];
+    __shared__ int s_nsel, s_bstar;
 
     const int qi = blockIdx.x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -603,139 +671,210 @@ __global__ void __launch_bounds__(kRescoreWarps * 32) rescore_kernel(const Resco
     }
     part = warp_sum(part);
     if (lane == 0) s_red[warp] = part;
-
-    // warp 0: merge the per-CTA survivor lists into the K' best approx scores
-    if (warp == 0) {
-        WarpTopK<KPL, L2> m;
-        m.init(p.kprime);
-        for (int g = 0; g < p.grid; g++) {
-            const Cand* src = p.cand + ((size_t)g * p.q_stride + qi) * p.kp_stride;
-#pragma unroll
-            for (int j = 0; j < KPL; j++) {
-                const int e = j * 32 + lane;
-                Cand c;
-                c.v = worst_val<L2>();
-                c.id = kEmptyId;
-                if (e < p.kprime) c = src[e];
-                m.offer_lanes(c.v, c.id);  // per-CTA lists are unsorted
-            }
-        }
-        m.store(surv);
+    // survivors per CTA list -> offsets
+    for (int g = threadIdx.x; g < p.grid; g += blockDim.x) {
+        int n_e = p.list_counts[(size_t)g * p.q_stride + qi];
+        s_off[g + 1] = n_e < p.kp_stride ? n_e : p.kp_stride;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
         float s = 0.f;
         for (int w = 0; w < kRescoreWarps; w++) s += s_red[w];
         s_qnorm2 = s;
+        int run = 0;
+        s_off[0] = 0;
+        for (int g = 0; g < p.grid; g++) {
+            run += s_off[g + 1];
+            s_off[g + 1] = run;
+        }
     }
+    __syncthreads();
+    const int total = s_off[p.grid];
+    // Select the K' best approx scores among the `total` survivors of all CTAs without sorting
+    // them all: histogram over the filter's own bucket map -> boundary bucket b* -> collect the
+    // candidates at or above b* (K' plus one bucket's worth) -> sort only those.
+    const float h_lo = p.qscale[2 * qi], h_per_unit = p.qscale[2 * qi + 1];
+    auto bucket_of = [&](float v) -> int {
+        const float good = L2 ? -v : v;
+        int bk = (int)((good - h_lo) * h_per_unit);
+        return bk < 0 ? 0 : (bk > kGemmBuckets - 1 ? kGemmBuckets - 1 : bk);
+    };
+    for (int i = threadIdx.x; i < kGemmBuckets; i += blockDim.x) s_hist[i] = 0u;
+    if (threadIdx.x == 0) s_nsel = 0;
+    __syncthreads();
+    int bstar = 0;
+    if (total > p.kprime) {
+        for (int g = warp; g < p.grid; g += kRescoreWarps) {
+            const Cand* src = p.cand + ((size_t)g * p.q_stride + qi) * p.kp_stride;
+            const int n_e = s_off[g + 1] - s_off[g];
+            for (int e = lane; e < n_e; e += 32) atomicAdd(&s_hist[bucket_of(src[e].v)], 1u);
+        }
+        __syncthreads();
+        if (warp == 0) {
+            unsigned c16[16], tot = 0;
+#pragma unroll
+            for (int u = 0; u < 16; u++) {
+                c16[u] = s_hist[lane * 16 + u];
+                tot += c16[u];
+            }
+            unsigned incl = tot;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned up = __shfl_down_sync(0xffffffffu, incl, o);
+                if (lane + o < 32) incl += up;
+            }
+            const unsigned need = (unsigned)p.kprime;
+            const unsigned reach = __ballot_sync(0xffffffffu, incl >= need);
+            const int lstar = 31 - __clz(reach);  // reach != 0 because total > K'
+            if (lane == lstar) {
+                unsigned run = incl - tot;
+                int bs = lane * 16;
+#pragma unroll
+                for (int u = 15; u >= 0; u--) {
+                    run += c16[u];
+                    if (run >= need) {
+                        bs = lane * 16 + u;
+                        break;
+                    }
+                }
+                s_bstar = bs;
+            }
+        }
+        __syncthreads();
+        bstar = s_bstar;
+    }
+    for (int g = warp; g < p.grid; g += kRescoreWarps) {
+        const Cand* src = p.cand + ((size_t)g * p.q_stride + qi) * p.kp_stride;
+        const int n_e = s_off[g + 1] - s_off[g];
+        for (int e = lane; e < n_e; e += 32) {
+            const Cand c = src[e];
+            if (bucket_of(c.v) >= bstar) {
+                const int pos = atomicAdd(&s_nsel, 1);
+                if (pos < kRescoreCap) buf[pos] = c;
+            }
+        }
+    }
+    __syncthreads();
+    const int n_sel = s_nsel;
+    if (n_sel > kRescoreCap) {
+        // one bucket holds thousands of candidates (massive ties): let the scan path answer
+        if (threadIdx.x == 0) {
+            p.fail_flags[qi] = 1;
+            atomicAdd(p.fail_count, 1);
+        }
+        return;
+    }
+    {
+        const int P = next_pow2(n_sel, 32);
+        for (int i = n_sel + threadIdx.x; i < P; i += blockDim.x) {
+            Cand c;
+            c.v = worst_val<L2>();
+            c.id = kEmptyId;
+            buf[i] = c;
+        }
+        __syncthreads();
+        block_sort_best_first<L2>(buf, P);
+    }
+    const int n_valid = n_sel < p.kprime ? n_sel : p.kprime;   // the K' best approx scores: buf[0..n_valid)
 
     // all warps: exact fp32 score of every survivor, same lane mapping / summation order as
     // the scan kernel (4 partial sums per lane, butterfly)
     const int nvec = BF16 ? (p.d_pad >> 3) : (p.d_pad >> 2);
-    for (int c = warp; c < p.kprime; c += kRescoreWarps) {
-        const uint32_t id = surv[c].id;
-        float sc = worst_val<L2>();
-        if (id != kEmptyId) {
-            const uint4* xr = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(p.corpus) +
-                                                             (size_t)id * p.row_bytes);
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-            for (int i = lane; i < nvec; i += 32) {
-                const uint4 xv = __ldg(xr + i);
-                if (!BF16) {
-                    const float4 qv = reinterpret_cast<const float4*>(qs)[i];
-                    const float x0 = __uint_as_float(xv.x), x1 = __uint_as_float(xv.y), x2 = __uint_as_float(xv.z),
-                                x3 = __uint_as_float(xv.w);
-                    if (L2) {
-                        const float t0 = qv.x - x0, t1 = qv.y - x1, t2 = qv.z - x2, t3 = qv.w - x3;
-                        a0 = fmaf(t0, t0, a0);
-                        a1 = fmaf(t1, t1, a1);
-                        a2 = fmaf(t2, t2, a2);
-                        a3 = fmaf(t3, t3, a3);
-                    } else {
-                        a0 = fmaf(qv.x, x0, a0);
-                        a1 = fmaf(qv.y, x1, a1);
-                        a2 = fmaf(qv.z, x2, a2);
-                        a3 = fmaf(qv.w, x3, a3);
-                    }
+    for (int c = warp; c < n_valid; c += kRescoreWarps) {
+        const uint32_t id = buf[c].id;
+        const uint4* xr = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(p.corpus) +
+                                                         (size_t)id * p.row_bytes);
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        for (int i = lane; i < nvec; i += 32) {
+            const uint4 xv = __ldg(xr + i);
+            if (!BF16) {
+                const float4 qv = reinterpret_cast<const float4*>(qs)[i];
+                const float x0 = __uint_as_float(xv.x), x1 = __uint_as_float(xv.y), x2 = __uint_as_float(xv.z),
+                            x3 = __uint_as_float(xv.w);
+                if (L2) {
+                    const float t0 = qv.x - x0, t1 = qv.y - x1, t2 = qv.z - x2, t3 = qv.w - x3;
+                    a0 = fmaf(t0, t0, a0);
+                    a1 = fmaf(t1, t1, a1);
+                    a2 = fmaf(t2, t2, a2);
+                    a3 = fmaf(t3, t3, a3);
                 } else {
-                    const float4 qa = reinterpret_cast<const float4*>(qs)[2 * i];
-                    const float4 qb = reinterpret_cast<const float4*>(qs)[2 * i + 1];
-                    const float qq[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
-                    const float x[8] = {__uint_as_float(xv.x << 16), __uint_as_float(xv.x & 0xffff0000u),
-                                        __uint_as_float(xv.y << 16), __uint_as_float(xv.y & 0xffff0000u),
-                                        __uint_as_float(xv.z << 16), __uint_as_float(xv.z & 0xffff0000u),
-                                        __uint_as_float(xv.w << 16), __uint_as_float(xv.w & 0xffff0000u)};
-                    float acc[4] = {a0, a1, a2, a3};
-#pragma unroll
-                    for (int e = 0; e < 8; e++) {
-                        if (L2) {
-                            const float tt = qq[e] - x[e];
-                            acc[e & 3] = fmaf(tt, tt, acc[e & 3]);
-                        } else {
-                            acc[e & 3] = fmaf(qq[e], x[e], acc[e & 3]);
-                        }
-                    }
-                    a0 = acc[0];
-                    a1 = acc[1];
-                    a2 = acc[2];
-                    a3 = acc[3];
+                    a0 = fmaf(qv.x, x0, a0);
+                    a1 = fmaf(qv.y, x1, a1);
+                    a2 = fmaf(qv.z, x2, a2);
+                    a3 = fmaf(qv.w, x3, a3);
                 }
+            } else {
+                const float4 qa = reinterpret_cast<const float4*>(qs)[2 * i];
+                const float4 qb = reinterpret_cast<const float4*>(qs)[2 * i + 1];
+                const float qq[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+                const float x[8] = {__uint_as_float(xv.x << 16), __uint_as_float(xv.x & 0xffff0000u),
+                                    __uint_as_float(xv.y << 16), __uint_as_float(xv.y & 0xffff0000u),
+                                    __uint_as_float(xv.z << 16), __uint_as_float(xv.z & 0xffff0000u),
+                                    __uint_as_float(xv.w << 16), __uint_as_float(xv.w & 0xffff0000u)};
+                float acc[4] = {a0, a1, a2, a3};
+#pragma unroll
+                for (int e = 0; e < 8; e++) {
+                    if (L2) {
+                        const float tt = qq[e] - x[e];
+                        acc[e & 3] = fmaf(tt, tt, acc[e & 3]);
+                    } else {
+                        acc[e & 3] = fmaf(qq[e], x[e], acc[e & 3]);
+                    }
+                }
+                a0 = acc[0];
+                a1 = acc[1];
+                a2 = acc[2];
+                a3 = acc[3];
             }
-            sc = warp_sum((a0 + a2) + (a1 + a3));
         }
-        if (lane == 0) exact[c] = sc;
+        const float sc = warp_sum((a0 + a2) + (a1 + a3));
+        if (lane == 0) {
+            Cand c2;
+            c2.v = sc;
+            c2.id = id;
+            ex[c] = c2;
+        }
+    }
+    const int P2 = next_pow2(n_valid, 32);
+    for (int i = n_valid + threadIdx.x; i < P2; i += blockDim.x) {
+        Cand c;
+        c.v = worst_val<L2>();
+        c.id = kEmptyId;
+        ex[i] = c;
     }
     __syncthreads();
+    block_sort_best_first<L2>(ex, P2);
 
-    // warp 0: exact top-k among the survivors + the containment check
-    if (warp == 0) {
-        WarpTopK<KPL, L2> m;
-        m.init(p.k);
-        int n_valid = 0;
-        float approx_worst = worst_val<L2>();  // approx score of the K'-th survivor
-#pragma unroll
-        for (int j = 0; j < KPL; j++) {
-            const int e = j * 32 + lane;
-            float v = worst_val<L2>();
-            uint32_t id = kEmptyId;
-            if (e < p.kprime) {
-                id = surv[e].id;
-                if (id != kEmptyId) v = exact[e];
-            }
-            n_valid += __popc(__ballot_sync(0xffffffffu, id != kEmptyId));
-            m.offer_lanes(v, id);
-        }
-        if (n_valid > 0) approx_worst = surv[n_valid - 1].v;
-        // every row outside the survivors has approx score no better than approx_worst
-        // (only meaningful when the list is full; otherwise every row IS a survivor)
+    // exact top-k = ex[0..k) + the containment check
+    for (int e = threadIdx.x; e < p.k; e += blockDim.x) {
+        Cand c;
+        c.v = worst_val<L2>();
+        c.id = kEmptyId;
+        if (e < P2) c = ex[e];
+        p.out_d[(size_t)qi * p.k + e] = c.v;
+        p.out_i[(size_t)qi * p.k + e] = (c.id == kEmptyId) ? -1 : (int64_t)c.id + p.id_base;
+    }
+    if (threadIdx.x == 0) {
         bool ok = true;
-        if (n_valid >= p.kprime && (int64_t)n_valid < p.n_rows) {
+        // every row outside buf[0..n_valid) has an approx score no better than buf[n_valid-1]
+        // (only meaningful when K' survivors exist; otherwise every row seen IS a survivor)
+        if (total >= p.kprime && (int64_t)n_valid < p.n_rows) {
+            const float approx_worst = buf[n_valid - 1].v;
             const float qn = sqrtf(s_qnorm2);
             const float xn = sqrtf(__uint_as_float(*p.max_norm_bits));
             float eps = p.err_coeff * qn * xn;
+            const Cand kth = (p.k - 1 < P2) ? ex[p.k - 1] : ex[P2 - 1];
             if (L2) {
                 // approx value is ||x||^2 - 2 q.x~ ; exact is sum (q-x)^2 = ||q||^2 + ||x||^2 - 2 q.x
                 eps = 2.f * eps + 1e-6f * (s_qnorm2 + xn * xn);
-                const float kth = m.thr;  // exact k-th smallest (FLT_MAX if fewer than k)
-                ok = (kth - s_qnorm2) < approx_worst - eps;
+                ok = (kth.v - s_qnorm2) < approx_worst - eps;
             } else {
-                const float kth = m.thr;
-                ok = kth > approx_worst + eps;
+                ok = kth.v > approx_worst + eps;
             }
-            if (m.thr_id == kEmptyId) ok = false;  // fewer than k finite survivors: be safe
+            if (kth.id == kEmptyId) ok = false;  // fewer than k finite survivors: be safe
         }
-#pragma unroll
-        for (int j = 0; j < KPL; j++) {
-            const int e = j * 32 + lane;
-            if (e < p.k) {
-                p.out_d[(size_t)qi * p.k + e] = m.v[j];
-                p.out_i[(size_t)qi * p.k + e] = (m.id[j] == kEmptyId) ? -1 : (int64_t)m.id[j] + p.id_base;
-            }
-        }
-        if (lane == 0) {
-            p.fail_flags[qi] = ok ? 0 : 1;
-            if (!ok) atomicAdd(p.fail_count, 1);
-        }
+        p.fail_flags[qi] = ok ? 0 : 1;
+        if (!ok) atomicAdd(p.fail_count, 1);
     }
 }
 
@@ -834,12 +973,16 @@ static bool make_map(CUtensorMap* map, const void* base, int64_t rows, int d_pad
 }
 
 size_t gemm_cand_bytes(int grid, int nq_pad, int kp_cap) { return (size_t)grid * nq_pad * kp_cap * sizeof(Cand); }
-size_t gemm_aux_bytes() { return (size_t)kGemmMaxBlock * (kGemmBuckets * sizeof(unsigned) + 2 * sizeof(float) + sizeof(int)) + 1024; }
-void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr) {
+size_t gemm_aux_bytes() {
+    return (size_t)kGemmMaxBlock * (kGemmBuckets * sizeof(unsigned) + 2 * sizeof(float) + sizeof(int)) +
+           (size_t)kGemmMaxGrid * kGemmMaxBlock * sizeof(int) + 1024;
+}
+void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr, int** list_counts) {
     uint8_t* b = reinterpret_cast<uint8_t*>(aux);
     *hist = reinterpret_cast<unsigned*>(b);
     *qscale = reinterpret_cast<float*>(b + (size_t)kGemmMaxBlock * kGemmBuckets * sizeof(unsigned));
     *gthr = reinterpret_cast<int*>(b + (size_t)kGemmMaxBlock * (kGemmBuckets * sizeof(unsigned) + 2 * sizeof(float)));
+    *list_counts = *gthr + kGemmMaxBlock;
 }
 
 // survivors kept per query: the slack beyond k must cover the rows whose approx score lies
@@ -871,12 +1014,20 @@ static cudaError_t launch_filter_l2(bool l2, const CUtensorMap& mq, const CUtens
               : launch_filter_one<BF16, MT, KP, false>(mq, mx, p, grid, st);
 }
 
-template <int KPL, bool L2>
+template <bool L2>
 static cudaError_t launch_rescore_bf(bool bf16, const RescoreParams& rp, int nq, size_t smem, cudaStream_t st) {
-    if (bf16)
-        rescore_kernel<KPL, L2, true><<<nq, kRescoreWarps * 32, smem, st>>>(rp);
-    else
-        rescore_kernel<KPL, L2, false><<<nq, kRescoreWarps * 32, smem, st>>>(rp);
+    cudaError_t e;
+    if (bf16) {
+        auto kern = rescore_kernel<L2, true>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        kern<<<nq, kRescoreWarps * 32, smem, st>>>(rp);
+    } else {
+        auto kern = rescore_kernel<L2, false>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        kern<<<nq, kRescoreWarps * 32, smem, st>>>(rp);
+    }
     return cudaGetLastError();
 }
 
@@ -909,12 +1060,20 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
         p.debug_no_select = dv ? atoi(dv) : 0;  // measured: the extra L2 fill stream hurts (r01 notes)
     }
     p.hist = a.hist;
+    p.list_counts = a.list_counts;
     p.qscale = a.qscale;
     gemm_prepare_kernel<<<MT * kGemmTileM, 32, 0, st>>>(a.q_f32, a.d_pad, a.nq, a.max_norm_bits, a.l2 ? 1 : 0, a.hist,
                                                         a.qscale, a.gthr);
     p.evict_first = ((size_t)a.n_rows * a.d_pad * (a.bf16 ? 2 : 4) > ((size_t)96 << 20)) ? 1 : 0;
     int grid = (int)(p.n_tiles < a.num_sms ? p.n_tiles : a.num_sms);
     if (grid < 1) grid = 1;
+    {
+        // warm-up pays one extra tile per CTA; worth it when the lists are large (memory heaps)
+        // and every CTA has several tiles
+        const char* wv = getenv("B200R_GEMM_WARMUP");
+        p.warmup = (kp_cap > 32 && p.n_tiles >= 4 * (int64_t)grid) ? 1 : 0;
+        if (wv) p.warmup = atoi(wv) && p.n_tiles >= (int64_t)grid;
+    }
     cudaError_t e;
     if (a.bf16) {
         if (MT == 1)
@@ -940,6 +1099,8 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     rp.row_bytes = a.d_pad * (a.bf16 ? 2 : 4);
     rp.q = a.q_f32;
     rp.cand = a.cand;
+    rp.list_counts = a.list_counts;
+    rp.qscale = a.qscale;
     rp.grid = grid;
     rp.q_stride = MT * kGemmTileM;
     rp.kp_stride = kp_cap;
@@ -952,14 +1113,8 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     rp.id_base = a.id_base;
     rp.fail_flags = a.fail_flags;
     rp.fail_count = a.fail_count;
-    const int kpl = kp_cap == 32 ? 1 : 8;
-    const size_t rs_smem = (size_t)a.d_pad * sizeof(float) + (size_t)kpl * 32 * (sizeof(Cand) + sizeof(float));
-    if (kpl == 1)
-        e = a.l2 ? launch_rescore_bf<1, true>(a.bf16, rp, a.nq, rs_smem, st)
-                 : launch_rescore_bf<1, false>(a.bf16, rp, a.nq, rs_smem, st);
-    else
-        e = a.l2 ? launch_rescore_bf<8, true>(a.bf16, rp, a.nq, rs_smem, st)
-                 : launch_rescore_bf<8, false>(a.bf16, rp, a.nq, rs_smem, st);
+    const size_t rs_smem = (size_t)a.d_pad * sizeof(float) + (size_t)(kRescoreCap + kRescoreMaxKp) * sizeof(Cand);
+    e = a.l2 ? launch_rescore_bf<true>(a.bf16, rp, a.nq, rs_smem, st) : launch_rescore_bf<false>(a.bf16, rp, a.nq, rs_smem, st);
     return e;
 }
 

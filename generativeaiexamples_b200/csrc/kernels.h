@@ -55,6 +55,7 @@ cudaError_t launch_merge(bool l2, const float* cand_d, const int64_t* cand_i, in
 // K3 (gemm.cu): tcgen05 GEMM filter + exact re-score for one block of <= 256 queries
 constexpr int kGemmSlack = 22;       // survivors kept beyond k when k + slack <= 32
 constexpr int kGemmMaxBlock = 256;   // queries per GEMM launch (two 128-row M tiles)
+constexpr int kGemmMaxGrid = 256;    // CTAs of a GEMM launch never exceed the SM count (148 on B200)
 struct GemmSearchArgs {
     const void* corpus;
     const float* norms;
@@ -68,6 +69,7 @@ struct GemmSearchArgs {
     int* gthr;            // [256] scratch: grid-wide per-query thresholds
     unsigned* hist;       // [256][512] scratch: score histograms
     float* qscale;        // [256][2] scratch: bucket maps
+    int* list_counts;     // [grid][256] scratch: survivors per (CTA, query)
     const unsigned* max_norm_bits;
     float* out_d;
     int64_t* out_i;
@@ -81,7 +83,7 @@ cudaError_t launch_max_norm(const float* norms, int64_t n, unsigned* out_bits, c
 cudaError_t launch_f32_to_bf16(const float* src, void* dst, int64_t n, cudaStream_t st);
 size_t gemm_cand_bytes(int grid, int nq_pad, int kp_cap);
 size_t gemm_aux_bytes();
-void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr);
+void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr, int** list_counts);
 int gemm_kp_cap(int k);
 
 // lets entry points outside api.cu fill b200r_last_error()
