@@ -488,7 +488,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
             a.k = k;
             a.cand = ix->gemm_cand;
             a.max_norm_bits = ix->max_norm_bits;
-            gemm_aux_layout(ix->gemm_aux, &a.hist, &a.qscale, &a.gthr, &a.list_counts);
+            gemm_aux_layout(ix->gemm_aux, &a.hist, &a.qscale, &a.gthr, &a.list_counts, &a.overflow);
             a.out_d = od + (size_t)q0 * k;
             a.out_i = oi + (size_t)q0 * k;
             a.id_base = ix->cfg.id_base;
@@ -506,6 +506,15 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
                            st));
         CU(cudaStreamSynchronize(st));
         ix->st.n_gemm_fallbacks += ix->fail_pin[ix->fail_cap];
+        if (getenv("B200R_DEBUG_FAILS") && ix->fail_pin[ix->fail_cap]) {
+            int cause[4] = {0, 0, 0, 0};
+            for (int64_t i = 0; i < nq; i++) cause[ix->fail_pin[i] & 3]++;
+            fprintf(stderr, "[b200r] gemm fallbacks: check=%d bucket=%d slice=%d; first failing queries:", cause[1], cause[2], cause[3]);
+            int shown = 0;
+            for (int64_t i = 0; i < nq && shown < 40; i++)
+                if (ix->fail_pin[i]) { fprintf(stderr, " %lld", (long long)i); shown++; }
+            fprintf(stderr, "\n");
+        }
     }
 
     ScanParams p{};

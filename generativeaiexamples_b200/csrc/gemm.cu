@@ -149,6 +149,7 @@ struct GemmParams {
     const float* qscale;  // [128*MT][2] bucket map per query: goodness lo, buckets per unit
     int warmup;           // 1: first tile of each CTA only feeds the histogram and is replayed at the end
     int* list_counts;     // [grid][128*MT] valid entries in each survivor list
+    int* overflow;        // [128*MT] set when some CTA's slice for the query overflowed
     int debug_no_select;  // timing experiments only: 1 = skip the selection, 2 = also skip the TMEM loads
     int evict_first;
 };
@@ -163,53 +164,6 @@ __device__ __forceinline__ float dec_ordered(int o) { return __int_as_float(o >=
 template <bool SMALL>
 __device__ __forceinline__ float better_of(float a, float b) {
     return SMALL ? fminf(a, b) : fmaxf(a, b);
-}
-
-// Per-thread survivor list in local memory, kept as a binary heap whose ROOT is the WORST
-// kept entry (the same structure faiss uses, faiss/utils/Heap.h).  Filling sifts up; once full
-// a better score replaces the root and sifts down: log2(K') dependent steps instead of a scan.
-// `lthr` is what a score must beat to enter (worst_val until the heap is full).
-template <int KP, bool SMALL>
-__device__ __noinline__ void list_offer(float* lv, uint32_t* li, int kp, int& count, float& lthr, float v,
-                                        uint32_t id) {
-    int i;
-    if (count < kp) {
-        i = count++;
-        while (i > 0) {
-            const int par = (i - 1) >> 1;
-            const float pv = lv[par];
-            if (!better_val<SMALL>(pv, v)) break;  // parent already at least as bad as v
-            lv[i] = pv;
-            li[i] = li[par];
-            i = par;
-        }
-        lv[i] = v;
-        li[i] = id;
-        if (count == kp) lthr = lv[0];
-        return;
-    }
-    i = 0;
-    for (;;) {
-        const int l = 2 * i + 1;
-        if (l >= kp) break;
-        const int r = l + 1;
-        float cv = lv[l];
-        int c = l;
-        if (r < kp) {
-            const float rv = lv[r];
-            if (better_val<SMALL>(cv, rv)) {  // right child is the worse one
-                cv = rv;
-                c = r;
-            }
-        }
-        if (!better_val<SMALL>(v, cv)) break;  // v is at least as bad as the worse child
-        lv[i] = cv;
-        li[i] = li[c];
-        i = c;
-    }
-    lv[i] = v;
-    li[i] = id;
-    lthr = lv[0];
 }
 
 template <bool BF16, int MT, int KP, bool L2>
@@ -360,7 +314,9 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         const float sgn = L2 ? -1.f : 1.f;
         int round = 0;
         while (*s_done < N_EPI_WARPS) {
-            const int q = (int)(((int64_t)blockIdx.x + (int64_t)round) % p.nq);  // every CTA walks all queries
+            // round r: the grid's CTAs cover queries {c + r*grid} -- together they sweep all queries
+            // every ceil(nq/grid) rounds (a few microseconds), so no query's threshold goes stale
+            const int q = (int)(((int64_t)blockIdx.x + (int64_t)round * gridDim.x) % p.nq);
             ++round;
             const uint4* h4 = reinterpret_cast<const uint4*>(p.hist + (size_t)q * kGemmBuckets) + lane * 4;
             unsigned c[16];
@@ -422,13 +378,19 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         const int quad = warp & 3;  // TMEM lane quadrant this warp may read
         const int qidx = mt * kGemmTileM + quad * 32 + lane;
         const bool active = qidx < p.nq;
-        // KP == 32: sorted list held entirely in registers (no memory traffic on insert: the
-        // L1 left over beside ~200 KB of pipeline smem is too small for local-memory lists).
-        // KP > 32: binary heap in local memory (list_offer).
-        float lv[KP];
-        uint32_t li[KP];
+        // KP == 32 (k <= 10): sorted list held entirely in registers -- no memory traffic on insert
+        // (the L1 left over beside ~200 KB of pipeline smem is too small for local-memory lists).
+        // KP > 32: the launch runs in warm-up mode, so a tight grid-wide threshold exists before
+        // the first row is kept and only ~K'/grid survivors reach each thread: they are simply
+        // APPENDED to the thread's slice of the global candidate buffer (one fire-and-forget
+        // store, nothing to read back).  A slice that overflows (adversarial row order) flags
+        // its query for the scan path.
+        constexpr int NREG = KP == 32 ? 32 : 1;
+        float lv[NREG];
+        uint32_t li[NREG];
         const int kp = p.kprime;
         int count = 0;
+        Cand* my_list = p.cand + ((size_t)blockIdx.x * (kGemmTileM * MT) + (qidx < kGemmTileM * MT ? qidx : 0)) * KP;
         if (KP == 32) {
 #pragma unroll
             for (int j = 0; j < KP; j++) {
@@ -473,7 +435,13 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             for (int c = 0; c < kGemmTileN / 32; c++) {
                 uint32_t r[32];
                 if (p.debug_no_select == 2) continue;
+                int g_enc = 0;
+                if (active) g_enc = *reinterpret_cast<volatile int*>(gthr);  // in flight during the TMEM load
                 tmem_ld32(taddr + c * 32, r);
+                if (active) {
+                    g = better_of<L2>(g, dec_ordered(g_enc));
+                    thr = better_of<L2>(lthr, g);
+                }
                 if (active && p.debug_no_select == 0) {
                     float v[32];
                     float best;
@@ -523,7 +491,26 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                                     lthr = lv[31];
                                     count = 32;  // sentinel slots make the list "full" from the start
                                 } else {
-                                    list_offer<KP, L2>(lv, li, kp, count, lthr, v[j], (uint32_t)(rbase + j));
+                                    if (count == KP) {
+                                        // slice full: entries admitted under an older, weaker threshold that
+                                        // the current one rules out can go (it is a lower bound of the final
+                                        // K'-th best, so they cannot be among the K' best)
+                                        g = better_of<L2>(g, dec_ordered(*reinterpret_cast<volatile int*>(gthr)));
+                                        int w = 0;
+                                        for (int e = 0; e < KP; e++) {
+                                            const Cand c2 = my_list[e];
+                                            if (better_val<L2>(c2.v, g)) my_list[w++] = c2;
+                                        }
+                                        count = w;
+                                    }
+                                    if (count < KP && better_val<L2>(v[j], g)) {
+                                        Cand cnd;
+                                        cnd.v = v[j];
+                                        cnd.id = (uint32_t)(rbase + j);
+                                        my_list[count++] = cnd;
+                                    } else if (count >= KP) {
+                                        count = KP + 1;  // still full after compaction: overflow
+                                    }
                                 }
                                 thr = better_of<L2>(lthr, g);
                                 improved = true;
@@ -548,7 +535,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                 }
             }
             // publish: only a FULL list's worst is a valid bound
-            if (active && improved && count >= kp && lthr != worst_val<L2>() && better_val<L2>(lthr, g)) {
+            if (KP == 32 && active && improved && count >= kp && lthr != worst_val<L2>() && better_val<L2>(lthr, g)) {
                 if (L2)
                     atomicMin(gthr, enc_ordered(lthr));
                 else
@@ -574,13 +561,8 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                 }
                 p.list_counts[(size_t)blockIdx.x * (kGemmTileM * MT) + qidx] = nv;
             } else {
-                p.list_counts[(size_t)blockIdx.x * (kGemmTileM * MT) + qidx] = count;
-                for (int j = 0; j < count; j++) {
-                    Cand cnd;
-                    cnd.v = lv[j];
-                    cnd.id = li[j];
-                    dst[j] = cnd;
-                }
+                p.list_counts[(size_t)blockIdx.x * (kGemmTileM * MT) + qidx] = count < KP ? count : KP;
+                if (count > KP) p.overflow[qidx] = 1;
             }
         }
     }
@@ -605,6 +587,7 @@ struct RescoreParams {
     const float* q;        // [nq][d_pad] fp32 (prepared)
     const Cand* cand;      // [grid][q_stride][KP] approx survivors
     const int* list_counts; // [grid][q_stride]
+    const int* overflow;    // [q_stride]
     const float* qscale;    // [q_stride][2] the filter's bucket map
     int grid, q_stride, kp_stride, kprime, k;
     const unsigned* max_norm_bits;  // max_i ||x_i||^2 as float bits
@@ -756,10 +739,10 @@ __global__ void __launch_bounds__(kRescoreWarps * 32) rescore_kernel(const Resco
     }
     __syncthreads();
     const int n_sel = s_nsel;
-    if (n_sel > kRescoreCap) {
+    if (n_sel > kRescoreCap || p.overflow[qi]) {
         // one bucket holds thousands of candidates (massive ties): let the scan path answer
         if (threadIdx.x == 0) {
-            p.fail_flags[qi] = 1;
+            p.fail_flags[qi] = p.overflow[qi] ? 3 : 2;  // cause codes: 1 check, 2 boundary bucket too full, 3 slice overflow
             atomicAdd(p.fail_count, 1);
         }
         return;
@@ -883,7 +866,7 @@ __global__ void __launch_bounds__(kRescoreWarps * 32) rescore_kernel(const Resco
 //   IP : goodness = score      in [-B, B],               B = ||q|| * max||x||
 //   L2 : goodness = -(||x||^2 - 2 q.x) in [-(maxn + 2B), 2B]
 __global__ void gemm_prepare_kernel(const float* __restrict__ q, int d_pad, int nq, const unsigned* max_norm_bits,
-                                    int l2, unsigned* hist, float* qscale, int* gthr) {
+                                    int l2, unsigned* hist, float* qscale, int* gthr, int* overflow) {
     const int qi = blockIdx.x;
     const int lane = threadIdx.x;
     float s = 0.f;
@@ -902,6 +885,7 @@ __global__ void gemm_prepare_kernel(const float* __restrict__ q, int d_pad, int 
         qscale[2 * qi] = lo;
         qscale[2 * qi + 1] = (hi > lo) ? (float)kGemmBuckets / (hi - lo) : 0.f;
         gthr[qi] = l2 ? 0x7F7FFFFF : (int)(0xFF7FFFFFu ^ 0x7FFFFFFFu);  // enc(+FLT_MAX) / enc(-FLT_MAX)
+        overflow[qi] = 0;
     }
 }
 
@@ -975,14 +959,15 @@ static bool make_map(CUtensorMap* map, const void* base, int64_t rows, int d_pad
 size_t gemm_cand_bytes(int grid, int nq_pad, int kp_cap) { return (size_t)grid * nq_pad * kp_cap * sizeof(Cand); }
 size_t gemm_aux_bytes() {
     return (size_t)kGemmMaxBlock * (kGemmBuckets * sizeof(unsigned) + 2 * sizeof(float) + sizeof(int)) +
-           (size_t)kGemmMaxGrid * kGemmMaxBlock * sizeof(int) + 1024;
+           (size_t)kGemmMaxGrid * kGemmMaxBlock * sizeof(int) + (size_t)kGemmMaxBlock * sizeof(int) + 1024;
 }
-void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr, int** list_counts) {
+void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr, int** list_counts, int** overflow) {
     uint8_t* b = reinterpret_cast<uint8_t*>(aux);
     *hist = reinterpret_cast<unsigned*>(b);
     *qscale = reinterpret_cast<float*>(b + (size_t)kGemmMaxBlock * kGemmBuckets * sizeof(unsigned));
     *gthr = reinterpret_cast<int*>(b + (size_t)kGemmMaxBlock * (kGemmBuckets * sizeof(unsigned) + 2 * sizeof(float)));
-    *list_counts = *gthr + kGemmMaxBlock;
+    *overflow = *gthr + kGemmMaxBlock;
+    *list_counts = *overflow + kGemmMaxBlock;
 }
 
 // survivors kept per query: the slack beyond k must cover the rows whose approx score lies
@@ -1061,9 +1046,10 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     }
     p.hist = a.hist;
     p.list_counts = a.list_counts;
+    p.overflow = a.overflow;
     p.qscale = a.qscale;
     gemm_prepare_kernel<<<MT * kGemmTileM, 32, 0, st>>>(a.q_f32, a.d_pad, a.nq, a.max_norm_bits, a.l2 ? 1 : 0, a.hist,
-                                                        a.qscale, a.gthr);
+                                                        a.qscale, a.gthr, a.overflow);
     p.evict_first = ((size_t)a.n_rows * a.d_pad * (a.bf16 ? 2 : 4) > ((size_t)96 << 20)) ? 1 : 0;
     int grid = (int)(p.n_tiles < a.num_sms ? p.n_tiles : a.num_sms);
     if (grid < 1) grid = 1;
@@ -1071,8 +1057,8 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
         // warm-up pays one extra tile per CTA; worth it when the lists are large (memory heaps)
         // and every CTA has several tiles
         const char* wv = getenv("B200R_GEMM_WARMUP");
-        p.warmup = (kp_cap > 32 && p.n_tiles >= 4 * (int64_t)grid) ? 1 : 0;
-        if (wv) p.warmup = atoi(wv) && p.n_tiles >= (int64_t)grid;
+        p.warmup = kp_cap > 32 ? 1 : 0;  // the append-only lists of the large-K' variant rely on it
+        if (wv && kp_cap == 32) p.warmup = atoi(wv);
     }
     cudaError_t e;
     if (a.bf16) {
@@ -1100,6 +1086,7 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     rp.q = a.q_f32;
     rp.cand = a.cand;
     rp.list_counts = a.list_counts;
+    rp.overflow = a.overflow;
     rp.qscale = a.qscale;
     rp.grid = grid;
     rp.q_stride = MT * kGemmTileM;

@@ -70,6 +70,7 @@ struct GemmSearchArgs {
     unsigned* hist;       // [256][512] scratch: score histograms
     float* qscale;        // [256][2] scratch: bucket maps
     int* list_counts;     // [grid][256] scratch: survivors per (CTA, query)
+    int* overflow;        // [256] scratch: survivor slice overflowed
     const unsigned* max_norm_bits;
     float* out_d;
     int64_t* out_i;
@@ -83,7 +84,7 @@ cudaError_t launch_max_norm(const float* norms, int64_t n, unsigned* out_bits, c
 cudaError_t launch_f32_to_bf16(const float* src, void* dst, int64_t n, cudaStream_t st);
 size_t gemm_cand_bytes(int grid, int nq_pad, int kp_cap);
 size_t gemm_aux_bytes();
-void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr, int** list_counts);
+void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr, int** list_counts, int** overflow);
 int gemm_kp_cap(int k);
 
 // lets entry points outside api.cu fill b200r_last_error()
