@@ -148,17 +148,22 @@ struct WarpTopK {
     }
 
     __device__ __forceinline__ void refresh_thr() {
+        // entry k-1 sits in slot (k-1)/32 of lane (k-1)%32.  Shuffle every slot first and choose
+        // among the results: choosing the slot first (v[e >> 5]) would be a runtime index into the
+        // register array and push the whole list into local memory.
         const int e = k - 1;
-        float tv = v[0];
-        uint32_t ti = id[0];
+        float tv = __shfl_sync(0xffffffffu, v[0], e & 31);
+        uint32_t ti = __shfl_sync(0xffffffffu, id[0], e & 31);
 #pragma unroll
-        for (int j = 1; j < KPL; j++)
-            if ((e >> 5) == j) {
-                tv = v[j];
-                ti = id[j];
-            }
-        thr = __shfl_sync(0xffffffffu, tv, e & 31);
-        thr_id = __shfl_sync(0xffffffffu, ti, e & 31);
+        for (int j = 1; j < KPL; j++) {
+            const float sv = __shfl_sync(0xffffffffu, v[j], e & 31);
+            const uint32_t si = __shfl_sync(0xffffffffu, id[j], e & 31);
+            const bool pick = (e >> 5) == j;
+            tv = pick ? sv : tv;
+            ti = pick ? si : ti;
+        }
+        thr = tv;
+        thr_id = ti;
     }
 
     // s/sid uniform across the warp.  Caller has checked that (s,sid) beats thr.
@@ -208,29 +213,136 @@ struct WarpTopK {
         }
     }
 
-    // merge `nlists` stored lists (each KPL*32 entries, `stride` entries apart)
+    // ---- bitonic machinery -------------------------------------------------------------
+    // Merge with another SORTED list of the same layout (bv/bi, best first): afterwards this
+    // list holds the KPL*32 best of the union, sorted.  max(A[e], B[KCAP-1-e]) is a bitonic
+    // sequence containing exactly those entries; log2(KCAP) half-cleaner stages sort it.
+    __device__ __forceinline__ void merge_sorted(const float (&bv)[KPL], const uint32_t (&bi)[KPL]) {
+        const int lane = threadIdx.x & 31;
+#pragma unroll
+        for (int j = 0; j < KPL; j++) {
+            const float rv = __shfl_sync(0xffffffffu, bv[KPL - 1 - j], 31 - lane);
+            const uint32_t ri = __shfl_sync(0xffffffffu, bi[KPL - 1 - j], 31 - lane);
+            if (better<SMALL>(rv, ri, v[j], id[j])) {
+                v[j] = rv;
+                id[j] = ri;
+            }
+        }
+#pragma unroll
+        for (int s = KPL / 2; s >= 1; s >>= 1) {  // partner lives s slots away, same lane
+#pragma unroll
+            for (int j = 0; j < KPL; j++)
+                if ((j & s) == 0) {
+                    if (better<SMALL>(v[j + s], id[j + s], v[j], id[j])) {
+                        const float tv = v[j];
+                        const uint32_t ti = id[j];
+                        v[j] = v[j + s];
+                        id[j] = id[j + s];
+                        v[j + s] = tv;
+                        id[j + s] = ti;
+                    }
+                }
+        }
+#pragma unroll
+        for (int s = 16; s >= 1; s >>= 1) {  // partner lives s lanes away, same slot
+            const bool low = (lane & s) == 0;
+#pragma unroll
+            for (int j = 0; j < KPL; j++) {
+                const float pv = __shfl_xor_sync(0xffffffffu, v[j], s);
+                const uint32_t pi = __shfl_xor_sync(0xffffffffu, id[j], s);
+                const bool p_better = better<SMALL>(pv, pi, v[j], id[j]);
+                if (low == p_better) {  // the lower lane keeps the better one, the upper lane the worse one
+                    v[j] = pv;
+                    id[j] = pi;
+                }
+            }
+        }
+        refresh_thr();
+    }
+
+    // sort one candidate per lane, best first (bitonic network over the 32 lanes)
+    __device__ __forceinline__ static void sort32(float& cv, uint32_t& ci) {
+        const int lane = threadIdx.x & 31;
+#pragma unroll
+        for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+            for (int s = k >> 1; s >= 1; s >>= 1) {
+                const float pv = __shfl_xor_sync(0xffffffffu, cv, s);
+                const uint32_t pi = __shfl_xor_sync(0xffffffffu, ci, s);
+                const bool low = (lane & s) == 0;
+                const bool desc = (lane & k) == 0;  // this k-block is being sorted best-first
+                const bool p_better = better<SMALL>(pv, pi, cv, ci);
+                if ((low == desc) == p_better) {
+                    cv = pv;
+                    ci = pi;
+                }
+            }
+        }
+    }
+
+    // each lane brings at most one candidate (kEmptyId = none): a few are inserted one by one,
+    // a crowd is sorted and merged in one go
+    __device__ __forceinline__ void offer_batch(float cv, uint32_t cid) {
+        const bool pass = cid != kEmptyId && better<SMALL>(cv, cid, thr, thr_id);
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        if (m == 0) return;
+        if (__popc(m) <= 4) {
+            offer_lanes(cv, cid);
+            return;
+        }
+        if (!pass) {
+            cv = worst_val<SMALL>();
+            cid = kEmptyId;
+        }
+        sort32(cv, cid);
+        float bv[KPL];
+        uint32_t bi[KPL];
+#pragma unroll
+        for (int j = 0; j < KPL; j++) {
+            bv[j] = j == 0 ? cv : worst_val<SMALL>();
+            bi[j] = j == 0 ? cid : kEmptyId;
+        }
+        merge_sorted(bv, bi);
+    }
+
+    // merge `nlists` stored SORTED lists (each KPL*32 entries, `stride` entries apart); the next
+    // list is fetched while the current one is being merged
     template <bool GLOBAL>
     __device__ __forceinline__ void merge_from(const Cand* lists, int first, int nlists, int step, size_t stride) {
         const int lane = threadIdx.x & 31;
-        for (int l = first; l < nlists; l += step) {
+        float bv[KPL];
+        uint32_t bi[KPL];
+        auto fetch = [&](int l) {
             const Cand* src = lists + (size_t)l * stride;
 #pragma unroll
             for (int j = 0; j < KPL; j++) {
-                Cand c;
                 if (GLOBAL) {
                     // written by other CTAs of this launch: read through L2
                     const unsigned long long raw =
                         __ldcg(reinterpret_cast<const unsigned long long*>(src + j * 32 + lane));
-                    c.v = __uint_as_float((uint32_t)(raw & 0xffffffffull));
-                    c.id = (uint32_t)(raw >> 32);
+                    bv[j] = __uint_as_float((uint32_t)(raw & 0xffffffffull));
+                    bi[j] = (uint32_t)(raw >> 32);
                 } else {
-                    c = src[j * 32 + lane];
+                    const Cand c = src[j * 32 + lane];
+                    bv[j] = c.v;
+                    bi[j] = c.id;
                 }
-                // lists are sorted: once a whole slot fails, the rest of the list fails too
-                const bool any = __any_sync(0xffffffffu, c.id != kEmptyId && better<SMALL>(c.v, c.id, thr, thr_id));
-                if (!any) break;
-                offer_lanes(c.v, c.id);
             }
+        };
+        if (first < nlists) fetch(first);
+        for (int l = first; l < nlists; l += step) {
+            float cv[KPL];
+            uint32_t ci[KPL];
+#pragma unroll
+            for (int j = 0; j < KPL; j++) {
+                cv[j] = bv[j];
+                ci[j] = bi[j];
+            }
+            if (l + step < nlists) fetch(l + step);
+            // a list whose best entry cannot enter changes nothing
+            const float head_v = __shfl_sync(0xffffffffu, cv[0], 0);
+            const uint32_t head_i = __shfl_sync(0xffffffffu, ci[0], 0);
+            if (head_i != kEmptyId && better<SMALL>(head_v, head_i, thr, thr_id)) merge_sorted(cv, ci);
         }
     }
 

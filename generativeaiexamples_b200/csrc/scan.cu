@@ -63,8 +63,18 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
     const int R = p.rows_per_tile;
 
     WarpTopK<KPL, L2> top[NQ];
+    // rows that beat the running threshold wait here (lane i holds the i-th of them) until 32 have
+    // gathered, then enter the list in one sort + bitonic merge instead of 32 serial inserts
+    float pend_v[NQ];
+    uint32_t pend_i[NQ];
+    int npend[NQ];
 #pragma unroll
-    for (int qi = 0; qi < NQ; qi++) top[qi].init(p.k);
+    for (int qi = 0; qi < NQ; qi++) {
+        top[qi].init(p.k);
+        pend_v[qi] = worst_val<L2>();
+        pend_i[qi] = kEmptyId;
+        npend[qi] = 0;
+    }
 
     if (warp == 0) {
         // ---- producer ---------------------------------------------------
@@ -178,7 +188,18 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
 #pragma unroll
                 for (int qi = 0; qi < NQ; qi++) {
                     const float sc = warp_sum((acc[qi][0] + acc[qi][2]) + (acc[qi][1] + acc[qi][3]));
-                    top[qi].offer_stream(sc, row);
+                    if (better_val<L2>(sc, top[qi].thr)) {  // row ids only grow: a tie never displaces
+                        if (lane == npend[qi]) {
+                            pend_v[qi] = sc;
+                            pend_i[qi] = row;
+                        }
+                        if (++npend[qi] == 32) {
+                            top[qi].offer_batch(pend_v[qi], pend_i[qi]);
+                            pend_v[qi] = worst_val<L2>();
+                            pend_i[qi] = kEmptyId;
+                            npend[qi] = 0;
+                        }
+                    }
                 }
             }
             __syncwarp();
@@ -192,6 +213,10 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
     }
 
     // ---- epilogue: per-CTA merge, then last-CTA grid merge ----------------
+    if (warp > 0) {
+#pragma unroll
+        for (int qi = 0; qi < NQ; qi++) top[qi].offer_batch(pend_v[qi], pend_i[qi]);  // stragglers
+    }
     __syncthreads();  // every stage consumed; the ring is free for reuse
     Cand* sm_lists = reinterpret_cast<Cand*>(smem);  // [NQ][NCW][KCAP]
     if (warp > 0) {
