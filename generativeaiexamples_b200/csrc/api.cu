@@ -422,7 +422,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     if ((q_mem_kind != B200R_HOST && q_mem_kind != B200R_DEVICE) ||
         (out_mem_kind != B200R_HOST && out_mem_kind != B200R_DEVICE))
         return fail(B200R_E_INVALID, "b200r_search: bad mem_kind");
-    if (k > kScanMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_search: k = %d exceeds the supported maximum %d", k, kScanMaxK);
+    if (k > kMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_search: k = %d exceeds the supported maximum %d", k, kMaxK);
 
     std::lock_guard<std::mutex> lk(ix->mu);
     DeviceGuard g(ix->device);
@@ -528,9 +528,11 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     p.scratch = ix->scratch;
     p.counter = ix->counter;
     p.id_base = ix->cfg.id_base;
-    for (int64_t q0 = 0; q0 < nq; q0 += (use_gemm ? 1 : kScanMaxNQ)) {
+    // one query per launch after a GEMM pass (only the flagged ones) and for k > 128 (wide lists)
+    const int scan_step = (use_gemm || k > kScanMaxK) ? 1 : kScanMaxNQ;
+    for (int64_t q0 = 0; q0 < nq; q0 += scan_step) {
         if (use_gemm && !ix->fail_pin[q0]) continue;  // only the queries whose check failed
-        const int nqg = use_gemm ? 1 : (int)std::min<int64_t>(kScanMaxNQ, nq - q0);
+        const int nqg = (int)std::min<int64_t>(scan_step, nq - q0);
         p.q = q_ready + (size_t)q0 * ix->d_pad;
         p.out_d = od + (size_t)q0 * k;
         p.out_i = oi + (size_t)q0 * k;
@@ -682,7 +684,7 @@ extern "C" int b200r_merge_topk(int32_t metric, const float* cand_D, const int64
         return fail(B200R_E_INVALID, "b200r_merge_topk: bad metric");
     if (nq < 0 || n_lists < 1 || k_in < 1 || k_out < 1 || stride_D < 0 || stride_I < 0)
         return fail(B200R_E_INVALID, "b200r_merge_topk: bad shape");
-    if (k_out > kScanMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_merge_topk: k_out %d > %d", k_out, kScanMaxK);
+    if (k_out > kMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_merge_topk: k_out %d > %d", k_out, kMaxK);
     if (nq == 0) return B200R_OK;
     if (!cand_D || !cand_I || !D || !I) return fail(B200R_E_INVALID, "b200r_merge_topk: null buffer");
     DeviceGuard g(device);

@@ -628,8 +628,8 @@ __device__ __forceinline__ int next_pow2(int v, int lo) {
     return p2;
 }
 
-constexpr int kRescoreCap = 2048;    // selected candidates (K' + one boundary bucket) that fit the sort buffer
-constexpr int kRescoreMaxKp = 256;
+constexpr int kRescoreCap = 4096;    // selected candidates (K' + one boundary bucket) that fit the sort buffer
+constexpr int kRescoreMaxKp = 2048;  // >= the largest K' (k = 1024 -> 1536)
 
 template <bool L2, bool BF16>
 __global__ void __launch_bounds__(kRescoreWarps * 32) rescore_kernel(const RescoreParams p) {
@@ -975,8 +975,9 @@ void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr, int
 int gemm_kp_cap(int k) { return (k + kGemmSlack <= 32) ? 32 : 256; }
 int gemm_kprime(int k) {
     if (k + kGemmSlack <= 32) return 32;  // the register list below always holds 32
-    const int kp = 2 * k + 24;
-    return kp < 256 ? kp : 256;
+    const int kp = 2 * k + 24;        // selection size K' (the per-thread slices stay at 256 entries:
+    const int cap = k + 512;          // with warm-up thresholds only ~K'/grid survivors reach a thread)
+    return kp < cap ? kp : cap;
 }
 
 template <bool BF16, int MT, int KP, bool L2>
@@ -1020,7 +1021,7 @@ static cudaError_t launch_rescore_bf(bool bf16, const RescoreParams& rp, int nq,
 //   q_f32:   [nq_pad][d_pad] prepared fp32 queries (nq_pad = 128 or 256 rows, unused rows zero)
 //   q_mma:   the same matrix in the MMA input type (== q_f32 for an fp32 corpus, bf16 copy otherwise)
 cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
-    if (a.nq < 1 || a.nq > 2 * kGemmTileM || a.k < 1 || a.k > kScanMaxK) return cudaErrorInvalidValue;
+    if (a.nq < 1 || a.nq > 2 * kGemmTileM || a.k < 1 || a.k > kMaxK) return cudaErrorInvalidValue;
     const int MT = a.nq <= kGemmTileM ? 1 : 2;
     const int kp_cap = gemm_kp_cap(a.k);
     const int kprime = gemm_kprime(a.k);

@@ -8,7 +8,9 @@ namespace b200r {
 struct Cand;
 
 constexpr int kScanMaxNQ = 4;    // queries per scan launch
-constexpr int kScanMaxK = 128;   // k served by the register-list scan path
+constexpr int kScanMaxK = 128;   // k served by the 4-query scan variants (and by b200r_search_noalloc)
+constexpr int kScanMaxKWide = 1024;  // k served by the single-query scan variants (lists of 8..32 slots per lane)
+constexpr int kMaxK = kScanMaxKWide; // largest k b200r_search accepts
 
 struct ScanParams {
     const void* corpus;   // [n_rows][d] fp32 or bf16, row-major, rows 16-byte multiples

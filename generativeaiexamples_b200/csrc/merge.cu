@@ -57,17 +57,30 @@ cudaError_t launch_merge(bool l2, const float* cand_d, const int64_t* cand_i, in
                          int64_t stride_d, int64_t stride_i, int k_out, float* out_d, int64_t* out_i,
                          cudaStream_t st) {
     if (nq <= 0) return cudaSuccess;
-    if (k_out < 1 || k_out > kScanMaxK || n_lists < 1 || k_in < 1) return cudaErrorInvalidValue;
+    if (k_out < 1 || k_out > kMaxK || n_lists < 1 || k_in < 1) return cudaErrorInvalidValue;
     if ((int64_t)n_lists * k_in >= 0xFFFFFFFFll) return cudaErrorInvalidValue;
     const int wpb = 4;
     const int g = (int)((nq + wpb - 1) / wpb);
-    if (k_out <= 32) {
-        if (l2) merge_topk_kernel<1, true><<<g, wpb * 32, 0, st>>>(cand_d, cand_i, nq, n_lists, k_in, stride_d, stride_i, k_out, out_d, out_i);
-        else merge_topk_kernel<1, false><<<g, wpb * 32, 0, st>>>(cand_d, cand_i, nq, n_lists, k_in, stride_d, stride_i, k_out, out_d, out_i);
-    } else {
-        if (l2) merge_topk_kernel<4, true><<<g, wpb * 32, 0, st>>>(cand_d, cand_i, nq, n_lists, k_in, stride_d, stride_i, k_out, out_d, out_i);
-        else merge_topk_kernel<4, false><<<g, wpb * 32, 0, st>>>(cand_d, cand_i, nq, n_lists, k_in, stride_d, stride_i, k_out, out_d, out_i);
-    }
+#define B200R_MERGE(KPLV)                                                                                        \
+    do {                                                                                                         \
+        if (l2)                                                                                                  \
+            merge_topk_kernel<KPLV, true><<<g, wpb * 32, 0, st>>>(cand_d, cand_i, nq, n_lists, k_in, stride_d,    \
+                                                                  stride_i, k_out, out_d, out_i);                \
+        else                                                                                                     \
+            merge_topk_kernel<KPLV, false><<<g, wpb * 32, 0, st>>>(cand_d, cand_i, nq, n_lists, k_in, stride_d,   \
+                                                                   stride_i, k_out, out_d, out_i);               \
+    } while (0)
+    if (k_out <= 32)
+        B200R_MERGE(1);
+    else if (k_out <= 128)
+        B200R_MERGE(4);
+    else if (k_out <= 256)
+        B200R_MERGE(8);
+    else if (k_out <= 512)
+        B200R_MERGE(16);
+    else
+        B200R_MERGE(32);
+#undef B200R_MERGE
     return cudaGetLastError();
 }
 

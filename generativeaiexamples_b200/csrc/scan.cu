@@ -284,18 +284,23 @@ static cudaError_t launch_mk(const ScanParams& p, bool l2, bool bf16, int grid, 
                 : launch_one<NQ, KPL, false, false>(p, grid, smem, st);
 }
 
-size_t scan_scratch_bytes(int max_grid) { return (size_t)max_grid * kScanMaxNQ * kScanMaxK * sizeof(Cand); }
+size_t scan_scratch_bytes(int max_grid) {
+    const size_t per_cta = kScanMaxNQ * kScanMaxK > kScanMaxKWide ? kScanMaxNQ * kScanMaxK : kScanMaxKWide;
+    return (size_t)max_grid * per_cta * sizeof(Cand);
+}
 
 // Fills in the tiling fields of `p` and launches.  p.q must hold nq_slots(nq) rows.
 cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st,
                         int* grid_out) {
     const int NQ = nq <= 1 ? 1 : 4;
-    const int KPL = p.k <= 32 ? 1 : 4;
-    if (nq < 1 || nq > kScanMaxNQ || p.k < 1 || p.k > kScanMaxK) return cudaErrorInvalidValue;
+    // list slots per lane: 32*KPL >= k.  Above 128 only the single-query variants exist.
+    const int KPL = p.k <= 32 ? 1 : p.k <= 128 ? 4 : p.k <= 256 ? 8 : p.k <= 512 ? 16 : 32;
+    if (nq < 1 || nq > kScanMaxNQ || p.k < 1 || p.k > kScanMaxKWide) return cudaErrorInvalidValue;
+    if (p.k > kScanMaxK && nq != 1) return cudaErrorInvalidValue;
     smem_limit -= 1024;  // static shared + slack
     const size_t q_bytes = (size_t)NQ * p.d * sizeof(float);
     const size_t bar_bytes = 2 * 16 * sizeof(uint64_t);
-    const size_t merge_bytes = (size_t)NQ * (kScanThreads / 32) * KPL * 32 * sizeof(Cand);
+    const size_t merge_bytes = (size_t)NQ * (kScanThreads / 32) * KPL * 32 * sizeof(Cand);  // <= 139 KB (NQ=1, KPL=32)
     // stage: as many whole rows as fit in 32 KB (at least one)
     int stage_bytes = 32 * 1024;
     if (p.row_bytes > stage_bytes) stage_bytes = (p.row_bytes + 127) / 128 * 128;
@@ -314,6 +319,9 @@ cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, s
     if (grid < 1) grid = 1;
     if (grid_out) *grid_out = grid;
     const size_t smem = (size_t)nst * stage_bytes + q_bytes + bar_bytes;
+    if (KPL == 8) return launch_mk<1, 8>(p, l2, bf16, grid, smem, st);
+    if (KPL == 16) return launch_mk<1, 16>(p, l2, bf16, grid, smem, st);
+    if (KPL == 32) return launch_mk<1, 32>(p, l2, bf16, grid, smem, st);
     if (NQ == 1) return KPL == 1 ? launch_mk<1, 1>(p, l2, bf16, grid, smem, st) : launch_mk<1, 4>(p, l2, bf16, grid, smem, st);
     return KPL == 1 ? launch_mk<4, 1>(p, l2, bf16, grid, smem, st) : launch_mk<4, 4>(p, l2, bf16, grid, smem, st);
 }

@@ -333,7 +333,7 @@ def test_merge_kernel(built_lib):
     from tests.test_sharded_gloo import _merge_ref
 
     rng = np.random.default_rng(77)
-    for metric, G, nq, k in ((0, 8, 1, 10), (1, 4, 5, 33), (0, 2, 256, 10), (1, 8, 3, 128)):
+    for metric, G, nq, k in ((0, 8, 1, 10), (1, 4, 5, 33), (0, 2, 256, 10), (1, 8, 3, 128), (0, 3, 2, 300), (1, 2, 1, 1024)):
         cd = rng.standard_normal((G, nq, k)).astype(np.float32)
         cd = np.sort(cd, axis=2) if metric == 1 else -np.sort(-cd, axis=2)
         cd[:, :, 1] = cd[:, :, 0]  # force ties
@@ -438,3 +438,33 @@ def test_gemm_bf16_storage(built_lib):
     xb = torch.from_numpy(x).to(torch.bfloat16).to(torch.float32).numpy()
     _check("ip", D, I, q, xb, k, "gemm bf16 vs rounded corpus")
     ix.close()
+
+
+@pytest.mark.parametrize("metric", ["ip", "l2"])
+def test_large_k(built_lib, metric):
+    """128 < k <= 1024: single-query wide-list scan variants and the GEMM path with a larger K'
+    ("typically 1000 for real world", RAG/notebooks/langchain/langchain_basic_RAG.ipynb:445)."""
+    from generativeaiexamples_b200 import _lib
+
+    rng = np.random.default_rng(77)
+    n, d = 30000, 256
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    q = rng.standard_normal((40, d), dtype=np.float32)
+    q[::2] = x[rng.integers(0, n, 20)] + 0.1 * q[::2]
+    ix = _mk(metric, d)
+    ix.add(x)
+    for nq, k, path in ((1, 129, _lib.PATH_SCAN), (1, 1000, _lib.PATH_SCAN), (3, 300, _lib.PATH_SCAN),
+                        (8, 500, _lib.PATH_GEMM), (40, 1024, _lib.PATH_GEMM)):
+        D, I = ix.search(q[:nq], k)
+        assert ix.stats()["last_path"] == path
+        _check(metric, D, I, q[:nq], x, k, f"large k {metric} nq={nq} k={k}")
+    with pytest.raises(RuntimeError):
+        ix.search(q[:1], 1025)
+    # k larger than the corpus: padding
+    small = _mk(metric, d)
+    small.add(x[:300])
+    D, I = small.search(q[:2], 700)
+    assert (I[:, 300:] == -1).all() and sorted(I[0, :300].tolist()) == list(range(300))
+    _check(metric, D[:, :300], I[:, :300], q[:2], x[:300], 300, "large k > ntotal")
+    ix.close()
+    small.close()
