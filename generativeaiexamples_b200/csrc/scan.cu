@@ -9,9 +9,9 @@
 //
 // Design (HBM-bound; roofline = N * d * sizeof(elem) bytes per launch):
 //  * persistent grid, one CTA per SM; tile t -> CTA (t mod grid), a tile is
-//    `rows_per_tile` consecutive rows = one contiguous <= 32 KB block;
+//    `rows_per_tile` consecutive rows = one contiguous <= 64 KB block;
 //  * warp 0 is the producer: one lane issues cp.async.bulk (TMA engine, SASS UBLKCP)
-//    into an NSTAGES-deep shared-memory ring, completion on mbarriers;
+//    into a 3-deep shared-memory ring (192 KB in flight per SM), completion on mbarriers;
 //  * 16 consumer warps: a warp owns whole rows, reads them with 128-bit LDS, keeps
 //    fp32 partial sums, butterfly-reduces, and offers the score to its register
 //    top-k list (WarpTopK).  Direct (q-x)^2 for L2, as faiss's nq<20 path does;
@@ -20,6 +20,8 @@
 //    vector is never written to HBM.
 #include "common.cuh"
 #include "kernels.h"
+
+#include <cstdlib>
 
 namespace b200r {
 
@@ -302,13 +304,19 @@ cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, s
     const size_t bar_bytes = 2 * 16 * sizeof(uint64_t);
     const size_t merge_bytes = (size_t)NQ * (kScanThreads / 32) * KPL * 32 * sizeof(Cand);  // <= 139 KB (NQ=1, KPL=32)
     // stage: as many whole rows as fit in 32 KB (at least one)
-    int stage_bytes = 32 * 1024;
+    // 64 KB stages: 16 rows at d = 1024 fp32, i.e. one row per consumer warp per stage, and fewer,
+    // larger bulk copies.  Measured on B200 (tools/tune_scan.py, 10M rows): 64 KB x 3 = 5.66 ms,
+    // 48 KB x 4 = 5.69, 32 KB x 6 = 5.74, 16 KB x 12 = 6.39, 8 KB x 16 = 8.00.
+    int stage_bytes = 64 * 1024;
+    int max_stages = 3;
+    if (const char* ev = getenv("B200R_SCAN_STAGE_KB")) stage_bytes = atoi(ev) * 1024;  // tuning knobs
+    if (const char* ev = getenv("B200R_SCAN_STAGES")) max_stages = atoi(ev);
     if (p.row_bytes > stage_bytes) stage_bytes = (p.row_bytes + 127) / 128 * 128;
     int R = stage_bytes / p.row_bytes;
     if (smem_limit < q_bytes + bar_bytes + 2 * (size_t)stage_bytes) return cudaErrorInvalidValue;
     int nst = (int)((smem_limit - q_bytes - bar_bytes) / stage_bytes);
     if (nst > 16) nst = 16;
-    if (nst > 6) nst = 6;
+    if (nst > max_stages) nst = max_stages;
     if ((size_t)nst * stage_bytes < merge_bytes) return cudaErrorInvalidValue;
     p.nstages = nst;
     p.stage_bytes = stage_bytes;
