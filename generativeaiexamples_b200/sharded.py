@@ -69,6 +69,7 @@ class ShardedFlatIndex:
         self._merge_fn = merge_fn
         self._on_gpu = merge_fn is None
         self._counts = [0] * self.world  # rows per rank
+        self._ws = {}  # host-caller staging buffers, per (nq, k)
         self.id_base = 0
 
     # -- bookkeeping ----------------------------------------------------------
@@ -107,6 +108,23 @@ class ShardedFlatIndex:
         lo, hi = shard_bounds(len(x), self.world, self.rank)
         self.add_local(x[lo:hi])
 
+    def _host_ws(self, nq, k, dev, block):
+        key = (nq, k)
+        ws = self._ws.get(key)
+        if ws is None:
+            if len(self._ws) > 64:
+                self._ws.clear()
+            ws = {
+                "q_pin": torch.empty((nq, self.d), dtype=torch.float32, pin_memory=True),
+                "q_dev": torch.empty((nq, self.d), dtype=torch.float32, device=dev),
+                "mine": torch.empty(block, dtype=torch.uint8, device=dev),
+                "out": torch.empty(block, dtype=torch.uint8, device=dev),
+                "allb": torch.empty(self.world * block, dtype=torch.uint8, device=dev),
+                "out_pin": torch.empty(block, dtype=torch.uint8, pin_memory=True),
+            }
+            self._ws[key] = ws
+        return ws
+
     # -- search ---------------------------------------------------------------
     def search(self, q, k: int):
         """All ranks pass the same queries; all ranks get the same (D, I)."""
@@ -116,23 +134,38 @@ class ShardedFlatIndex:
         as_numpy = not (isinstance(q, torch.Tensor) and q.is_cuda)
         if self._on_gpu:
             dev = self._buf_device()
-            qd = q if not as_numpy else torch.as_tensor(np.ascontiguousarray(q, dtype=np.float32)).to(dev, non_blocking=True)
             d_bytes, block = _packed_layout(nq, k)
-            mine = torch.empty(block, dtype=torch.uint8, device=dev)
+            if as_numpy:
+                # host caller: staging buffers are cached per (nq, k); one pinned H2D for the queries,
+                # one packed [scores | ids] D2H for the results
+                ws = self._host_ws(nq, k, dev, block)
+                ws["q_pin"].numpy()[...] = np.asarray(q, dtype=np.float32)
+                qd = ws["q_dev"]
+                qd.copy_(ws["q_pin"], non_blocking=True)
+                mine, out = ws["mine"], ws["out"]
+            else:
+                qd = q
+                mine = torch.empty(block, dtype=torch.uint8, device=dev)
+                out = torch.empty(block, dtype=torch.uint8, device=dev) if self.world > 1 else mine
             Dl = mine[: nq * k * 4].view(torch.float32).view(nq, k)
             Il = mine[d_bytes:].view(torch.int64).view(nq, k)
             self.local.search(qd, k, D=Dl, I=Il)  # ids already carry id_base
             if self.world == 1:
-                D, I = Dl, Il
+                res = mine
             else:
-                allb = torch.empty(self.world * block, dtype=torch.uint8, device=dev)
+                allb = ws["allb"] if as_numpy else torch.empty(self.world * block, dtype=torch.uint8, device=dev)
                 dist.all_gather_into_tensor(allb, mine, group=self.group)
-                D = torch.empty((nq, k), dtype=torch.float32, device=dev)
-                I = torch.empty((nq, k), dtype=torch.int64, device=dev)
+                D = out[: nq * k * 4].view(torch.float32).view(nq, k)
+                I = out[d_bytes:].view(torch.int64).view(nq, k)
                 _merge_on_device(self.metric_type, allb, nq, self.world, k, k, self.device, D, I)
+                res = out
             if as_numpy:
-                return D.cpu().numpy(), I.cpu().numpy()
-            return D, I
+                ws["out_pin"].copy_(res, non_blocking=True)
+                torch.cuda.current_stream(self.device).synchronize()
+                host = ws["out_pin"].numpy()
+                return (host[: nq * k * 4].view(np.float32).reshape(nq, k).copy(),
+                        host[d_bytes:].view(np.int64).reshape(nq, k).copy())
+            return (res[: nq * k * 4].view(torch.float32).view(nq, k), res[d_bytes:].view(torch.int64).view(nq, k))
         # host-logic path for CPU tests: same packing and layout, device steps injected
         Dl, Il = self.local.search(np.ascontiguousarray(q, dtype=np.float32), k)
         d_bytes, block = _packed_layout(nq, k)
