@@ -1,0 +1,78 @@
+"""Micro-batching of concurrent single-query searches.
+
+The only batched caller in the reference,
+``FaissVectorDBResourceService.similarity_search(embeddings, k)``
+(community/event-driven-rag-cve-analysis/cyber_dev_day/faiss_vdb_service.py:147-174), fans a
+list of B query embeddings out as ``asyncio.gather`` of B ``asimilarity_search_by_vector`` calls,
+i.e. B threads each running an nq=1 ``index.search``.  On a CPU that is how faiss gets its
+parallelism; on the GPU it would serialise B full corpus scans.  ``SearchCoalescer`` sits between
+the store and the index: while one search is in flight the requests that arrive are queued, and
+the next launch serves all of them as ONE nq=B search (the tensor-core path from B >= 5).  An idle
+coalescer adds no waiting: the first request starts immediately.
+"""
+from __future__ import annotations
+
+import threading
+from typing import List, Optional, Tuple
+
+import numpy as np
+
+
+class _Request:
+    __slots__ = ("vec", "k", "done", "D", "I", "err")
+
+    def __init__(self, vec, k):
+        self.vec, self.k = vec, k
+        self.done = threading.Event()
+        self.D = self.I = self.err = None
+
+
+class SearchCoalescer:
+    def __init__(self, index, max_batch: int = 256):
+        self.index = index
+        self.max_batch = int(max_batch)
+        self._lock = threading.Lock()
+        self._pending: List[_Request] = []
+        self._busy = False
+        self.n_requests = 0
+        self.n_launches = 0
+
+    def search(self, vec: np.ndarray, k: int) -> Tuple[np.ndarray, np.ndarray]:
+        """vec: (1, d) float32.  Blocks until this request has been served; thread-safe."""
+        req = _Request(np.ascontiguousarray(vec, dtype=np.float32).reshape(1, -1), int(k))
+        with self._lock:
+            self._pending.append(req)
+            self.n_requests += 1
+            lead = not self._busy
+            if lead:
+                self._busy = True
+        if lead:
+            self._drain()
+        req.done.wait()
+        if req.err is not None:
+            raise req.err
+        return req.D, req.I
+
+    def _drain(self) -> None:
+        """Run by whichever caller found the coalescer idle: serve batches until nothing is queued."""
+        while True:
+            with self._lock:
+                if not self._pending:
+                    self._busy = False
+                    return
+                k = self._pending[0].k
+                batch = [r for r in self._pending if r.k == k][: self.max_batch]
+                taken = set(map(id, batch))
+                self._pending = [r for r in self._pending if id(r) not in taken]
+            try:
+                Q = np.concatenate([r.vec for r in batch], axis=0)
+                D, I = self.index.search(Q, k)
+                self.n_launches += 1
+                for j, r in enumerate(batch):
+                    r.D, r.I = D[j:j + 1], I[j:j + 1]
+            except BaseException as e:  # deliver the failure to every waiter of this batch
+                for r in batch:
+                    r.err = e
+            finally:
+                for r in batch:
+                    r.done.set()

@@ -199,7 +199,7 @@ class B200FlatVectorStore(_VSBase):
                  index_to_docstore_id: Optional[Dict[int, str]] = None,
                  relevance_score_fn: Optional[Callable[[float], float]] = None, normalize_L2: bool = False,
                  distance_strategy: DistanceStrategy = DistanceStrategy.EUCLIDEAN_DISTANCE, *, storage: str = "f32",
-                 device: int = 0, reserve_rows: int = 0):
+                 device: int = 0, reserve_rows: int = 0, coalesce: bool = False):
         """``index`` is a ``B200IndexFlat`` or, for lazy construction, the embedding
         dimension (int) / None (sized from the first vectors added, like ``FAISS.__from``)."""
         if not (hasattr(embedding_function, "embed_documents") and hasattr(embedding_function, "embed_query")):
@@ -212,6 +212,10 @@ class B200FlatVectorStore(_VSBase):
         self.override_relevance_score_fn = relevance_score_fn
         self._normalize_L2 = bool(normalize_L2)
         self._opts = dict(storage=storage, device=device, reserve_rows=reserve_rows)
+        # coalesce=True: concurrent single-query searches (e.g. asyncio.gather of
+        # asimilarity_search_by_vector, faiss_vdb_service.py:169-174) share one batched launch
+        self._coalesce = bool(coalesce)
+        self._coalescer = None
         if self.distance_strategy != DistanceStrategy.EUCLIDEAN_DISTANCE and self._normalize_L2:
             warnings.warn(f"Normalizing L2 is not applicable for metric type: {self.distance_strategy}")
         if index is None:
@@ -310,7 +314,15 @@ class B200FlatVectorStore(_VSBase):
                                                **kwargs: Any) -> List[Tuple[Document, float]]:
         if self.index is None:
             return []
-        scores, indices = self.index.search(_to_matrix(embedding), k if filter is None else fetch_k)
+        want = k if filter is None else fetch_k
+        if self._coalesce:
+            if self._coalescer is None or self._coalescer.index is not self.index:
+                from .batching import SearchCoalescer
+
+                self._coalescer = SearchCoalescer(self.index)
+            scores, indices = self._coalescer.search(_to_matrix(embedding), want)
+        else:
+            scores, indices = self.index.search(_to_matrix(embedding), want)
         return self._hits(scores[0], indices[0], k, filter, kwargs)
 
     def similarity_search_with_score(self, query: str, k: int = 4, filter: Optional[Dict[str, Any]] = None,

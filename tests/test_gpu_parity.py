@@ -468,3 +468,29 @@ def test_large_k(built_lib, metric):
     _check(metric, D[:, :300], I[:, :300], q[:2], x[:300], 300, "large k > ntotal")
     ix.close()
     small.close()
+
+
+def test_coalesced_concurrent_searches(built_lib):
+    """f2 on the real engine: 64 threads, one query each, served by a handful of batched launches."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from generativeaiexamples_b200.batching import SearchCoalescer
+
+    rng = np.random.default_rng(67)
+    n, d = 200000, 256
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    ix = _mk("l2", d)
+    ix.add(x)
+    co = SearchCoalescer(ix)
+    rows = rng.integers(0, n, 64)
+    calls0 = ix.stats()["n_search_calls"]
+    with ThreadPoolExecutor(64) as ex:
+        res = list(ex.map(lambda r: co.search(x[r:r + 1], 3), rows))
+    assert [int(I[0, 0]) for _, I in res] == rows.tolist()
+    launches = ix.stats()["n_search_calls"] - calls0
+    assert launches == co.n_launches and launches < 64
+    single = [ix.search(x[r:r + 1], 3) for r in rows[:8]]
+    for (D1, I1), (D2, I2) in zip(res[:8], single):
+        np.testing.assert_array_equal(I1, I2)
+        np.testing.assert_array_equal(D1, D2)
+    ix.close()

@@ -171,3 +171,78 @@ def test_empty_store_and_bad_embedding_function(caplog):
     assert vs.similarity_search_with_score_by_vector([0.0] * D) == []
     with pytest.raises(NotImplementedError):
         vs.max_marginal_relevance_search("q")
+
+
+def test_coalescer_batches_concurrent_callers():
+    """f2: B threads with one query each (faiss_vdb_service.py:169-174) end up in few launches."""
+    import threading
+    import time
+
+    from generativeaiexamples_b200.batching import SearchCoalescer
+
+    class SlowIndex:
+        def __init__(self):
+            self.ix = IndexFlatRef(D, METRIC_L2)
+            self.calls = []
+
+        def search(self, x, k):
+            self.calls.append(x.shape[0])
+            time.sleep(0.02)  # a search in flight: later arrivals must queue up behind it
+            return self.ix.search(x, k)
+
+    rng = np.random.default_rng(1)
+    x = rng.standard_normal((500, D)).astype(np.float32)
+    slow = SlowIndex()
+    slow.ix.add(x)
+    co = SearchCoalescer(slow)
+    res = [None] * 32
+
+    def work(i):
+        res[i] = co.search(x[i:i + 1], 3 if i % 8 else 5)  # two different k values in the mix
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(32)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert all(r[1][0, 0] == i for i, r in enumerate(res))
+    assert all(r[0].shape == (1, 3 if i % 8 else 5) for i, r in enumerate(res))
+    assert sum(slow.calls) == 32 and len(slow.calls) < 16 and max(slow.calls) > 4
+    assert co.n_requests == 32 and co.n_launches == len(slow.calls)
+
+
+def test_store_with_coalescing_and_async_gather():
+    ours = B200FlatVectorStore(Emb(), IndexFlatRef(D, METRIC_L2), InMemoryDocstore(), {}, coalesce=True)
+    ours.add_texts([f"t{i}" for i in range(50)])
+    e = Emb()
+
+    async def go():
+        return await asyncio.gather(*[ours.asimilarity_search_by_vector(e._v(f"t{i}"), k=2) for i in range(20)])
+
+    res = asyncio.run(go())
+    assert [r[0].page_content for r in res] == [f"t{i}" for i in range(20)]
+    assert ours._coalescer.n_requests == 20
+
+
+def test_multi_turn_rag_surface():
+    """f1: multi_turn_rag keeps two stores (documents + conversation), adds a turn at a time with
+    add_texts and fetches k=40 candidates for the reranker
+    (RAG/examples/advanced_rag/multi_turn_rag/chains.py:63-68,138,147-172)."""
+    docstore, _ = _pair()
+    conv_store, ref_conv = _pair()
+    docs = [f"doc chunk {i}" for i in range(100)]
+    docstore.add_texts(docs, metadatas=[{"source": "a.pdf"}] * 100)
+    for turn in range(6):  # one small add per turn
+        t = [f"user said {turn}", f"assistant said {turn}"]
+        conv_store.add_texts(t)
+        ref_conv.add_texts(t)
+    r = docstore.as_retriever(search_kwargs={"k": 40})
+    got = r.get_relevant_documents("doc chunk 7")
+    assert len(got) == 40 and got[0].page_content == "doc chunk 7"
+    _same(conv_store.as_retriever(search_kwargs={"k": 4}).get_relevant_documents("user said 3"),
+          ref_conv.retrieve("user said 3", "similarity", {"k": 4}))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        thr = conv_store.as_retriever(search_type="similarity_score_threshold",
+                                      search_kwargs={"score_threshold": 0.25, "k": 40})
+        assert [d.page_content for d in thr.get_relevant_documents("user said 3")] == ["user said 3"]
