@@ -494,3 +494,29 @@ def test_coalesced_concurrent_searches(built_lib):
         np.testing.assert_array_equal(I1, I2)
         np.testing.assert_array_equal(D1, D2)
     ix.close()
+
+
+def test_incremental_growth_and_interleaved_ops(built_lib):
+    """Ingest the way the chain server does -- a few hundred chunks per uploaded file, searches in
+    between, a delete now and then -- so that the HBM buffer re-allocates several times."""
+    from oracle.flat_ref import IndexFlatRef
+
+    rng = np.random.default_rng(91)
+    d = 384
+    ix, ref = _mk("l2", d), IndexFlatRef(d, 1)
+    for step in range(12):
+        m = int(rng.integers(50, 900))
+        x = rng.standard_normal((m, d), dtype=np.float32)
+        ix.add(x)
+        ref.add(x)
+        assert ix.ntotal == ref.ntotal
+        if step % 4 == 3:
+            ids = rng.integers(0, ref.ntotal, 40).astype(np.int64)
+            assert ix.remove_ids(ids) == ref.remove_ids(ids)
+        q = ref._codes[rng.integers(0, ref.ntotal, 6)] + 0.01
+        for nq in (1, 6):
+            D, I = ix.search(q[:nq], 5)
+            _check("l2", D, I, q[:nq], ref._codes, 5, f"growth step {step} nq={nq}")
+    assert ix.stats()["capacity_rows"] >= ix.ntotal > 1024  # grew past the initial allocation
+    np.testing.assert_array_equal(ix.reconstruct(ix.ntotal - 1), ref.reconstruct(ref.ntotal - 1))
+    ix.close()
