@@ -51,6 +51,7 @@ SIGNATURES = {
     "b200r_remove_ids": (_int, [_vp, _vp, _i64, ctypes.POINTER(_i64)]),
     "b200r_ntotal": (_int, [_vp, ctypes.POINTER(_i64)]),
     "b200r_reconstruct": (_int, [_vp, _i64, _vp]),
+    "b200r_reconstruct_batch": (_int, [_vp, _vp, _i64, _vp]),
     "b200r_reset": (_int, [_vp]),
     "b200r_normalize_l2": (_int, [_vp, _i64, _i32, _int, _i32, _vp]),
     "b200r_save": (_int, [_vp, ctypes.c_char_p]),

@@ -645,6 +645,36 @@ extern "C" int b200r_reconstruct(b200r_index* ix, int64_t key, float* out) {
     return B200R_OK;
 }
 
+extern "C" int b200r_reconstruct_batch(b200r_index* ix, const int64_t* keys, int64_t n, float* out) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_reconstruct_batch: null index");
+    if (n < 0 || (n > 0 && (!keys || !out))) return fail(B200R_E_INVALID, "b200r_reconstruct_batch: bad arguments");
+    if (n == 0) return B200R_OK;
+    std::lock_guard<std::mutex> lk(ix->mu);
+    for (int64_t i = 0; i < n; i++)
+        if (keys[i] < 0 || keys[i] >= ix->ntotal)
+            return fail(B200R_E_INVALID, "b200r_reconstruct_batch: key %lld out of range [0, %lld)", (long long)keys[i],
+                        (long long)ix->ntotal);
+    DeviceGuard g(ix->device);
+    int64_t* kd = nullptr;
+    float* od = nullptr;
+    cudaError_t e = cudaMalloc(&kd, (size_t)n * sizeof(int64_t));
+    if (e == cudaSuccess) e = cudaMalloc(&od, (size_t)n * ix->d * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(kd, keys, (size_t)n * sizeof(int64_t), cudaMemcpyHostToDevice, ix->stream);
+    if (e == cudaSuccess) e = launch_rows_to_f32(ix->rows, ix->row_bytes, ix->d, ix->bf16, kd, n, od, ix->stream);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(out, od, (size_t)n * ix->d * sizeof(float), cudaMemcpyDeviceToHost, ix->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ix->stream);
+    cudaFree(kd);
+    cudaFree(od);
+    ix->st.n_kernel_launches++;
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(e == cudaErrorMemoryAllocation ? B200R_E_NOMEM : B200R_E_CUDA, "b200r_reconstruct_batch: %s",
+                    cudaGetErrorString(e));
+    }
+    return B200R_OK;
+}
+
 // ---------------------------------------------------------------------------
 // stand-alone normalise and merge
 // ---------------------------------------------------------------------------

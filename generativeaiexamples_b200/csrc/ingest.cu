@@ -204,6 +204,28 @@ __global__ void row_to_f32_kernel(const void* row, int d, int bf16, float* out) 
                       : reinterpret_cast<const float*>(row)[j];
 }
 
+// rows[ids[i]] -> out[i][0..d) as fp32, one warp per requested row (ids already validated)
+__global__ void __launch_bounds__(kRowWarps * 32) rows_to_f32_kernel(const uint8_t* __restrict__ rows, int row_bytes,
+                                                                      int d, int bf16, const int64_t* __restrict__ ids,
+                                                                      int64_t n, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t i = (int64_t)blockIdx.x * kRowWarps + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const uint8_t* r = rows + ids[i] * (int64_t)row_bytes;
+    for (int j = lane; j < d; j += 32)
+        out[i * d + j] = bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(r)[j])
+                              : reinterpret_cast<const float*>(r)[j];
+}
+
+cudaError_t launch_rows_to_f32(const void* rows, int row_bytes, int d, bool bf16, const int64_t* ids, int64_t n,
+                               float* out, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    const int g = (int)((n + kRowWarps - 1) / kRowWarps);
+    rows_to_f32_kernel<<<g, kRowWarps * 32, 0, st>>>(reinterpret_cast<const uint8_t*>(rows), row_bytes, d, bf16 ? 1 : 0,
+                                                     ids, n, out);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_row_to_f32(const void* row, int d, bool bf16, float* out, cudaStream_t st) {
     row_to_f32_kernel<<<1, 256, 0, st>>>(row, d, bf16 ? 1 : 0, out);
     return cudaGetLastError();

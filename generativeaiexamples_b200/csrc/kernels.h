@@ -94,5 +94,7 @@ void set_last_error(const char* msg);
 
 // reconstruct helper: corpus row -> fp32
 cudaError_t launch_row_to_f32(const void* row, int d, bool bf16, float* out, cudaStream_t st);
+cudaError_t launch_rows_to_f32(const void* rows, int row_bytes, int d, bool bf16, const int64_t* ids, int64_t n,
+                               float* out, cudaStream_t st);
 
 }  // namespace b200r

@@ -157,6 +157,15 @@ class B200IndexFlat:
         _lib.check(self._L.b200r_reconstruct(self._h, int(key), x.ctypes.data_as(ctypes.c_void_p)))
         return x
 
+    def reconstruct_batch(self, keys) -> np.ndarray:
+        """faiss ``reconstruct_batch``: (n, d) float32 for the given positions, one launch."""
+        keys = np.ascontiguousarray(keys, dtype="int64")
+        assert keys.ndim == 1
+        out = np.empty((keys.size, self.d), dtype=np.float32)
+        _lib.check(self._L.b200r_reconstruct_batch(self._h, keys.ctypes.data_as(ctypes.c_void_p), keys.size,
+                                                   out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
     def reset(self) -> None:
         _lib.check(self._L.b200r_reset(self._h))
 

@@ -406,9 +406,60 @@ class B200FlatVectorStore(_VSBase):
                 warnings.warn(f"No relevant docs were retrieved using the relevance score threshold {score_threshold}")
         return scored
 
+    # -- MMR (langchain_community FAISS.max_marginal_relevance_search*) ---------------------
+    def max_marginal_relevance_search_with_score_by_vector(self, embedding: List[float], *, k: int = 4,
+                                                           fetch_k: int = 20, lambda_mult: float = 0.5,
+                                                           filter: Optional[Dict[str, Any]] = None,
+                                                           ) -> List[Tuple[Document, float]]:
+        """The engine fetches ``fetch_k`` candidates (one search + one gather of their rows); the
+        greedy diversity selection over those <= fetch_k vectors is LangChain's own host-side
+        ``maximal_marginal_relevance`` (cosine similarities), restated below."""
+        if self.index is None:
+            return []
+        scores, indices = self.index.search(_to_matrix(embedding), fetch_k if filter is None else fetch_k * 2)
+        scores, indices = scores[0], indices[0]
+        if filter is not None:
+            wanted = {key: (value if isinstance(value, list) else [value]) for key, value in filter.items()}
+            keep = []
+            for pos in indices:
+                if pos == -1:
+                    continue
+                doc = self.docstore.search(self.index_to_docstore_id[int(pos)])
+                if not isinstance(doc, Document):
+                    raise ValueError(f"Could not find document for id {self.index_to_docstore_id[int(pos)]}, got {doc}")
+                if all(doc.metadata.get(key) in value for key, value in wanted.items()):
+                    keep.append(int(pos))
+            order = {int(p_): j for j, p_ in enumerate(indices)}
+            scores = np.array([scores[order[p_]] for p_ in keep], dtype=np.float32)
+            indices = np.array(keep, dtype=np.int64)
+        valid = [int(i) for i in indices if i != -1]  # -1 happens when not enough docs are returned
+        if hasattr(self.index, "reconstruct_batch"):
+            embeddings = self.index.reconstruct_batch(np.array(valid, dtype=np.int64))
+        else:
+            embeddings = np.stack([self.index.reconstruct(i) for i in valid]) if valid else np.zeros((0, 1), np.float32)
+        selected = maximal_marginal_relevance(np.array([embedding], dtype=np.float32), embeddings, k=k,
+                                              lambda_mult=lambda_mult)
+        out = []
+        for i in selected:
+            if indices[i] == -1:
+                continue
+            _id = self.index_to_docstore_id[int(indices[i])]
+            doc = self.docstore.search(_id)
+            if not isinstance(doc, Document):
+                raise ValueError(f"Could not find document for id {_id}, got {doc}")
+            out.append((doc, scores[i]))
+        return out
+
+    def max_marginal_relevance_search_by_vector(self, embedding: List[float], k: int = 4, fetch_k: int = 20,
+                                                lambda_mult: float = 0.5, filter: Optional[Dict[str, Any]] = None,
+                                                **kwargs: Any) -> List[Document]:
+        return [doc for doc, _ in self.max_marginal_relevance_search_with_score_by_vector(
+            embedding, k=k, fetch_k=fetch_k, lambda_mult=lambda_mult, filter=filter)]
+
     def max_marginal_relevance_search(self, query: str, k: int = 4, fetch_k: int = 20, lambda_mult: float = 0.5,
-                                      **kwargs: Any) -> List[Document]:
-        raise NotImplementedError("mmr search is outside the hot-path scope (SURVEY.md section 8f, row f4)")
+                                      filter: Optional[Dict[str, Any]] = None, **kwargs: Any) -> List[Document]:
+        return self.max_marginal_relevance_search_by_vector(self._embed_query(query), k=k, fetch_k=fetch_k,
+                                                            lambda_mult=lambda_mult, filter=filter, **kwargs)
 
     # -- retriever ------------------------------------------------------------------
     def as_retriever(self, **kwargs: Any) -> VectorStoreRetriever:
@@ -484,6 +535,51 @@ class B200FlatVectorStore(_VSBase):
         if "distance_strategy" not in kwargs and index.metric_type == METRIC_INNER_PRODUCT:
             kwargs["distance_strategy"] = DistanceStrategy.MAX_INNER_PRODUCT
         return cls(embeddings, index, docstore, index_to_docstore_id, storage=storage, device=device, **kwargs)
+
+
+def _cosine_similarity(X: np.ndarray, Y: np.ndarray) -> np.ndarray:
+    """langchain_community.utils.math.cosine_similarity: row-wise, zero norms give 0."""
+    if len(X) == 0 or len(Y) == 0:
+        return np.array([])
+    X = np.array(X)
+    Y = np.array(Y)
+    if X.shape[1] != Y.shape[1]:
+        raise ValueError(f"Number of columns in X and Y must be the same. X has shape {X.shape} and Y has shape "
+                         f"{Y.shape}.")
+    X_norm = np.linalg.norm(X, axis=1)
+    Y_norm = np.linalg.norm(Y, axis=1)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        similarity = np.dot(X, Y.T) / np.outer(X_norm, Y_norm)
+    similarity[np.isnan(similarity) | np.isinf(similarity)] = 0.0
+    return similarity
+
+
+def maximal_marginal_relevance(query_embedding: np.ndarray, embedding_list, lambda_mult: float = 0.5,
+                               k: int = 4) -> List[int]:
+    """langchain_community.vectorstores.utils.maximal_marginal_relevance (greedy MMR)."""
+    if min(k, len(embedding_list)) <= 0:
+        return []
+    if query_embedding.ndim == 1:
+        query_embedding = np.expand_dims(query_embedding, axis=0)
+    similarity_to_query = _cosine_similarity(query_embedding, embedding_list)[0]
+    most_similar = int(np.argmax(similarity_to_query))
+    idxs = [most_similar]
+    selected = np.array([embedding_list[most_similar]])
+    while len(idxs) < min(k, len(embedding_list)):
+        best_score = -np.inf
+        idx_to_add = -1
+        similarity_to_selected = _cosine_similarity(embedding_list, selected)
+        for i, query_score in enumerate(similarity_to_query):
+            if i in idxs:
+                continue
+            redundant_score = max(similarity_to_selected[i])
+            equation_score = lambda_mult * query_score - (1 - lambda_mult) * redundant_score
+            if equation_score > best_score:
+                best_score = equation_score
+                idx_to_add = i
+        idxs.append(idx_to_add)
+        selected = np.append(selected, [embedding_list[idx_to_add]], axis=0)
+    return idxs
 
 
 def _is_cuda_tensor(x) -> bool:

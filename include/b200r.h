@@ -127,6 +127,11 @@ int b200r_ntotal(const b200r_index* idx, int64_t* out);
 /* IndexFlat.reconstruct(key): the stored row as fp32 into a host buffer of d floats */
 int b200r_reconstruct(b200r_index* idx, int64_t key, float* out);
 
+/* IndexFlat.reconstruct_batch(keys) / the per-id reconstruct loop of LangChain FAISS
+ * max_marginal_relevance_search_with_score_by_vector: rows keys[0..n) as fp32 into a host
+ * buffer of n*d floats, one gather launch.  Any key out of range fails the whole call. */
+int b200r_reconstruct_batch(b200r_index* idx, const int64_t* keys, int64_t n, float* out);
+
 /* IndexFlat.reset() */
 int b200r_reset(b200r_index* idx);
 

@@ -188,6 +188,33 @@ class RefFAISS:
                 warnings.warn(f"No relevant docs were retrieved using the relevance score threshold {score_threshold}")
         return docs_and_similarities
 
+    # -- MMR ----------------------------------------------------------------
+    def max_marginal_relevance_search_by_vector(self, embedding, k=4, fetch_k=20, lambda_mult=0.5):
+        q = np.asarray(embedding, dtype=np.float64)
+        scores, indices = self.index.search(np.array([embedding], dtype=np.float32), fetch_k)
+        cand = [int(i) for i in indices[0] if i != -1]
+        if not cand or k <= 0:
+            return []
+        E = np.stack([self.index.reconstruct(i) for i in cand]).astype(np.float32)
+
+        def cos(a, b):
+            na, nb = np.linalg.norm(a), np.linalg.norm(b)
+            return 0.0 if na == 0 or nb == 0 else float(np.dot(a, b) / (na * nb))
+
+        to_q = [cos(np.float32(q), e) for e in E]
+        chosen = [int(np.argmax(to_q))]
+        while len(chosen) < min(k, len(cand)):
+            best, best_i = -np.inf, -1
+            for i in range(len(cand)):
+                if i in chosen:
+                    continue
+                red = max(cos(E[i], E[j]) for j in chosen)
+                sc = lambda_mult * to_q[i] - (1 - lambda_mult) * red
+                if sc > best:
+                    best, best_i = sc, i
+            chosen.append(best_i)
+        return [self.docstore.search(self.index_to_docstore_id[cand[i]]) for i in chosen]
+
     # -- delete -------------------------------------------------------------
     def delete(self, ids: Optional[List[str]] = None, **kwargs):
         if ids is None:

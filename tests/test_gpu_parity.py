@@ -520,3 +520,25 @@ def test_incremental_growth_and_interleaved_ops(built_lib):
     assert ix.stats()["capacity_rows"] >= ix.ntotal > 1024  # grew past the initial allocation
     np.testing.assert_array_equal(ix.reconstruct(ix.ntotal - 1), ref.reconstruct(ref.ntotal - 1))
     ix.close()
+
+
+def test_reconstruct_batch_and_mmr_on_engine(built_lib):
+    from generativeaiexamples_b200 import B200FlatVectorStore
+
+    rng = np.random.default_rng(92)
+    n, d = 5000, 1024
+    for storage in ("f32", "bf16"):
+        x = rng.standard_normal((n, d), dtype=np.float32)
+        ix = _mk("l2", d, storage=storage)
+        ix.add(x)
+        keys = rng.integers(0, n, 37)
+        got = ix.reconstruct_batch(keys)
+        want = np.stack([ix.reconstruct(int(i)) for i in keys])
+        np.testing.assert_array_equal(got, want)
+        with pytest.raises(RuntimeError):
+            ix.reconstruct_batch(np.array([0, n]))
+        ix.close()
+    vs = B200FlatVectorStore(lambda t: [0.0] * d, d)
+    vs.add_embeddings([(f"t{i}", x[i].tolist()) for i in range(200)])
+    docs = vs.max_marginal_relevance_search_by_vector(x[5].tolist(), k=4, fetch_k=20)
+    assert docs[0].page_content == "t5" and len(docs) == 4 and len({d_.page_content for d_ in docs}) == 4

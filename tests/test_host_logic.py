@@ -169,8 +169,34 @@ def test_add_embeddings_and_async():
 def test_empty_store_and_bad_embedding_function(caplog):
     vs = B200FlatVectorStore(lambda t: [0.0] * D, None)
     assert vs.similarity_search_with_score_by_vector([0.0] * D) == []
-    with pytest.raises(NotImplementedError):
-        vs.max_marginal_relevance_search("q")
+    assert vs.max_marginal_relevance_search("q") == []
+
+
+def test_mmr_matches_restatement():
+    """search_type="mmr" (langchain allowed_search_types): engine fetches, LangChain's greedy
+    diversity selection runs on the <= fetch_k reconstructed vectors."""
+    ours, ref = _pair()
+    rng = np.random.default_rng(3)
+    base = rng.standard_normal((8, D))
+    texts, embs = [], []
+    for c in range(8):  # 8 clusters of 10 near-duplicates: MMR must spread over clusters
+        for j in range(10):
+            v = base[c] + 0.05 * rng.standard_normal(D)
+            texts.append(f"c{c}-{j}")
+            embs.append((v / np.linalg.norm(v)).astype(np.float32).tolist())
+    ours.add_embeddings(list(zip(texts, embs)), ids=list(texts))
+    ref.add_embeddings(list(zip(texts, embs)), ids=list(texts))
+    qv = (base[2] + 0.3 * base[5]).astype(np.float32)
+    qv = (qv / np.linalg.norm(qv)).tolist()
+    for lam in (0.5, 0.1, 0.9):
+        got = ours.max_marginal_relevance_search_by_vector(qv, k=5, fetch_k=30, lambda_mult=lam)
+        want = ref.max_marginal_relevance_search_by_vector(qv, k=5, fetch_k=30, lambda_mult=lam)
+        assert [d.page_content for d in got] == [d.page_content for d in want], lam
+    plain = [d.page_content for d in ours.similarity_search_by_vector(qv, k=5)]
+    mmr = [d.page_content for d in ours.max_marginal_relevance_search_by_vector(qv, k=5, fetch_k=30, lambda_mult=0.1)]
+    assert len({t.split("-")[0] for t in mmr}) > len({t.split("-")[0] for t in plain})
+    r = ours.as_retriever(search_type="mmr", search_kwargs={"k": 3, "fetch_k": 20})
+    assert len(r.get_relevant_documents("c2-0")) == 3
 
 
 def test_coalescer_batches_concurrent_callers():
