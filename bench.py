@@ -338,6 +338,30 @@ def main_gpu(args):
                 "hbm_frac": (max_rows * DIM * 4 / (per * 1e-3) / 1e9) / peak,
                 "note": "crossover config (128 flop/B): both fractions reported; flops = 2*nq*N*d, bytes = N*d*4"}
 
+    # ---- service view: 64 concurrent single-query callers through the coalescer (N=1 only) -------
+    conc = None
+    if world == 1 and args.concurrent > 0:
+        from concurrent.futures import ThreadPoolExecutor
+
+        from generativeaiexamples_b200.batching import SearchCoalescer
+
+        co = SearchCoalescer(index.local)
+        nreq = args.concurrent * 8
+
+        def one(i):
+            return co.search(Qh[i % pool: i % pool + 1], TOPK)
+
+        with ThreadPoolExecutor(args.concurrent) as ex:
+            list(ex.map(one, range(args.concurrent)))  # warm-up
+            co.n_requests = co.n_launches = 0
+            t0 = time.perf_counter()
+            list(ex.map(one, range(nreq)))
+            dt = time.perf_counter() - t0
+        conc = {"value": nreq / dt, "unit": "queries/s", "callers": args.concurrent, "requests": nreq,
+                "launches": co.n_launches,
+                "note": "threads each calling an nq=1 host search (the pattern of faiss_vdb_service.py:169-174); "
+                        "SearchCoalescer merges the queued ones into one launch (wall clock, host buffers)"}
+
     if rank == 0:
         qps = args.steps * 1000.0 / ms_dev
         e2e_qps = args.steps * 1000.0 / ms_e2e_wall
@@ -352,7 +376,10 @@ def main_gpu(args):
                        "l2_policy": "no flush: per-GPU corpus (>=5 GB) >> 126 MB L2, new query every step",
                        "ingest_s": round(ingest_s, 3)},
             "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": DIM * 4,
-                    "d2h_bytes_per_step": TOPK * 12, "api": "ShardedFlatIndex.search(numpy) -> b200r_search(HOST,HOST)"},
+                    "d2h_bytes_per_step": TOPK * 12,
+                    "api": ("B200IndexFlat.search(numpy) = b200r_search(HOST query, HOST results)" if world == 1 else
+                            "ShardedFlatIndex.search(numpy): pinned H2D -> b200r_search(DEVICE) -> NCCL allgather -> "
+                            "b200r_merge_topk -> one packed D2H")},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": (algo_bytes * traffic["traffic_over_algorithmic"]) if traffic else None,
@@ -365,6 +392,7 @@ def main_gpu(args):
                          "note": "kernel_ms = prep_queries + scan launch, CUDA events on the launching stream"},
             "cpu_baseline": cb,
             "batch256": b256,
+            "concurrent_callers": conc,
             "clocks": clocks,
         }
         print(json.dumps(line))
@@ -382,6 +410,7 @@ if __name__ == "__main__":
     ap.add_argument("--rows", type=int, default=N_TOTAL, help="total corpus rows (default: the 10M headline config)")
     ap.add_argument("--batch256-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--concurrent", type=int, default=64, help="callers for the coalesced service-view number (0 = skip)")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
     sys.exit(main_reference(a) if a.impl == "reference" else main_gpu(a))

@@ -118,17 +118,24 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// K-major, 128-byte-swizzled operand tile (rows of 128 B, 8-row groups 1024 B apart):
-// start>>4 | LBO=1 (unused for swizzled K-major) | SBO=1024>>4 | version=1 | SWIZZLE_128B
+#ifndef B200R_GEMM_KBYTES
+#define B200R_GEMM_KBYTES 128  // bytes of K per pipeline stage = width of the swizzle atom (128 or 64)
+#endif
+
+// K-major swizzled operand tile: rows of KBYTES bytes, 8-row groups 8*KBYTES apart.
+// start>>4 | LBO=1 (unused for swizzled K-major) | SBO=(8*KBYTES)>>4 | version=1 | layout
+// (SWIZZLE_128B = 2, SWIZZLE_64B = 4)
 __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(const void* smem_tile) {
     const uint64_t addr = (uint64_t)((smem_u32(smem_tile) & 0x3FFFFu) >> 4);
-    return addr | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+    constexpr uint64_t sbo = (8ull * B200R_GEMM_KBYTES) >> 4;
+    constexpr uint64_t layout = B200R_GEMM_KBYTES == 128 ? 2ull : 4ull;
+    return addr | (1ull << 16) | (sbo << 32) | (1ull << 46) | (layout << 61);
 }
 
 // ---------------------------------------------------------------------------
 constexpr int kGemmTileN = 256;        // corpus rows per tile (UMMA N)
 constexpr int kGemmTileM = 128;        // queries per M tile (UMMA M)
-constexpr int kGemmKBytes = 128;       // one swizzle atom of K per stage
+constexpr int kGemmKBytes = B200R_GEMM_KBYTES;  // one swizzle atom of K per stage
 constexpr int kGemmBBytes = kGemmTileN * kGemmKBytes;   // 32 KB
 constexpr int kGemmABytes = kGemmTileM * kGemmKBytes;   // 16 KB per M tile
 constexpr int kGemmBuckets = 512;      // score histogram resolution for the grid-wide threshold
@@ -171,7 +178,7 @@ __global__ void __launch_bounds__(128 + 128 * MT, 1)
 gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                    const GemmParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    constexpr int STAGES = MT == 1 ? 4 : 3;
+    constexpr int STAGES = (MT == 1 ? 4 : 3) * (128 / kGemmKBytes);
     constexpr int STAGE_BYTES = kGemmBBytes + MT * kGemmABytes;
     constexpr int ACC_STAGES = MT == 1 ? 2 : 1;      // 512 TMEM columns in total
     constexpr int ACC_COLS = MT * kGemmTileN;        // columns per accumulator stage
@@ -224,7 +231,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             const uint64_t pol = policy_evict_first();
             int s = 0;
             uint32_t ph = 0;
-            const int kstep = BF16 ? 64 : 32;  // elements per 128-byte K block
+            const int kstep = kGemmKBytes / (BF16 ? 2 : 4);  // elements per K block
             // The K-blocked tile loads touch 256 rows x 128 B each: scattered for DRAM.  Stream the
             // tile's rows (one contiguous block) into L2 a few tiles ahead with bulk prefetches, so
             // that DRAM sees long sequential reads and the TMA tile loads hit L2.
@@ -947,11 +954,12 @@ static bool make_map(CUtensorMap* map, const void* base, int64_t rows, int d_pad
     if (!enc) return false;
     const cuuint64_t dims[2] = {(cuuint64_t)d_pad, (cuuint64_t)(rows > 0 ? rows : 1)};
     const cuuint64_t strides[1] = {(cuuint64_t)d_pad * (bf16 ? 2 : 4)};
-    const cuuint32_t box[2] = {(cuuint32_t)(bf16 ? 64 : 32), (cuuint32_t)box_rows};
+    const cuuint32_t box[2] = {(cuuint32_t)(kGemmKBytes / (bf16 ? 2 : 4)), (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1, 1};
     const CUresult r = enc(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
                            const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           kGemmKBytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS;
 }
@@ -983,7 +991,7 @@ int gemm_kprime(int k) {
 template <bool BF16, int MT, int KP, bool L2>
 static cudaError_t launch_filter_one(const CUtensorMap& mq, const CUtensorMap& mx, const GemmParams& p, int grid,
                                      cudaStream_t st) {
-    constexpr int STAGES = MT == 1 ? 4 : 3;
+    constexpr int STAGES = (MT == 1 ? 4 : 3) * (128 / kGemmKBytes);
     constexpr int STAGE_BYTES = kGemmBBytes + MT * kGemmABytes;
     const size_t smem = 1024 + (size_t)STAGES * STAGE_BYTES + 256 + (L2 ? (size_t)4 * MT * kGemmTileN * sizeof(float) : 0);
     auto kern = gemm_filter_kernel<BF16, MT, KP, L2>;

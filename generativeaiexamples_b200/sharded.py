@@ -132,6 +132,9 @@ class ShardedFlatIndex:
         assert q.shape[1] == self.d
         assert k > 0
         as_numpy = not (isinstance(q, torch.Tensor) and q.is_cuda)
+        if self._on_gpu and self.world == 1 and as_numpy:
+            # a single shard and a host caller: this IS faiss's index.search -> b200r_search(HOST, HOST)
+            return self.local.search(np.ascontiguousarray(q, dtype=np.float32), k)
         if self._on_gpu:
             dev = self._buf_device()
             d_bytes, block = _packed_layout(nq, k)
