@@ -156,8 +156,18 @@ def cpu_reference(steps: int, warmup: int, sample_rows: int = 400_000, budget_s:
     qps_faithful, n1 = run(lambda v: FlatRef.knn(0, v, x, TOPK), min(warmup, 2), steps, budget_s * 0.4)
     # (ii) the same scan row-parallel over all cores (not a faiss code path; stronger baseline)
     qps_all, n2 = run(lambda v: FlatRef.knn_allcores(0, v, x, TOPK), min(warmup, 3), steps, budget_s * 0.6)
+    cpu_model = ""
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name"):
+                cpu_model = ln.split(":", 1)[1].strip()
+                break
+    except OSError:
+        pass
     return {
-        "value": qps_all * scale, "unit": "queries/s", "cores": threads, "kind": "port",
+        "value": qps_all * scale, "unit": "queries/s", "cores": threads, "kind": "port", "cpu_model": cpu_model,
+        "omp_num_threads": os.environ.get("OMP_NUM_THREADS", "unset (OpenMP default = all cores)"),
+        "blas": "OpenBLAS bundled with numpy (not on the nq=1 path)",
         "sample": (f"nq=1 top-{TOPK} scans over a {sample_rows} x {DIM} fp32 slice ({n2} all-core steps, {n1} "
                    f"single-thread steps), scaled linearly to {N_TOTAL} rows"),
         "faithful_1thread_value": qps_faithful * scale,
@@ -295,6 +305,14 @@ def main_gpu(args):
         launches += args.steps  # K4 merge, one per step
     clocks = sampler.stop() if sampler else None
     _, ms_e2e_wall = timed(e2e_step, args.steps, args.warmup)
+    # per-call latency distribution of the host-buffer path (wall clock around each call)
+    lat = []
+    for i in range(min(args.steps, 200)):
+        t0 = time.perf_counter()
+        e2e_step(i)
+        lat.append((time.perf_counter() - t0) * 1e6)
+    lat.sort()
+    e2e_lat = {"p50_us": lat[len(lat) // 2], "p99_us": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "calls": len(lat)}
 
     # ---- scan kernel alone: CUDA events on the launching stream, live -----------------------
     index.local.set_timing(True)
@@ -376,7 +394,7 @@ def main_gpu(args):
                        "l2_policy": "no flush: per-GPU corpus (>=5 GB) >> 126 MB L2, new query every step",
                        "ingest_s": round(ingest_s, 3)},
             "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": DIM * 4,
-                    "d2h_bytes_per_step": TOPK * 12,
+                    "d2h_bytes_per_step": TOPK * 12, "latency": e2e_lat,
                     "api": ("B200IndexFlat.search(numpy) = b200r_search(HOST query, HOST results)" if world == 1 else
                             "ShardedFlatIndex.search(numpy): pinned H2D -> b200r_search(DEVICE) -> NCCL allgather -> "
                             "b200r_merge_topk -> one packed D2H")},
