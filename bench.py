@@ -390,7 +390,8 @@ def main_gpu(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD if n_total == N_TOTAL else f"REDUCED ({n_total} rows) " + WORKLOAD,
                        "rows": n_total, "rows_per_gpu": max_rows, "dim": DIM, "k": TOPK, "nq": 1,
-                       "parallelism": f"row-shard x{world} + NCCL allgather merge" if world > 1 else "single GPU",
+                       "parallelism": (f"row-shard x{world} + " + ("fused NVLink peer-store exchange" if getattr(index, "_xchg", None)
+                                                                  else "NCCL allgather") + " + K4 select") if world > 1 else "single GPU",
                        "l2_policy": "no flush: per-GPU corpus (>=5 GB) >> 126 MB L2, new query every step",
                        "ingest_s": round(ingest_s, 3)},
             "e2e": {"value": e2e_qps, "unit": "queries/s", "h2d_bytes_per_step": DIM * 4,

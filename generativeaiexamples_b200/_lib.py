@@ -58,6 +58,9 @@ SIGNATURES = {
     "b200r_load": (_int, [ctypes.c_char_p, ctypes.POINTER(Config), ctypes.POINTER(_vp)]),
     "b200r_merge_topk": (_int, [_i32, _vp, _vp, _i64, _i32, _i32, _i64, _i64, _i32, _vp, _vp, _i32, _vp]),
     "b200r_search_noalloc": (_int, [_vp, _i64, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _i64, _i32, _vp]),
+    "b200r_exchange_buffer_bytes": (_i64, []),
+    "b200r_search_exchange": (_int, [_vp, _vp, _i64, _int, ctypes.POINTER(_vp), _i32, _i32, ctypes.c_uint32, _vp, _vp,
+                                     _vp]),
     "b200r_set_id_base": (_int, [_vp, _i64]),
     "b200r_stats_get": (_int, [_vp, ctypes.POINTER(Stats)]),
     "b200r_set_timing": (_int, [_vp, _i32]),

@@ -567,6 +567,59 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
 }
 
 // ---------------------------------------------------------------------------
+// fused search + NVLink exchange (multi-GPU small batches)
+// ---------------------------------------------------------------------------
+extern "C" int64_t b200r_exchange_buffer_bytes(void) { return kXchgBytes; }
+
+extern "C" int b200r_search_exchange(b200r_index* ix, const float* q, int64_t nq, int k, void* const* peer_bufs,
+                                     int32_t world, int32_t rank, uint32_t epoch, float* D, int64_t* I, void* stream) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_search_exchange: null index");
+    if (!q || !D || !I || !peer_bufs) return fail(B200R_E_INVALID, "b200r_search_exchange: null buffer");
+    if (nq < 1 || nq > kScanMaxNQ)
+        return fail(B200R_E_UNSUPPORTED, "b200r_search_exchange: nq %lld outside 1..%d", (long long)nq, kScanMaxNQ);
+    if (k < 1 || k > kScanMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_search_exchange: k %d outside 1..%d", k, kScanMaxK);
+    if (world < 1 || world > kXchgMaxWorld || rank < 0 || rank >= world)
+        return fail(B200R_E_INVALID, "b200r_search_exchange: bad world/rank %d/%d", world, rank);
+    if (epoch == 0) return fail(B200R_E_INVALID, "b200r_search_exchange: epoch must start at 1");
+    for (int r = 0; r < world; r++)
+        if (!peer_bufs[r]) return fail(B200R_E_INVALID, "b200r_search_exchange: null peer buffer %d", r);
+    std::lock_guard<std::mutex> lk(ix->mu);
+    DeviceGuard g(ix->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t nq_slots = round_up(nq, kScanMaxNQ);
+    int rc = ensure_search_ws(ix, nq_slots, nq, k);
+    if (rc != B200R_OK) return rc;
+    CU(launch_prep_queries(q, nq, ix->d, ix->d_pad, nq_slots, ix->cfg.normalize_queries != 0, ix->q_dev, st));
+    ScanParams p{};
+    p.corpus = ix->rows;
+    p.n_rows = ix->ntotal;
+    p.d = ix->d_pad;
+    p.row_bytes = ix->row_bytes;
+    p.k = k;
+    p.evict_first = ((size_t)ix->ntotal * ix->row_bytes > (size_t)96 << 20) ? 1 : 0;
+    p.scratch = ix->scratch;
+    p.counter = ix->counter;
+    p.id_base = ix->cfg.id_base;
+    p.q = ix->q_dev;
+    p.out_d = ix->out_d;  // unused in exchange mode
+    p.out_i = ix->out_i;
+    p.xchg_world = world;
+    p.xchg_rank = rank;
+    p.xchg_epoch = epoch;
+    for (int r = 0; r < world; r++) p.xchg_peer[r] = reinterpret_cast<uint8_t*>(peer_bufs[r]);
+    int grid = 0;
+    CU(launch_scan(p, (int)nq, ix->l2, ix->bf16, ix->num_sms, ix->smem_optin, st, &grid));
+    CU(launch_merge_wait(ix->l2, reinterpret_cast<uint8_t*>(peer_bufs[rank]), world, (int)nq, k, epoch, D, I, st));
+    ix->st.n_kernel_launches += 3;
+    ix->st.last_grid = grid;
+    ix->st.last_path = B200R_PATH_SCAN;
+    ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
+    ix->st.n_search_calls++;
+    ix->st.n_queries += nq;
+    return B200R_OK;
+}
+
+// ---------------------------------------------------------------------------
 // remove_ids / reconstruct
 // ---------------------------------------------------------------------------
 extern "C" int b200r_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, int64_t* n_removed) {

@@ -28,7 +28,26 @@ struct ScanParams {
     float* out_d;         // [nq][k]
     int64_t* out_i;       // [nq][k]
     int64_t id_base;      // added to every returned id (row-sharded multi-GPU)
+    // fused exchange (xchg_world > 0): the final writer stores this shard's result straight into every
+    // peer's exchange buffer over NVLink and raises a flag there, instead of writing out_d / out_i
+    int xchg_world, xchg_rank;
+    uint32_t xchg_epoch;
+    uint8_t* xchg_peer[8];  // peer-mapped base of each rank's exchange buffer (layout below)
 };
+
+// Exchange buffer of one rank (symmetric: same layout on every rank, peer-mapped over NVLink):
+//   [parity 0|1][slot of source rank 0..7] of kXchgSlotBytes: scores fp32 [nq][k] at +0, ids int64 [nq][k] at +2048
+//   then flags: one uint32 per (parity, source rank), 128 bytes apart; then one status word
+constexpr int kXchgMaxWorld = 8;
+constexpr int kXchgSlotBytes = 8192;
+constexpr int kXchgIdOffset = 2048;
+constexpr int kXchgParityBytes = kXchgMaxWorld * kXchgSlotBytes;
+constexpr int kXchgFlagOffset = 2 * kXchgParityBytes;
+constexpr int kXchgStatusOffset = kXchgFlagOffset + 2 * kXchgMaxWorld * 128;
+constexpr int kXchgBytes = kXchgStatusOffset + 256;
+
+cudaError_t launch_merge_wait(bool l2, uint8_t* my_buf, int world, int nq, int k, uint32_t epoch, float* out_d,
+                              int64_t* out_i, cudaStream_t st);
 
 size_t scan_scratch_bytes(int max_grid);
 cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st,

@@ -53,6 +53,83 @@ __global__ void __launch_bounds__(128) merge_topk_kernel(const float* __restrict
     }
 }
 
+// Fused-exchange variant: first wait until every rank's scan kernel has delivered this epoch's
+// result into the local exchange buffer (flags written with st.release.sys over NVLink), then run
+// the same select over the `world` slots.  The wait is bounded: if a peer never shows up the status
+// word is set and the output is padding, instead of a kernel that spins forever.
+template <int KPL, bool L2>
+__global__ void __launch_bounds__(128) merge_wait_kernel(uint8_t* buf, int world, int nq, int k, uint32_t epoch,
+                                                         float* __restrict__ out_d, int64_t* __restrict__ out_i) {
+    __shared__ int s_ok;
+    const uint32_t parity = epoch & 1u;
+    if (threadIdx.x == 0) s_ok = 1;
+    __syncthreads();
+    if (threadIdx.x < world) {
+        const uint32_t* flag =
+            reinterpret_cast<const uint32_t*>(buf + kXchgFlagOffset + (parity * kXchgMaxWorld + threadIdx.x) * 128);
+        const long long t_end = clock64() + 4000000000ll;  // ~2 s
+        uint32_t seen;
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(flag) : "memory");
+        } while (seen != epoch && clock64() < t_end);
+        if (seen != epoch) {
+            s_ok = 0;
+            *reinterpret_cast<int*>(buf + kXchgStatusOffset) = 1 + (int)threadIdx.x;
+        }
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int q = threadIdx.x >> 5;
+    if (q >= nq) return;
+    const uint8_t* base = buf + (size_t)parity * kXchgParityBytes;
+    const int total = world * k;
+    WarpTopK<KPL, L2> m;
+    m.init(k);
+    if (s_ok) {
+        for (int b0 = 0; b0 < total; b0 += 32) {
+            const int pos = b0 + lane;
+            float v = worst_val<L2>();
+            uint32_t id = kEmptyId;
+            if (pos < total) {
+                const int l = pos / k, e = pos - l * k;
+                const uint8_t* slot = base + (size_t)l * kXchgSlotBytes;
+                if (reinterpret_cast<const int64_t*>(slot + kXchgIdOffset)[q * k + e] >= 0) {
+                    v = reinterpret_cast<const float*>(slot)[q * k + e];
+                    id = (uint32_t)pos;
+                }
+            }
+            m.offer_lanes(v, id);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < KPL; j++) {
+        const int e = j * 32 + lane;
+        if (e < k) {
+            int64_t gid = -1;
+            if (m.id[j] != kEmptyId) {
+                const int l = m.id[j] / k, ee = m.id[j] - l * k;
+                gid = reinterpret_cast<const int64_t*>(base + (size_t)l * kXchgSlotBytes + kXchgIdOffset)[q * k + ee];
+            }
+            out_d[q * k + e] = m.v[j];
+            out_i[q * k + e] = gid;
+        }
+    }
+}
+
+cudaError_t launch_merge_wait(bool l2, uint8_t* my_buf, int world, int nq, int k, uint32_t epoch, float* out_d,
+                              int64_t* out_i, cudaStream_t st) {
+    if (world < 1 || world > kXchgMaxWorld || nq < 1 || nq > kScanMaxNQ || k < 1 || k > kScanMaxK)
+        return cudaErrorInvalidValue;
+    if (k <= 32) {
+        if (l2) merge_wait_kernel<1, true><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i);
+        else merge_wait_kernel<1, false><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i);
+    } else {
+        if (l2) merge_wait_kernel<4, true><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i);
+        else merge_wait_kernel<4, false><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i);
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t launch_merge(bool l2, const float* cand_d, const int64_t* cand_i, int64_t nq, int n_lists, int k_in,
                          int64_t stride_d, int64_t stride_i, int k_out, float* out_d, int64_t* out_i,
                          cudaStream_t st) {

@@ -256,13 +256,40 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
         WarpTopK<KPL, L2> m;
         m.init(p.k);
         m.template merge_from<false>(sm_lists + (size_t)warp * NW * KCAP, 0, NW, 1, KCAP);
+        if (p.xchg_world == 0) {
 #pragma unroll
-        for (int j = 0; j < KPL; j++) {
-            const int e = j * 32 + lane;
-            if (e < p.k) {
-                p.out_d[(size_t)warp * p.k + e] = m.v[j];
-                p.out_i[(size_t)warp * p.k + e] = (m.id[j] == kEmptyId) ? -1 : (int64_t)m.id[j] + p.id_base;
+            for (int j = 0; j < KPL; j++) {
+                const int e = j * 32 + lane;
+                if (e < p.k) {
+                    p.out_d[(size_t)warp * p.k + e] = m.v[j];
+                    p.out_i[(size_t)warp * p.k + e] = (m.id[j] == kEmptyId) ? -1 : (int64_t)m.id[j] + p.id_base;
+                }
             }
+        } else {
+            // fused exchange: this shard's top-k goes straight into slot [my rank] of EVERY rank's
+            // exchange buffer (plain stores to peer-mapped addresses = NVLink writes)
+            const size_t slot = (size_t)(p.xchg_epoch & 1u) * kXchgParityBytes + (size_t)p.xchg_rank * kXchgSlotBytes;
+            for (int r = 0; r < p.xchg_world; r++) {
+                float* pd = reinterpret_cast<float*>(p.xchg_peer[r] + slot);
+                int64_t* pi = reinterpret_cast<int64_t*>(p.xchg_peer[r] + slot + kXchgIdOffset);
+#pragma unroll
+                for (int j = 0; j < KPL; j++) {
+                    const int e = j * 32 + lane;
+                    if (e < p.k) {
+                        pd[(size_t)warp * p.k + e] = m.v[j];
+                        pi[(size_t)warp * p.k + e] = (m.id[j] == kEmptyId) ? -1 : (int64_t)m.id[j] + p.id_base;
+                    }
+                }
+            }
+            __threadfence_system();
+        }
+    }
+    if (p.xchg_world > 0) {
+        __syncthreads();  // every result store of this CTA is fenced; now raise the flags
+        if (threadIdx.x < p.xchg_world) {
+            uint32_t* flag = reinterpret_cast<uint32_t*>(p.xchg_peer[threadIdx.x] + kXchgFlagOffset +
+                                                        ((p.xchg_epoch & 1u) * kXchgMaxWorld + p.xchg_rank) * 128);
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(p.xchg_epoch) : "memory");
         }
     }
     if (threadIdx.x == 0) *p.counter = 0;  // ready for the next launch on this stream

@@ -174,6 +174,21 @@ int b200r_search_noalloc(const void* corpus, int64_t n_rows, int32_t dim, int32_
                          const float* q, int32_t nq, int32_t k, float* D, int64_t* I, int64_t id_base,
                          int32_t device, void* stream);
 
+/* No faiss counterpart: the multi-GPU search for small batches (nq <= 4, k <= 128) with the
+ * exchange FUSED into the kernels instead of an NCCL call.  Every rank owns one exchange buffer of
+ * b200r_exchange_buffer_bytes() bytes, zero-filled once, in memory that all ranks can address
+ * (CUDA IPC / torch symmetric memory); peer_bufs[r] is rank r's buffer as mapped in THIS process.
+ * The scan kernel's final writer stores this shard's top-k straight into slot [rank] of every
+ * rank's buffer (NVLink stores) and raises a per-(epoch parity, rank) flag there; the select kernel
+ * that follows on the same stream waits (bounded, ~2 s) for the `world` flags of this epoch in its
+ * own buffer and writes the global top-k to the DEVICE arrays D / I.  All ranks must call it
+ * collectively with the same nq, k and epoch; epoch starts at 1 and grows by 1 per call (two
+ * epochs are buffered, which the stream order of scan -> select on every rank makes sufficient).
+ * q is a DEVICE array (nq, d); the call is asynchronous on `stream`. */
+int64_t b200r_exchange_buffer_bytes(void);
+int b200r_search_exchange(b200r_index* idx, const float* q, int64_t nq, int k, void* const* peer_bufs, int32_t world,
+                          int32_t rank, uint32_t epoch, float* D, int64_t* I, void* stream);
+
 /* row-sharding support: change the id offset after the shard layout moved */
 int b200r_set_id_base(b200r_index* idx, int64_t id_base);
 

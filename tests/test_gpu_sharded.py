@@ -15,7 +15,8 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, out):
+def _worker(rank, world, port, out, fused):
+    os.environ["B200R_FUSED_EXCHANGE"] = fused
     import torch
     import torch.distributed as dist
 
@@ -40,13 +41,20 @@ def _worker(rank, world, port, out):
                 res[(metric, nq, k)] = (D, I)
             Dd, Id = idx.search(torch.from_numpy(q[:2]).cuda(), 5)  # device in -> device out
             res[(metric, "dev")] = (Dd.cpu().numpy(), Id.cpu().numpy())
+            # a run of back-to-back small searches: exercises the two-epoch buffering of the fused
+            # exchange (device outputs are only read after the whole run)
+            outs = [idx.search(torch.from_numpy(q[i:i + 1]).cuda(), 10) for i in range(12)]
+            res[(metric, "run")] = (np.concatenate([o[0].cpu().numpy() for o in outs]),
+                                    np.concatenate([o[1].cpu().numpy() for o in outs]))
+            res[(metric, "fused")] = idx._xchg is not None
         if rank == 0:
             out.put(res)
     finally:
         dist.destroy_process_group()
 
 
-def test_sharded_nccl_two_ranks(built_lib):
+@pytest.mark.parametrize("fused", ["0", "1"])
+def test_sharded_nccl_two_ranks(built_lib, fused):
     import torch
     import torch.multiprocessing as mp
 
@@ -57,7 +65,7 @@ def test_sharded_nccl_two_ranks(built_lib):
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, out)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, out, fused)) for r in range(2)]
     for p in procs:
         p.start()
     res = out.get(timeout=300)
@@ -67,10 +75,14 @@ def test_sharded_nccl_two_ranks(built_lib):
     rng = np.random.default_rng(11)
     x = rng.standard_normal((50001, 256), dtype=np.float32)
     q = rng.standard_normal((40, 256), dtype=np.float32)
-    for (metric, nq, k), (D, I) in ((kk, v) for kk, v in res.items() if kk[1] != "dev"):
+    for (metric, nq, k), (D, I) in ((kk, v) for kk, v in res.items() if len(kk) == 3):
         Dt, It = truth_topk("l2" if metric else "ip", q[:nq], x, k + 8)
         assert_topk_parity(D, I, Dt, It, what=f"sharded nccl metric={metric} nq={nq} k={k}")
     for metric in (0, 1):
         D, I = res[(metric, "dev")]
         Dt, It = truth_topk("l2" if metric else "ip", q[:2], x, 13)
         assert_topk_parity(D, I, Dt, It, what="sharded nccl device tensors")
+        D, I = res[(metric, "run")]
+        Dt, It = truth_topk("l2" if metric else "ip", q[:12], x, 18)
+        assert_topk_parity(D, I, Dt, It, what="sharded back-to-back run")
+    assert res[(0, "fused")] == (fused == "1")
