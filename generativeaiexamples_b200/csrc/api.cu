@@ -73,6 +73,11 @@ struct b200r_index {
     int64_t ntotal = 0, capacity = 0;
 
     cudaStream_t stream = nullptr;  // the index's own stream
+    // last writer of rows/norms: searches on another stream wait for it (add() with a device tensor
+    // runs asynchronously on the caller's stream)
+    cudaEvent_t data_ev = nullptr;
+    bool data_ev_set = false;
+    cudaStream_t data_ev_stream = nullptr;
     // add(): double-buffered host->device staging
     uint8_t* pin_add = nullptr;
     uint8_t* dev_add = nullptr;
@@ -136,6 +141,8 @@ static int ensure_capacity(b200r_index* ix, int64_t need, cudaStream_t st) {
         CU(cudaMemcpyAsync(nn, ix->norms, (size_t)ix->ntotal * sizeof(float), cudaMemcpyDeviceToDevice, st));
     }
     CU(cudaStreamSynchronize(st));
+    // asynchronous searches on other streams may still be reading the old buffers
+    if (ix->rows) CU(cudaDeviceSynchronize());
     if (ix->rows) cudaFree(ix->rows);
     if (ix->norms) cudaFree(ix->norms);
     ix->rows = nr;
@@ -168,6 +175,7 @@ static void free_index(b200r_index* ix) {
     cudaFreeHost(ix->fail_pin);
     for (auto& e : ix->add_ev)
         if (e) cudaEventDestroy(e);
+    if (ix->data_ev) cudaEventDestroy(ix->data_ev);
     if (ix->t0) cudaEventDestroy(ix->t0);
     if (ix->t1) cudaEventDestroy(ix->t1);
     if (ix->stream) cudaStreamDestroy(ix->stream);
@@ -231,6 +239,7 @@ extern "C" int b200r_create(const b200r_config* cfg, b200r_index** out) {
     CU_OR_FREE(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
     CU_OR_FREE(cudaEventCreateWithFlags(&ix->add_ev[0], cudaEventDisableTiming));
     CU_OR_FREE(cudaEventCreateWithFlags(&ix->add_ev[1], cudaEventDisableTiming));
+    CU_OR_FREE(cudaEventCreateWithFlags(&ix->data_ev, cudaEventDisableTiming));
     CU_OR_FREE(cudaEventCreate(&ix->t0));
     CU_OR_FREE(cudaEventCreate(&ix->t1));
     CU_OR_FREE(cudaMalloc(&ix->scratch, scan_scratch_bytes(ix->num_sms)));
@@ -339,6 +348,13 @@ extern "C" int b200r_add(b200r_index* ix, const void* x, int64_t n, int dtype, i
     ix->ntotal += n;
     ix->max_norm_dirty = true;
     ix->st.n_rows_added += n;
+    if (mem_kind == B200R_DEVICE) {  // still in flight on the caller's stream
+        CU(cudaEventRecord(ix->data_ev, st));
+        ix->data_ev_set = true;
+        ix->data_ev_stream = st;
+    } else {
+        ix->data_ev_set = false;  // host adds return after a stream synchronize
+    }
     return B200R_OK;
 }
 
@@ -444,6 +460,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
         if (rc != B200R_OK) return rc;
     }
 
+    if (ix->data_ev_set && ix->data_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->data_ev, 0));
     if (ix->timing) CU(cudaEventRecord(ix->t0, st));
     const float* q_src = (const float*)q;
     if (q_mem_kind == B200R_HOST) {
@@ -589,6 +606,7 @@ extern "C" int b200r_search_exchange(b200r_index* ix, const float* q, int64_t nq
     const int64_t nq_slots = round_up(nq, kScanMaxNQ);
     int rc = ensure_search_ws(ix, nq_slots, nq, k);
     if (rc != B200R_OK) return rc;
+    if (ix->data_ev_set && ix->data_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->data_ev, 0));
     CU(launch_prep_queries(q, nq, ix->d, ix->d_pad, nq_slots, ix->cfg.normalize_queries != 0, ix->q_dev, st));
     ScanParams p{};
     p.corpus = ix->rows;
@@ -642,6 +660,8 @@ extern "C" int b200r_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, 
 
     DeviceGuard g(ix->device);
     cudaStream_t st = ix->stream;
+    CU(cudaDeviceSynchronize());  // rows move in place: nothing may be reading or writing them
+    ix->data_ev_set = false;
     int64_t* adj_dev = nullptr;
     uint8_t* bounce = nullptr;
     const int64_t chunk_rows = std::max<int64_t>(1, (int64_t)((64u << 20) / ix->row_bytes));
@@ -687,6 +707,7 @@ extern "C" int b200r_reconstruct(b200r_index* ix, int64_t key, float* out) {
         return fail(B200R_E_INVALID, "b200r_reconstruct: key %lld out of range [0, %lld)", (long long)key,
                     (long long)ix->ntotal);
     DeviceGuard g(ix->device);
+    if (ix->data_ev_set) CU(cudaStreamWaitEvent(ix->stream, ix->data_ev, 0));
     float* tmp = nullptr;
     CU(cudaMalloc(&tmp, (size_t)ix->d * sizeof(float)));
     cudaError_t e = launch_row_to_f32(ix->rows + (size_t)key * ix->row_bytes, ix->d, ix->bf16, tmp, ix->stream);
@@ -708,6 +729,7 @@ extern "C" int b200r_reconstruct_batch(b200r_index* ix, const int64_t* keys, int
             return fail(B200R_E_INVALID, "b200r_reconstruct_batch: key %lld out of range [0, %lld)", (long long)keys[i],
                         (long long)ix->ntotal);
     DeviceGuard g(ix->device);
+    if (ix->data_ev_set) cudaStreamWaitEvent(ix->stream, ix->data_ev, 0);
     int64_t* kd = nullptr;
     float* od = nullptr;
     cudaError_t e = cudaMalloc(&kd, (size_t)n * sizeof(int64_t));
@@ -792,6 +814,7 @@ extern "C" int b200r_save(b200r_index* ix, const char* path) {
     if (!ix || !path) return fail(B200R_E_INVALID, "b200r_save: null argument");
     std::lock_guard<std::mutex> lk(ix->mu);
     DeviceGuard g(ix->device);
+    if (ix->data_ev_set) cudaStreamWaitEvent(ix->stream, ix->data_ev, 0);
     FILE* f = fopen(path, "wb");
     if (!f) return fail(B200R_E_IO, "b200r_save: cannot open %s", path);
     const uint32_t h = fourcc(ix->l2 ? "IxF2" : "IxFI");

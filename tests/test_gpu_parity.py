@@ -542,3 +542,24 @@ def test_reconstruct_batch_and_mmr_on_engine(built_lib):
     vs.add_embeddings([(f"t{i}", x[i].tolist()) for i in range(200)])
     docs = vs.max_marginal_relevance_search_by_vector(x[5].tolist(), k=4, fetch_k=20)
     assert docs[0].page_content == "t5" and len(docs) == 4 and len({d_.page_content for d_ in docs}) == 4
+
+
+def test_cross_stream_ordering(built_lib):
+    """add() with a CUDA tensor is asynchronous on the caller's stream; a host search right after
+    it runs on the index's own stream and must still see the rows (the library orders them)."""
+    import torch
+
+    d = 1024
+    n = 400_000
+    side = torch.cuda.Stream()
+    for _ in range(3):
+        ix = _mk("ip", d, reserve_rows=n)
+        with torch.cuda.stream(side):
+            x = torch.randn((n, d), device="cuda")
+            x /= x.norm(dim=1, keepdim=True)
+            ix.add(x)                                   # queued behind the generation kernels
+            q = x[n - 5: n - 4].cpu().numpy()           # (this D2H also runs on `side`)
+        D, I = ix.search(q, 1)                          # host path, the index's own stream
+        assert I[0, 0] == n - 5 and D[0, 0] > 0.999
+        np.testing.assert_array_equal(ix.reconstruct(n - 5), q[0])
+        ix.close()
