@@ -61,6 +61,28 @@ __device__ __forceinline__ void bulk_prefetch_l2(const void* gmem, uint32_t byte
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem), "r"(bytes) : "memory");
 }
 
+// multicast: the tile lands at the same CTA-relative offset in every CTA of `mask` and completes
+// bytes on the mbarrier at the same offset in each of them
+__device__ __forceinline__ void tma_load_2d_mc(void* dst_smem, const CUtensorMap* map, int c0, int c1, uint64_t* bar,
+                                               uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, "
+        "{%3, %4}], [%2], %5;" ::"r"(smem_u32(dst_smem)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+        : "memory");
+}
+
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ uint32_t cluster_cta_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }
@@ -83,6 +105,15 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                  : "memory");
+}
+
+// same, arriving on the barrier at this offset in every CTA of `mask`
+__device__ __forceinline__ void tc_commit_mc(uint64_t* bar, uint16_t mask) {
+    asm volatile(
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            smem_u32(bar)),
+        "h"(mask)
+        : "memory");
 }
 
 template <bool BF16>
@@ -173,7 +204,12 @@ __device__ __forceinline__ float better_of(float a, float b) {
     return SMALL ? fminf(a, b) : fmaxf(a, b);
 }
 
-template <bool BF16, int MT, int KP, bool L2>
+// CS = cluster size.  CS > 1: the CTAs of a cluster walk their (different) corpus tiles in lock
+// step, and every K block of the query operand -- identical for all of them -- is fetched ONCE per
+// cluster: CTA r loads rows [r*128/CS, (r+1)*128/CS) of each M tile and TMA-multicasts them into
+// all CS shared memories.  That removes (CS-1)/CS of the query re-reads from the L2->SM traffic,
+// which is what bounds the 256-query variants (operands at MMA rate need ~14 TB/s of it).
+template <bool BF16, int MT, int KP, bool L2, int CS>
 __global__ void __launch_bounds__(128 + 128 * MT, 1)
 gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                    const GemmParams p) {
@@ -202,7 +238,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; s++) {
             mbar_init(&full_bar[s], 1);
-            mbar_init(&empty_bar[s], 1);
+            mbar_init(&empty_bar[s], CS);  // one MMA commit from every CTA whose multicast fills this stage
         }
         for (int a = 0; a < ACC_STAGES; a++) {
             mbar_init(&tfull_bar[a], 1);
@@ -218,10 +254,16 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    const uint32_t cta_rank = CS > 1 ? cluster_cta_rank() : 0u;
+    constexpr uint16_t kClusterMask = (uint16_t)((1u << CS) - 1u);
+    if (CS > 1) cluster_sync_all();  // every CTA's barriers exist before any remote arrive / multicast
 
     const int64_t n_tiles = p.n_tiles;
-    // tiles of this CTA: blockIdx.x, +grid, ...; with warm-up the first one is visited once more at the end
-    const int64_t n_my = (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    // tiles of this CTA: blockIdx.x, +grid, ...; with warm-up the first one is visited once more at the
+    // end.  In a cluster every CTA runs the same number of iterations (tiles past the end are all
+    // out-of-bounds rows: TMA zero-fills them and the epilogue masks them).
+    const int64_t n_my = CS > 1 ? (n_tiles + gridDim.x - 1) / gridDim.x
+                                : (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
     const int64_t n_iter = n_my + (p.warmup ? 1 : 0);
     auto tile_of = [&](int64_t i) -> int64_t { return (int64_t)blockIdx.x + (i < n_my ? i : 0) * (int64_t)gridDim.x; };
 
@@ -262,9 +304,15 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                     else
                         tma_load_2d(st, &map_x, kb * kstep, row0, &full_bar[s]);
 #pragma unroll
-                    for (int mt = 0; mt < MT; mt++)
-                        tma_load_2d(st + kGemmBBytes + mt * kGemmABytes, &map_q, kb * kstep, mt * kGemmTileM,
-                                    &full_bar[s]);
+                    for (int mt = 0; mt < MT; mt++) {
+                        if (CS == 1)
+                            tma_load_2d(st + kGemmBBytes + mt * kGemmABytes, &map_q, kb * kstep, mt * kGemmTileM,
+                                        &full_bar[s]);
+                        else
+                            tma_load_2d_mc(st + kGemmBBytes + mt * kGemmABytes + cta_rank * (kGemmABytes / CS), &map_q,
+                                           kb * kstep, mt * kGemmTileM + (int)cta_rank * (kGemmTileM / CS), &full_bar[s],
+                                           kClusterMask);
+                    }
                     if (++s == STAGES) {
                         s = 0;
                         ph ^= 1;
@@ -302,7 +350,11 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                             umma<BF16>(td, da + adv, db + adv, idesc, (uint32_t)((kb | k4) != 0));
                         }
                     }
-                    tc_commit(&empty_bar[s]);  // frees the smem stage when these MMAs are done
+                    // frees the smem stage when these MMAs are done (in every CTA that multicasts into it)
+                    if (CS == 1)
+                        tc_commit(&empty_bar[s]);
+                    else
+                        tc_commit_mc(&empty_bar[s], kClusterMask);
                     if (kb == p.num_kb - 1) tc_commit(&tfull_bar[as]);
                     if (++s == STAGES) {
                         s = 0;
@@ -576,6 +628,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
 
     tc_fence_before();
     __syncthreads();
+    if (CS > 1) cluster_sync_all();  // no CTA leaves while a peer may still arrive on its barriers
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
@@ -988,24 +1041,42 @@ int gemm_kprime(int k) {
     return kp < cap ? kp : cap;
 }
 
-template <bool BF16, int MT, int KP, bool L2>
+template <bool BF16, int MT, int KP, bool L2, int CS>
 static cudaError_t launch_filter_one(const CUtensorMap& mq, const CUtensorMap& mx, const GemmParams& p, int grid,
                                      cudaStream_t st) {
     constexpr int STAGES = (MT == 1 ? 4 : 3) * (128 / kGemmKBytes);
     constexpr int STAGE_BYTES = kGemmBBytes + MT * kGemmABytes;
     const size_t smem = 1024 + (size_t)STAGES * STAGE_BYTES + 256 + (L2 ? (size_t)4 * MT * kGemmTileN * sizeof(float) : 0);
-    auto kern = gemm_filter_kernel<BF16, MT, KP, L2>;
+    auto kern = gemm_filter_kernel<BF16, MT, KP, L2, CS>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    kern<<<grid, 128 + 128 * MT, smem, st>>>(mq, mx, p);
-    return cudaGetLastError();
+    if (CS == 1) {
+        kern<<<grid, 128 + 128 * MT, smem, st>>>(mq, mx, p);
+        return cudaGetLastError();
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(128 + 128 * MT);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CS;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, mq, mx, p);
 }
 
 template <bool BF16, int MT, int KP>
-static cudaError_t launch_filter_l2(bool l2, const CUtensorMap& mq, const CUtensorMap& mx, const GemmParams& p, int grid,
-                                    cudaStream_t st) {
-    return l2 ? launch_filter_one<BF16, MT, KP, true>(mq, mx, p, grid, st)
-              : launch_filter_one<BF16, MT, KP, false>(mq, mx, p, grid, st);
+static cudaError_t launch_filter_l2(bool l2, int cs, const CUtensorMap& mq, const CUtensorMap& mx, const GemmParams& p,
+                                    int grid, cudaStream_t st) {
+    if (cs == 2)
+        return l2 ? launch_filter_one<BF16, MT, KP, true, 2>(mq, mx, p, grid, st)
+                  : launch_filter_one<BF16, MT, KP, false, 2>(mq, mx, p, grid, st);
+    return l2 ? launch_filter_one<BF16, MT, KP, true, 1>(mq, mx, p, grid, st)
+              : launch_filter_one<BF16, MT, KP, false, 1>(mq, mx, p, grid, st);
 }
 
 template <bool L2>
@@ -1033,8 +1104,12 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     const int MT = a.nq <= kGemmTileM ? 1 : 2;
     const int kp_cap = gemm_kp_cap(a.k);
     const int kprime = gemm_kprime(a.k);
+    const int64_t n_tiles_all = (a.n_rows + kGemmTileN - 1) / kGemmTileN;
+    int cs = 2;  // query-operand multicast over CTA pairs
+    if (const char* ev = getenv("B200R_GEMM_CLUSTER")) cs = atoi(ev) == 1 ? 1 : 2;
+    if (n_tiles_all < 2 || a.num_sms < 2) cs = 1;
     CUtensorMap mq, mx;
-    if (!make_map(&mq, a.q_mma, (int64_t)MT * kGemmTileM, a.d_pad, a.bf16, kGemmTileM)) return cudaErrorNotSupported;
+    if (!make_map(&mq, a.q_mma, (int64_t)MT * kGemmTileM, a.d_pad, a.bf16, kGemmTileM / cs)) return cudaErrorNotSupported;
     if (!make_map(&mx, a.corpus, a.n_rows, a.d_pad, a.bf16, kGemmTileN)) return cudaErrorNotSupported;
     GemmParams p{};
     p.n_rows = a.n_rows;
@@ -1062,6 +1137,9 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     p.evict_first = ((size_t)a.n_rows * a.d_pad * (a.bf16 ? 2 : 4) > ((size_t)96 << 20)) ? 1 : 0;
     int grid = (int)(p.n_tiles < a.num_sms ? p.n_tiles : a.num_sms);
     if (grid < 1) grid = 1;
+    grid -= grid % cs;
+    // TMA coordinates are 32-bit: rows (including the padded tail tiles of a cluster launch) must fit
+    if (a.n_rows + (int64_t)kGemmTileN * (grid + 1) >= (1ll << 31)) return cudaErrorNotSupported;
     {
         // warm-up pays one extra tile per CTA; worth it when the lists are large (memory heaps)
         // and every CTA has several tiles
@@ -1072,18 +1150,18 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     cudaError_t e;
     if (a.bf16) {
         if (MT == 1)
-            e = kp_cap == 32 ? launch_filter_l2<true, 1, 32>(a.l2, mq, mx, p, grid, st)
-                             : launch_filter_l2<true, 1, 256>(a.l2, mq, mx, p, grid, st);
+            e = kp_cap == 32 ? launch_filter_l2<true, 1, 32>(a.l2, cs, mq, mx, p, grid, st)
+                             : launch_filter_l2<true, 1, 256>(a.l2, cs, mq, mx, p, grid, st);
         else
-            e = kp_cap == 32 ? launch_filter_l2<true, 2, 32>(a.l2, mq, mx, p, grid, st)
-                             : launch_filter_l2<true, 2, 256>(a.l2, mq, mx, p, grid, st);
+            e = kp_cap == 32 ? launch_filter_l2<true, 2, 32>(a.l2, cs, mq, mx, p, grid, st)
+                             : launch_filter_l2<true, 2, 256>(a.l2, cs, mq, mx, p, grid, st);
     } else {
         if (MT == 1)
-            e = kp_cap == 32 ? launch_filter_l2<false, 1, 32>(a.l2, mq, mx, p, grid, st)
-                             : launch_filter_l2<false, 1, 256>(a.l2, mq, mx, p, grid, st);
+            e = kp_cap == 32 ? launch_filter_l2<false, 1, 32>(a.l2, cs, mq, mx, p, grid, st)
+                             : launch_filter_l2<false, 1, 256>(a.l2, cs, mq, mx, p, grid, st);
         else
-            e = kp_cap == 32 ? launch_filter_l2<false, 2, 32>(a.l2, mq, mx, p, grid, st)
-                             : launch_filter_l2<false, 2, 256>(a.l2, mq, mx, p, grid, st);
+            e = kp_cap == 32 ? launch_filter_l2<false, 2, 32>(a.l2, cs, mq, mx, p, grid, st)
+                             : launch_filter_l2<false, 2, 256>(a.l2, cs, mq, mx, p, grid, st);
     }
     if (e != cudaSuccess) return e;
 
