@@ -71,3 +71,59 @@ def test_c2_properties(built_lib):
     np.testing.assert_array_equal(Dm.cpu().numpy(), Dh)
     for i in (ix, half_a, half_b):
         i.close()
+
+
+def test_c3_full_size_both_paths(built_lib):
+    """BASELINE config C3 at its full single-GPU size (10M x 1024 fp32 = 41 GB): the scan path
+    (nq=4) and the tensor-core path (nq=32) against a float64 brute force computed chunk by chunk
+    on the device while the corpus is being ingested (checker only; nothing is kept but top-k)."""
+    import torch
+
+    from generativeaiexamples_b200 import B200IndexFlatIP, synth
+    from oracle import assert_topk_parity
+
+    free, _ = torch.cuda.mem_get_info()
+    if free < 60 * (1 << 30):
+        pytest.skip("needs ~50 GB of free HBM")
+    n, d, k, nq = 10_000_000, 1024, 10, 32
+    dev = torch.device("cuda", 0)
+    ix = B200IndexFlatIP(d, reserve_rows=n)
+    g = torch.Generator(device=dev)
+    g.manual_seed(99)
+    q = torch.randn((nq, d), generator=g, device=dev)
+    best_s = torch.empty((nq, 0), dtype=torch.float64, device=dev)
+    best_i = torch.empty((nq, 0), dtype=torch.int64, device=dev)
+    for c in range(n // synth.CHUNK_ROWS):
+        x = synth.corpus_chunk_device(c, synth.CHUNK_ROWS, d, dev)
+        if c == 3:
+            q[::2] = x[:nq // 2] + 0.1 * q[::2] / d ** 0.5   # plant neighbours at rows 3_000_000 ...
+            q /= q.norm(dim=1, keepdim=True)
+            # scores of the chunks already seen were computed with the old q: redo them
+            best_s = torch.empty((nq, 0), dtype=torch.float64, device=dev)
+            best_i = torch.empty((nq, 0), dtype=torch.int64, device=dev)
+            for c2 in range(c):
+                x2 = synth.corpus_chunk_device(c2, synth.CHUNK_ROWS, d, dev)
+                s2 = q.double() @ x2.double().T
+                ts, ti = torch.topk(torch.cat([best_s, s2], 1), k + 8, dim=1)
+                ids = torch.cat([best_i, torch.arange(c2 * synth.CHUNK_ROWS, (c2 + 1) * synth.CHUNK_ROWS,
+                                                      device=dev).expand(nq, -1)], 1)
+                best_s, best_i = ts, torch.gather(ids, 1, ti)
+                del x2, s2
+        ix.add(x)
+        s = q.double() @ x.double().T
+        ts, ti = torch.topk(torch.cat([best_s, s], 1), k + 8, dim=1)
+        ids = torch.cat([best_i, torch.arange(c * synth.CHUNK_ROWS, (c + 1) * synth.CHUNK_ROWS,
+                                              device=dev).expand(nq, -1)], 1)
+        best_s, best_i = ts, torch.gather(ids, 1, ti)
+        del x, s
+    torch.cuda.synchronize()
+    assert ix.ntotal == n
+    Dt, It = best_s.cpu().numpy(), best_i.cpu().numpy()
+    D4, I4 = ix.search(q[:4].contiguous(), k)
+    assert ix.stats()["last_path"] == 1
+    assert_topk_parity(D4.cpu().numpy(), I4.cpu().numpy(), Dt[:4], It[:4], what="C3 full size, scan path")
+    D32, I32 = ix.search(q, k)
+    assert ix.stats()["last_path"] == 2
+    assert_topk_parity(D32.cpu().numpy(), I32.cpu().numpy(), Dt, It, what="C3 full size, GEMM path")
+    assert (I32[::2, 0].cpu() == 3_000_000 + torch.arange(nq // 2)).all()
+    ix.close()
