@@ -72,6 +72,34 @@ __device__ __forceinline__ void tma_load_2d_mc(void* dst_smem, const CUtensorMap
         : "memory");
 }
 
+// 2-CTA (cta_group::2) TMA load: the bytes land in THIS CTA's shared memory, the transaction is
+// counted on the LEADER CTA's mbarrier (bit 24 of a shared address selects the odd CTA of a pair)
+__device__ __forceinline__ void tma_load_2d_pair(void* dst_smem, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, "
+        "%4}], [%2];" ::"r"(smem_u32(dst_smem)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+        : "memory");
+}
+
+__device__ __forceinline__ void tma_load_2d_pair_hint(void* dst_smem, const CUtensorMap* map, int c0, int c1,
+                                                      uint64_t* bar, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+        "[%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst_smem)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1), "l"(policy)
+        : "memory");
+}
+
+// arrive on the mbarrier at this offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t rank) {
+    asm volatile(
+        "{\n\t.reg .b32 rem;\n\tmapa.shared::cluster.u32 rem, %0, %1;\n\t"
+        "mbarrier.arrive.shared::cluster.b64 _, [rem];\n\t}" ::"r"(smem_u32(bar)),
+        "r"(rank)
+        : "memory");
+}
+
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -99,6 +127,47 @@ __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
 
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+                 "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
+// cta_group::2 commit: arrives (once the pair's MMAs are done) on the barrier at this offset in
+// every CTA of `mask`
+__device__ __forceinline__ void tc_commit_pair(uint64_t* bar, uint16_t mask) {
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            smem_u32(bar)),
+        "h"(mask)
+        : "memory");
+}
+
+// one M=256 MMA over a CTA pair: each CTA's tensor core computes its 128 rows of D from its own A
+// half and BOTH halves of B (N/2 rows in each CTA's shared memory)
+template <bool BF16>
+__device__ __forceinline__ void umma_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+    if (BF16) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+            "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+            : "memory");
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+            "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+            : "memory");
+    }
 }
 
 // mbarrier arrives once all tcgen05.mma issued so far by this thread have completed
@@ -209,13 +278,24 @@ __device__ __forceinline__ float better_of(float a, float b) {
 // cluster: CTA r loads rows [r*128/CS, (r+1)*128/CS) of each M tile and TMA-multicasts them into
 // all CS shared memories.  That removes (CS-1)/CS of the query re-reads from the L2->SM traffic,
 // which is what bounds the 256-query variants (operands at MMA rate need ~14 TB/s of it).
-template <bool BF16, int MT, int KP, bool L2, int CS>
+//
+// PAIR = 2-CTA MMA (cta_group::2, cluster of 2, MT must be 1, CS must be 1): 256 queries x 256 rows
+// per tile over a CTA PAIR.  CTA r stages queries [128r, 128r+128) and corpus rows [128r, 128r+128)
+// of the tile (32 KB per K block instead of 64 KB -> 6 stages), the leader CTA issues one M=256
+// tcgen05.mma.cta_group::2 per K step, and each CTA's TMEM receives its 128 queries x 256 rows --
+// 256 columns per accumulator stage, so the accumulator is DOUBLE-buffered and the ~4k-clock TMEM
+// drain of a tile overlaps the next tile's MMAs (with two M tiles in one CTA all 512 columns are one
+// stage and the tensor pipe waits for every drain).
+template <bool BF16, int MT, int KP, bool L2, int CS, bool PAIR>
 __global__ void __launch_bounds__(128 + 128 * MT, 1)
 gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x,
                    const GemmParams p) {
+    static_assert(!PAIR || (MT == 1 && CS == 1), "the 2-CTA mode has one M tile per CTA and no query multicast");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    constexpr int STAGES = (MT == 1 ? 4 : 3) * (128 / kGemmKBytes);
-    constexpr int STAGE_BYTES = kGemmBBytes + MT * kGemmABytes;
+    constexpr int B_ROWS = PAIR ? kGemmTileN / 2 : kGemmTileN;  // corpus rows this CTA stages per tile
+    constexpr int B_BYTES = B_ROWS * kGemmKBytes;
+    constexpr int STAGES = (PAIR ? 6 : (MT == 1 ? 4 : 3)) * (128 / kGemmKBytes);
+    constexpr int STAGE_BYTES = B_BYTES + MT * kGemmABytes;
     constexpr int ACC_STAGES = MT == 1 ? 2 : 1;      // 512 TMEM columns in total
     constexpr int ACC_COLS = MT * kGemmTileN;        // columns per accumulator stage
     constexpr int UMMA_K_BYTES = 32;                 // 8 tf32 / 16 bf16
@@ -242,30 +322,39 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         }
         for (int a = 0; a < ACC_STAGES; a++) {
             mbar_init(&tfull_bar[a], 1);
-            mbar_init(&tempty_bar[a], N_EPI_WARPS);
+            // PAIR: the leader's barrier collects the epilogue warps of both CTAs
+            mbar_init(&tempty_bar[a], PAIR ? 2 * N_EPI_WARPS : N_EPI_WARPS);
         }
         *s_done = 0;
         fence_mbar_init();
         prefetch_tmap(&map_q);
         prefetch_tmap(&map_x);
     }
-    if (warp == 2) tmem_alloc(tmem_slot, 512);
+    if (PAIR) cluster_sync_all();  // both CTAs of the pair are resident before the paired TMEM allocation
+    if (warp == 2) {
+        if (PAIR)
+            tmem_alloc_pair(tmem_slot, 512);
+        else
+            tmem_alloc(tmem_slot, 512);
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t cta_rank = CS > 1 ? cluster_cta_rank() : 0u;
+    const uint32_t cta_rank = (CS > 1 || PAIR) ? cluster_cta_rank() : 0u;
     constexpr uint16_t kClusterMask = (uint16_t)((1u << CS) - 1u);
-    if (CS > 1) cluster_sync_all();  // every CTA's barriers exist before any remote arrive / multicast
+    if (CS > 1 || PAIR) cluster_sync_all();  // every CTA's barriers exist before any remote arrive / multicast
 
     const int64_t n_tiles = p.n_tiles;
     // tiles of this CTA: blockIdx.x, +grid, ...; with warm-up the first one is visited once more at the
     // end.  In a cluster every CTA runs the same number of iterations (tiles past the end are all
     // out-of-bounds rows: TMA zero-fills them and the epilogue masks them).
-    const int64_t n_my = CS > 1 ? (n_tiles + gridDim.x - 1) / gridDim.x
-                                : (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+    // work unit: a CTA, or a CTA pair in 2-CTA mode (tiles are dealt to pairs)
+    const int64_t unit = PAIR ? (int64_t)(blockIdx.x >> 1) : (int64_t)blockIdx.x;
+    const int64_t n_units = PAIR ? (int64_t)(gridDim.x >> 1) : (int64_t)gridDim.x;
+    const int64_t n_my = (CS > 1 || PAIR) ? (n_tiles + n_units - 1) / n_units : (n_tiles - unit + n_units - 1) / n_units;
     const int64_t n_iter = n_my + (p.warmup ? 1 : 0);
-    auto tile_of = [&](int64_t i) -> int64_t { return (int64_t)blockIdx.x + (i < n_my ? i : 0) * (int64_t)gridDim.x; };
+    auto tile_of = [&](int64_t i) -> int64_t { return unit + (i < n_my ? i : 0) * n_units; };
 
     if (warp == 0) {
         // ---------------- TMA producer ----------------
@@ -290,14 +379,29 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                     bulk_prefetch_l2(base + o, (uint32_t)len);
                 }
             };
-            for (int pf = 0; pf < p.prefetch_tiles; pf++) prefetch_tile((int64_t)blockIdx.x + (int64_t)pf * gridDim.x);
+            for (int pf = 0; pf < p.prefetch_tiles; pf++) prefetch_tile(unit + (int64_t)pf * n_units);
             for (int64_t i = 0; i < n_iter; i++) {
                 const int64_t t = tile_of(i);
                 const int row0 = (int)(t * kGemmTileN);
-                if (p.prefetch_tiles > 0) prefetch_tile(t + (int64_t)p.prefetch_tiles * gridDim.x);
+                if (p.prefetch_tiles > 0) prefetch_tile(t + (int64_t)p.prefetch_tiles * n_units);
                 for (int kb = 0; kb < p.num_kb; kb++) {
                     mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t* st = stages + (size_t)s * STAGE_BYTES;
+                    if (PAIR) {
+                        // both CTAs' loads are counted on the leader's barrier
+                        if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+                        const int xr = row0 + (int)cta_rank * B_ROWS;
+                        if (p.evict_first)
+                            tma_load_2d_pair_hint(st, &map_x, kb * kstep, xr, &full_bar[s], pol);
+                        else
+                            tma_load_2d_pair(st, &map_x, kb * kstep, xr, &full_bar[s]);
+                        tma_load_2d_pair(st + B_BYTES, &map_q, kb * kstep, (int)cta_rank * kGemmTileM, &full_bar[s]);
+                        if (++s == STAGES) {
+                            s = 0;
+                            ph ^= 1;
+                        }
+                        continue;
+                    }
                     mbar_arrive_expect_tx(&full_bar[s], STAGE_BYTES);
                     if (p.evict_first)
                         tma_load_2d_hint(st, &map_x, kb * kstep, row0, &full_bar[s], pol);
@@ -306,10 +410,10 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
 #pragma unroll
                     for (int mt = 0; mt < MT; mt++) {
                         if (CS == 1)
-                            tma_load_2d(st + kGemmBBytes + mt * kGemmABytes, &map_q, kb * kstep, mt * kGemmTileM,
+                            tma_load_2d(st + B_BYTES + mt * kGemmABytes, &map_q, kb * kstep, mt * kGemmTileM,
                                         &full_bar[s]);
                         else
-                            tma_load_2d_mc(st + kGemmBBytes + mt * kGemmABytes + cta_rank * (kGemmABytes / CS), &map_q,
+                            tma_load_2d_mc(st + B_BYTES + mt * kGemmABytes + cta_rank * (kGemmABytes / CS), &map_q,
                                            kb * kstep, mt * kGemmTileM + (int)cta_rank * (kGemmTileM / CS), &full_bar[s],
                                            kClusterMask);
                     }
@@ -322,12 +426,12 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ---------------- MMA issuer ----------------
-        if (lane == 0) {
+        // ---------------- MMA issuer (in 2-CTA mode: the leader CTA's, for the pair) ----------------
+        if (lane == 0 && (!PAIR || cta_rank == 0)) {
             // idesc: D=f32 (1<<4) | A,B format (tf32=2 / bf16=1) | K-major both | N>>3 | M>>4
             const uint32_t fmt = BF16 ? 1u : 2u;
             const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(kGemmTileN >> 3) << 17) |
-                                   ((uint32_t)(kGemmTileM >> 4) << 24);
+                                   ((uint32_t)((PAIR ? 2 * kGemmTileM : kGemmTileM) >> 4) << 24);
             int s = 0;
             uint32_t ph = 0;
             for (int64_t it = 0; it < n_iter; ++it) {
@@ -342,20 +446,30 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                     const uint64_t db = make_kmajor_sw128_desc(st);
 #pragma unroll
                     for (int mt = 0; mt < MT; mt++) {
-                        const uint64_t da = make_kmajor_sw128_desc(st + kGemmBBytes + mt * kGemmABytes);
+                        const uint64_t da = make_kmajor_sw128_desc(st + B_BYTES + mt * kGemmABytes);
                         const uint32_t td = tmem_base + (uint32_t)(as * ACC_COLS + mt * kGemmTileN);
 #pragma unroll
                         for (int k4 = 0; k4 < kGemmKBytes / UMMA_K_BYTES; k4++) {
                             const uint64_t adv = (uint64_t)((k4 * UMMA_K_BYTES) >> 4);
-                            umma<BF16>(td, da + adv, db + adv, idesc, (uint32_t)((kb | k4) != 0));
+                            if (PAIR)
+                                umma_pair<BF16>(td, da + adv, db + adv, idesc, (uint32_t)((kb | k4) != 0));
+                            else
+                                umma<BF16>(td, da + adv, db + adv, idesc, (uint32_t)((kb | k4) != 0));
                         }
                     }
-                    // frees the smem stage when these MMAs are done (in every CTA that multicasts into it)
-                    if (CS == 1)
+                    // frees the smem stage when these MMAs are done (in every CTA that fills / reads it)
+                    if (PAIR)
+                        tc_commit_pair(&empty_bar[s], 0x3);
+                    else if (CS == 1)
                         tc_commit(&empty_bar[s]);
                     else
                         tc_commit_mc(&empty_bar[s], kClusterMask);
-                    if (kb == p.num_kb - 1) tc_commit(&tfull_bar[as]);
+                    if (kb == p.num_kb - 1) {
+                        if (PAIR)
+                            tc_commit_pair(&tfull_bar[as], 0x3);  // both CTAs drain their half of D
+                        else
+                            tc_commit(&tfull_bar[as]);
+                    }
                     if (++s == STAGES) {
                         s = 0;
                         ph ^= 1;
@@ -435,7 +549,9 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         const int ew = warp - 4;
         const int mt = ew >> 2;
         const int quad = warp & 3;  // TMEM lane quadrant this warp may read
-        const int qidx = mt * kGemmTileM + quad * 32 + lane;
+        // query of this thread inside the launch's block of queries; Q_STRIDE = queries per work unit
+        constexpr int Q_STRIDE = PAIR ? 2 * kGemmTileM : kGemmTileM * MT;
+        const int qidx = (PAIR ? (int)cta_rank * kGemmTileM : mt * kGemmTileM) + quad * 32 + lane;
         const bool active = qidx < p.nq;
         // KP == 32 (k <= 10): sorted list held entirely in registers -- no memory traffic on insert
         // (the L1 left over beside ~200 KB of pipeline smem is too small for local-memory lists).
@@ -449,7 +565,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         uint32_t li[NREG];
         const int kp = p.kprime;
         int count = 0;
-        Cand* my_list = p.cand + ((size_t)blockIdx.x * (kGemmTileM * MT) + (qidx < kGemmTileM * MT ? qidx : 0)) * KP;
+        Cand* my_list = p.cand + ((size_t)unit * Q_STRIDE + qidx) * KP;
         if (KP == 32) {
 #pragma unroll
             for (int j = 0; j < KP; j++) {
@@ -474,7 +590,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             // Any CTA's full-list worst is a lower bound of the final K'-th best, so filtering with
             // the best such bound published by any CTA never drops a row of the global top-K'.
             float g = worst_val<L2>();
-            if (active) g = dec_ordered(*reinterpret_cast<volatile int*>(gthr));
+            int g_pend = active ? *reinterpret_cast<volatile int*>(gthr) : 0;  // consumed one step later
             if (L2) {
                 // stage ||x||^2 of the tile's rows; rows past the end never win
                 __syncwarp();
@@ -485,7 +601,6 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                 }
                 __syncwarp();
             }
-            thr = better_of<L2>(lthr, g);
             mbar_wait(&tfull_bar[as], aph);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * ACC_COLS + mt * kGemmTileN);
@@ -494,8 +609,10 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             for (int c = 0; c < kGemmTileN / 32; c++) {
                 uint32_t r[32];
                 if (p.debug_no_select == 2) continue;
-                int g_enc = 0;
-                if (active) g_enc = *reinterpret_cast<volatile int*>(gthr);  // in flight during the TMEM load
+                // the grid-wide threshold is re-read every chunk, but the value is only used one chunk
+                // later, so its L2 round trip (~700 clk) never stalls the accumulator drain
+                const int g_enc = g_pend;
+                if (active) g_pend = *reinterpret_cast<volatile int*>(gthr);
                 tmem_ld32(taddr + c * 32, r);
                 if (active) {
                     g = better_of<L2>(g, dec_ordered(g_enc));
@@ -585,7 +702,12 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[as]);
+            if (lane == 0) {
+                if (PAIR && cta_rank != 0)
+                    mbar_arrive_remote(&tempty_bar[as], 0);  // the leader's MMA issuer owns the accumulator hand-off
+                else
+                    mbar_arrive(&tempty_bar[as]);
+            }
             if (hist_only && active) {
                 // give the refresher warps (any CTA's) a moment to turn the first counts into a
                 // threshold; bounded wait, the result is correct with or without it
@@ -605,7 +727,7 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
         if (lane == 0) atomicAdd(const_cast<int*>(s_done), 1);
         // survivors -> global, [cta][query][KP] (unsorted; unused slots empty)
         if (active) {
-            Cand* dst = p.cand + ((size_t)blockIdx.x * (kGemmTileM * MT) + qidx) * KP;
+            Cand* dst = p.cand + ((size_t)unit * Q_STRIDE + qidx) * KP;
             if (KP == 32) {
                 int nv = 0;
 #pragma unroll
@@ -618,9 +740,9 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                         nv++;
                     }
                 }
-                p.list_counts[(size_t)blockIdx.x * (kGemmTileM * MT) + qidx] = nv;
+                p.list_counts[(size_t)unit * Q_STRIDE + qidx] = nv;
             } else {
-                p.list_counts[(size_t)blockIdx.x * (kGemmTileM * MT) + qidx] = count < KP ? count : KP;
+                p.list_counts[(size_t)unit * Q_STRIDE + qidx] = count < KP ? count : KP;
                 if (count > KP) p.overflow[qidx] = 1;
             }
         }
@@ -628,10 +750,13 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
 
     tc_fence_before();
     __syncthreads();
-    if (CS > 1) cluster_sync_all();  // no CTA leaves while a peer may still arrive on its barriers
+    if (CS > 1 || PAIR) cluster_sync_all();  // no CTA leaves while a peer may still arrive on its barriers
     if (warp == 2) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 512);
+        if (PAIR)
+            tmem_dealloc_pair(tmem_base, 512);
+        else
+            tmem_dealloc(tmem_base, 512);
     }
 }
 
@@ -1041,16 +1166,16 @@ int gemm_kprime(int k) {
     return kp < cap ? kp : cap;
 }
 
-template <bool BF16, int MT, int KP, bool L2, int CS>
+template <bool BF16, int MT, int KP, bool L2, int CS, bool PAIR = false>
 static cudaError_t launch_filter_one(const CUtensorMap& mq, const CUtensorMap& mx, const GemmParams& p, int grid,
                                      cudaStream_t st) {
-    constexpr int STAGES = (MT == 1 ? 4 : 3) * (128 / kGemmKBytes);
-    constexpr int STAGE_BYTES = kGemmBBytes + MT * kGemmABytes;
+    constexpr int STAGES = (PAIR ? 6 : (MT == 1 ? 4 : 3)) * (128 / kGemmKBytes);
+    constexpr int STAGE_BYTES = (PAIR ? kGemmBBytes / 2 : kGemmBBytes) + MT * kGemmABytes;
     const size_t smem = 1024 + (size_t)STAGES * STAGE_BYTES + 256 + (L2 ? (size_t)4 * MT * kGemmTileN * sizeof(float) : 0);
-    auto kern = gemm_filter_kernel<BF16, MT, KP, L2, CS>;
+    auto kern = gemm_filter_kernel<BF16, MT, KP, L2, CS, PAIR>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    if (CS == 1) {
+    if (CS == 1 && !PAIR) {
         kern<<<grid, 128 + 128 * MT, smem, st>>>(mq, mx, p);
         return cudaGetLastError();
     }
@@ -1061,7 +1186,7 @@ static cudaError_t launch_filter_one(const CUtensorMap& mq, const CUtensorMap& m
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CS;
+    attr[0].val.clusterDim.x = PAIR ? 2 : CS;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
@@ -1069,9 +1194,15 @@ static cudaError_t launch_filter_one(const CUtensorMap& mq, const CUtensorMap& m
     return cudaLaunchKernelEx(&cfg, kern, mq, mx, p);
 }
 
+// mode: 1 = plain CTAs, 2 = CTA pairs with query multicast, 3 = 2-CTA MMA (MT must be 1)
 template <bool BF16, int MT, int KP>
 static cudaError_t launch_filter_l2(bool l2, int cs, const CUtensorMap& mq, const CUtensorMap& mx, const GemmParams& p,
                                     int grid, cudaStream_t st) {
+    if constexpr (MT == 1) {
+        if (cs == 3)
+            return l2 ? launch_filter_one<BF16, 1, KP, true, 1, true>(mq, mx, p, grid, st)
+                      : launch_filter_one<BF16, 1, KP, false, 1, true>(mq, mx, p, grid, st);
+    }
     if (cs == 2)
         return l2 ? launch_filter_one<BF16, MT, KP, true, 2>(mq, mx, p, grid, st)
                   : launch_filter_one<BF16, MT, KP, false, 2>(mq, mx, p, grid, st);
@@ -1108,9 +1239,14 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     int cs = 2;  // query-operand multicast over CTA pairs
     if (const char* ev = getenv("B200R_GEMM_CLUSTER")) cs = atoi(ev) == 1 ? 1 : 2;
     if (n_tiles_all < 2 || a.num_sms < 2) cs = 1;
+    // more than 128 queries: 2-CTA MMA over CTA pairs (double-buffered accumulators) unless turned off
+    bool pair = MT == 2 && cs == 2;
+    if (const char* ev = getenv("B200R_GEMM_PAIR")) pair = pair && atoi(ev) != 0;
+    if (pair) cs = 3;
     CUtensorMap mq, mx;
-    if (!make_map(&mq, a.q_mma, (int64_t)MT * kGemmTileM, a.d_pad, a.bf16, kGemmTileM / cs)) return cudaErrorNotSupported;
-    if (!make_map(&mx, a.corpus, a.n_rows, a.d_pad, a.bf16, kGemmTileN)) return cudaErrorNotSupported;
+    if (!make_map(&mq, a.q_mma, (int64_t)MT * kGemmTileM, a.d_pad, a.bf16, pair ? kGemmTileM : kGemmTileM / cs))
+        return cudaErrorNotSupported;
+    if (!make_map(&mx, a.corpus, a.n_rows, a.d_pad, a.bf16, pair ? kGemmTileN / 2 : kGemmTileN)) return cudaErrorNotSupported;
     GemmParams p{};
     p.n_rows = a.n_rows;
     p.nq = a.nq;
@@ -1137,7 +1273,8 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     p.evict_first = ((size_t)a.n_rows * a.d_pad * (a.bf16 ? 2 : 4) > ((size_t)96 << 20)) ? 1 : 0;
     int grid = (int)(p.n_tiles < a.num_sms ? p.n_tiles : a.num_sms);
     if (grid < 1) grid = 1;
-    grid -= grid % cs;
+    if (pair && grid < 2) grid = 2;
+    grid -= grid % (pair ? 2 : cs);
     // TMA coordinates are 32-bit: rows (including the padded tail tiles of a cluster launch) must fit
     if (a.n_rows + (int64_t)kGemmTileN * (grid + 1) >= (1ll << 31)) return cudaErrorNotSupported;
     {
@@ -1152,6 +1289,9 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
         if (MT == 1)
             e = kp_cap == 32 ? launch_filter_l2<true, 1, 32>(a.l2, cs, mq, mx, p, grid, st)
                              : launch_filter_l2<true, 1, 256>(a.l2, cs, mq, mx, p, grid, st);
+        else if (pair)
+            e = kp_cap == 32 ? launch_filter_l2<true, 1, 32>(a.l2, 3, mq, mx, p, grid, st)
+                             : launch_filter_l2<true, 1, 256>(a.l2, 3, mq, mx, p, grid, st);
         else
             e = kp_cap == 32 ? launch_filter_l2<true, 2, 32>(a.l2, cs, mq, mx, p, grid, st)
                              : launch_filter_l2<true, 2, 256>(a.l2, cs, mq, mx, p, grid, st);
@@ -1159,6 +1299,9 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
         if (MT == 1)
             e = kp_cap == 32 ? launch_filter_l2<false, 1, 32>(a.l2, cs, mq, mx, p, grid, st)
                              : launch_filter_l2<false, 1, 256>(a.l2, cs, mq, mx, p, grid, st);
+        else if (pair)
+            e = kp_cap == 32 ? launch_filter_l2<false, 1, 32>(a.l2, 3, mq, mx, p, grid, st)
+                             : launch_filter_l2<false, 1, 256>(a.l2, 3, mq, mx, p, grid, st);
         else
             e = kp_cap == 32 ? launch_filter_l2<false, 2, 32>(a.l2, cs, mq, mx, p, grid, st)
                              : launch_filter_l2<false, 2, 256>(a.l2, cs, mq, mx, p, grid, st);
@@ -1175,7 +1318,7 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     rp.list_counts = a.list_counts;
     rp.overflow = a.overflow;
     rp.qscale = a.qscale;
-    rp.grid = grid;
+    rp.grid = pair ? grid / 2 : grid;  // survivor lists per query: one per work unit (CTA or CTA pair)
     rp.q_stride = MT * kGemmTileM;
     rp.kp_stride = kp_cap;
     rp.kprime = kprime;
