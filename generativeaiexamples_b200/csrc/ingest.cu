@@ -27,6 +27,64 @@ __global__ void __launch_bounds__(kRowWarps * 32) ingest_kernel(const float* src
     const int64_t warps_total = (int64_t)gridDim.x * kRowWarps;
     for (int64_t row = (int64_t)blockIdx.x * kRowWarps + (threadIdx.x >> 5); row < n; row += warps_total) {
         const float* s = src + row * d_in;
+        if (VEC && d_pad <= 32 * 8 * 4) {
+            // rows of up to 1024 floats: the whole row lives in registers (8 x 128-bit per lane), so
+            // normalising costs no second read and all eight loads are in flight at once
+            const float4* s4 = reinterpret_cast<const float4*>(s);
+            const int n4_in = d_in >> 2, n4_pad = d_pad >> 2;
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int i = u * 32 + lane;
+                v[u] = i < n4_in ? s4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            float sc = 1.f;
+            if (normalize) {
+                float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    a0 = fmaf(v[u].x, v[u].x, a0);
+                    a1 = fmaf(v[u].y, v[u].y, a1);
+                    a2 = fmaf(v[u].z, v[u].z, a2);
+                    a3 = fmaf(v[u].w, v[u].w, a3);
+                }
+                const float nr = warp_sum((a0 + a2) + (a1 + a3));
+                if (nr > 0.f) sc = 1.0f / sqrtf(nr);
+            }
+            float c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int i = u * 32 + lane;
+                float4 w = v[u];
+                w.x *= sc;
+                w.y *= sc;
+                w.z *= sc;
+                w.w *= sc;
+                if (TO_BF16) {
+                    const __nv_bfloat162 lo = __floats2bfloat162_rn(w.x, w.y);
+                    const __nv_bfloat162 hi = __floats2bfloat162_rn(w.z, w.w);
+                    w.x = __low2float(lo);
+                    w.y = __high2float(lo);
+                    w.z = __low2float(hi);
+                    w.w = __high2float(hi);
+                    if (i < n4_pad) {
+                        uint2 pk;
+                        pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+                        pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+                        reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(dst) + row * d_pad)[i] = pk;
+                    }
+                } else if (i < n4_pad) {
+                    reinterpret_cast<float4*>(reinterpret_cast<float*>(dst) + row * d_pad)[i] = w;
+                }
+                c0 = fmaf(w.x, w.x, c0);
+                c1 = fmaf(w.y, w.y, c1);
+                c2 = fmaf(w.z, w.z, c2);
+                c3 = fmaf(w.w, w.w, c3);
+            }
+            const float nn1 = warp_sum((c0 + c2) + (c1 + c3));
+            if (lane == 0 && norms) norms[row] = nn1;
+            continue;
+        }
         float scale = 1.f;
         if (normalize) {
             float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
