@@ -12,6 +12,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace b200r;
@@ -111,6 +112,27 @@ struct b200r_index {
 };
 
 static int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+// pageable -> pinned staging copy; one core moves ~12 GB/s, PCIe Gen5 takes ~50, so large
+// copies are split over a few threads
+static void staged_memcpy(void* dst, const void* src, size_t bytes) {
+    constexpr size_t kMinPerThread = 4u << 20;
+    unsigned hw = std::thread::hardware_concurrency();
+    int nt = (int)std::min<size_t>(std::min<unsigned>(hw ? hw : 1, 4), bytes / kMinPerThread);
+    if (nt <= 1) {
+        memcpy(dst, src, bytes);
+        return;
+    }
+    std::vector<std::thread> th;
+    const size_t per = (bytes / nt + 4095) & ~(size_t)4095;
+    for (int t = 1; t < nt; t++) {
+        const size_t lo = std::min(bytes, per * t), hi = std::min(bytes, per * (t + 1));
+        if (hi > lo)
+            th.emplace_back([=] { memcpy((uint8_t*)dst + lo, (const uint8_t*)src + lo, hi - lo); });
+    }
+    memcpy(dst, src, std::min(bytes, per));
+    for (auto& t : th) t.join();
+}
 
 static int ensure_capacity(b200r_index* ix, int64_t need, cudaStream_t st) {
     if (need <= ix->capacity) return B200R_OK;
@@ -335,7 +357,7 @@ extern "C" int b200r_add(b200r_index* ix, const void* x, int64_t n, int dtype, i
             if (used[half]) CU(cudaEventSynchronize(ix->add_ev[half]));
             uint8_t* ph = ix->pin_add + half * kStageHalfBytes;
             uint8_t* dh = ix->dev_add + half * kStageHalfBytes;
-            memcpy(ph, (const uint8_t*)x + (size_t)r0 * in_row, (size_t)m * in_row);
+            staged_memcpy(ph, (const uint8_t*)x + (size_t)r0 * in_row, (size_t)m * in_row);
             CU(cudaMemcpyAsync(dh, ph, (size_t)m * in_row, cudaMemcpyHostToDevice, st));
             CU(launch_ingest((const float*)dh, m, ix->d, ix->d_pad, norm, ix->bf16, dst + (size_t)r0 * ix->row_bytes,
                              dstn + r0, st));
