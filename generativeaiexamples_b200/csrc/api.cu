@@ -568,7 +568,8 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     p.counter = ix->counter;
     p.id_base = ix->cfg.id_base;
     // one query per launch after a GEMM pass (only the flagged ones) and for k > 128 (wide lists)
-    const int scan_step = (use_gemm || k > kScanMaxK) ? 1 : kScanMaxNQ;
+    // ... and for rows so wide that four queries do not fit in shared memory beside the stages
+    const int scan_step = (use_gemm || k > kScanMaxK) ? 1 : scan_queries_per_launch(ix->d_pad, ix->row_bytes, ix->smem_optin);
     for (int64_t q0 = 0; q0 < nq; q0 += scan_step) {
         if (use_gemm && !ix->fail_pin[q0]) continue;  // only the queries whose check failed
         const int nqg = (int)std::min<int64_t>(scan_step, nq - q0);

@@ -50,6 +50,7 @@ cudaError_t launch_merge_wait(bool l2, uint8_t* my_buf, int world, int nq, int k
                               int64_t* out_i, cudaStream_t st);
 
 size_t scan_scratch_bytes(int max_grid);
+int scan_queries_per_launch(int d_pad, int row_bytes, size_t smem_limit);
 cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st,
                         int* grid_out);
 

@@ -319,6 +319,14 @@ size_t scan_scratch_bytes(int max_grid) {
 }
 
 // Fills in the tiling fields of `p` and launches.  p.q must hold nq_slots(nq) rows.
+// how many queries one launch can serve for rows this wide: the 4-query variants keep 4 x d floats
+// of queries in shared memory beside at least two stages
+int scan_queries_per_launch(int d_pad, int row_bytes, size_t smem_limit) {
+    const size_t stage = row_bytes > 64 * 1024 ? (size_t)(row_bytes + 127) / 128 * 128 : (size_t)64 * 1024;
+    const size_t fixed = 1024 + 2 * 16 * sizeof(uint64_t) + 2 * stage;
+    return (fixed + (size_t)kScanMaxNQ * d_pad * sizeof(float) <= smem_limit) ? kScanMaxNQ : 1;
+}
+
 cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st,
                         int* grid_out) {
     const int NQ = nq <= 1 ? 1 : 4;

@@ -88,10 +88,10 @@ def test_golden_fixtures(built_lib, gold):
 
 
 @pytest.mark.parametrize("metric", ["ip", "l2"])
-@pytest.mark.parametrize("d", [1024, 384, 100, 4, 2048])
+@pytest.mark.parametrize("d", [1024, 384, 100, 4, 2048, 8192])
 def test_scan_parity_dims(built_lib, metric, d):
     rng = np.random.default_rng(d)
-    n = 30011 if d <= 1024 else 9001  # ragged: not a multiple of the tile height
+    n = 30011 if d <= 1024 else (9001 if d <= 2048 else 2003)  # ragged: not a multiple of the tile height
     x = rng.standard_normal((n, d), dtype=np.float32)
     q = rng.standard_normal((6, d), dtype=np.float32)
     q[::2] = x[rng.integers(0, n, 3)] + 0.05 * q[::2]
