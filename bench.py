@@ -343,7 +343,7 @@ def main_gpu(args):
         def b256_step(i):
             results["b256"] = index.search(Q256, TOPK)
 
-        ms256, _ = timed(b256_step, args.batch256_steps, 1)
+        ms256, _ = timed(b256_step, args.batch256_steps, 3)
         per = ms256 / args.batch256_steps
         flops = 2.0 * 256 * n_total * DIM
         tf32_peak, _, tf32_src = _tensor_peaks()
@@ -427,7 +427,7 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=N_TOTAL, help="total corpus rows (default: the 10M headline config)")
-    ap.add_argument("--batch256-steps", type=int, default=10)
+    ap.add_argument("--batch256-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--concurrent", type=int, default=64, help="callers for the coalesced service-view number (0 = skip)")
     a = ap.parse_args()
