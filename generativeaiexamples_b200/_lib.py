@@ -23,7 +23,7 @@ class Config(ctypes.Structure):
     _fields_ = [
         ("dim", ctypes.c_int32), ("metric", ctypes.c_int32), ("storage", ctypes.c_int32),
         ("normalize_on_add", ctypes.c_int32), ("normalize_queries", ctypes.c_int32),
-        ("device", ctypes.c_int32), ("search_path", ctypes.c_int32), ("reserved0", ctypes.c_int32),
+        ("device", ctypes.c_int32), ("search_path", ctypes.c_int32), ("shadow_bf16", ctypes.c_int32),
         ("reserve_rows", ctypes.c_int64), ("id_base", ctypes.c_int64),
     ]
 
@@ -63,6 +63,7 @@ SIGNATURES = {
                                      _vp]),
     "b200r_set_id_base": (_int, [_vp, _i64]),
     "b200r_stats_get": (_int, [_vp, ctypes.POINTER(Stats)]),
+    "b200r_set_shadow_filter": (_int, [_vp, _i32]),
     "b200r_set_timing": (_int, [_vp, _i32]),
     "b200r_last_error": (ctypes.c_char_p, []),
     "b200r_version": (_int, []),

@@ -71,6 +71,10 @@ struct b200r_index {
 
     uint8_t* rows = nullptr;  // [capacity][row_bytes]
     float* norms = nullptr;   // [capacity] squared norms of the stored rows
+    // optional (cfg.shadow_bf16, fp32 storage): the same rows rounded to bf16, [capacity][d_pad];
+    // batches on the GEMM path filter on it (half the bytes, bf16 MMA rate) and re-score on `rows`
+    uint8_t* shadow = nullptr;
+    bool shadow_on = false;   // b200r_set_shadow_filter
     int64_t ntotal = 0, capacity = 0;
 
     cudaStream_t stream = nullptr;  // the index's own stream
@@ -106,6 +110,13 @@ struct b200r_index {
     int* fail_dev = nullptr;       // [fail_cap] flags + 1 counter at the end
     int* fail_pin = nullptr;
     int64_t fail_cap = 0;
+    // K' multiplier in percent: raised after a search whose containment check failed for some
+    // query (corpus with many near-ties), so the next batches filter with more slack
+    int kp_boost = 100;
+    // scan-path fallback of flagged queries, four per corpus pass: gathered queries / their results
+    float* fb_q = nullptr;
+    float* fb_d = nullptr;
+    int64_t* fb_i = nullptr;
 
     std::mutex mu;
     b200r_stats st{};
@@ -158,6 +169,19 @@ static int ensure_capacity(b200r_index* ix, int64_t need, cudaStream_t st) {
         cudaFree(nr);
         return fail(B200R_E_NOMEM, "cudaMalloc of row norms failed: %s", cudaGetErrorString(e));
     }
+    uint8_t* ns = nullptr;
+    if (ix->cfg.shadow_bf16) {
+        e = cudaMalloc(&ns, (size_t)cap * ix->d_pad * 2);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            cudaFree(nr);
+            cudaFree(nn);
+            return fail(B200R_E_NOMEM, "cudaMalloc of %.2f GB for the bf16 shadow failed: %s",
+                        cap * (double)ix->d_pad * 2 / 1e9, cudaGetErrorString(e));
+        }
+        if (ix->ntotal > 0)
+            CU(cudaMemcpyAsync(ns, ix->shadow, (size_t)ix->ntotal * ix->d_pad * 2, cudaMemcpyDeviceToDevice, st));
+    }
     if (ix->ntotal > 0) {
         CU(cudaMemcpyAsync(nr, ix->rows, (size_t)ix->ntotal * ix->row_bytes, cudaMemcpyDeviceToDevice, st));
         CU(cudaMemcpyAsync(nn, ix->norms, (size_t)ix->ntotal * sizeof(float), cudaMemcpyDeviceToDevice, st));
@@ -167,8 +191,10 @@ static int ensure_capacity(b200r_index* ix, int64_t need, cudaStream_t st) {
     if (ix->rows) CU(cudaDeviceSynchronize());
     if (ix->rows) cudaFree(ix->rows);
     if (ix->norms) cudaFree(ix->norms);
+    if (ix->shadow) cudaFree(ix->shadow);
     ix->rows = nr;
     ix->norms = nn;
+    ix->shadow = ns;
     ix->capacity = cap;
     return B200R_OK;
 }
@@ -179,6 +205,7 @@ static void free_index(b200r_index* ix) {
     if (ix->stream) cudaStreamSynchronize(ix->stream);
     cudaFree(ix->rows);
     cudaFree(ix->norms);
+    cudaFree(ix->shadow);
     cudaFreeHost(ix->pin_add);
     cudaFree(ix->dev_add);
     cudaFreeHost(ix->q_pin);
@@ -195,6 +222,9 @@ static void free_index(b200r_index* ix) {
     cudaFree(ix->gemm_aux);
     cudaFree(ix->fail_dev);
     cudaFreeHost(ix->fail_pin);
+    cudaFree(ix->fb_q);
+    cudaFree(ix->fb_d);
+    cudaFree(ix->fb_i);
     for (auto& e : ix->add_ev)
         if (e) cudaEventDestroy(e);
     if (ix->data_ev) cudaEventDestroy(ix->data_ev);
@@ -238,7 +268,13 @@ extern "C" int b200r_create(const b200r_config* cfg, b200r_index** out) {
     ix->d = cfg->dim;
     ix->bf16 = cfg->storage == B200R_BF16;
     ix->l2 = cfg->metric == B200R_METRIC_L2;
-    ix->d_pad = (int)round_up(cfg->dim, ix->bf16 ? 8 : 4);
+    if (cfg->shadow_bf16 && ix->bf16) {
+        delete ix;
+        return fail(B200R_E_INVALID, "shadow_bf16 needs fp32 storage (a bf16 index is its own shadow)");
+    }
+    ix->cfg.shadow_bf16 = cfg->shadow_bf16 ? 1 : 0;
+    ix->shadow_on = ix->cfg.shadow_bf16 != 0;
+    ix->d_pad = (int)round_up(cfg->dim, (ix->bf16 || ix->cfg.shadow_bf16) ? 8 : 4);
     ix->row_bytes = ix->d_pad * (ix->bf16 ? 2 : 4);
     ix->device = cfg->device;
     ix->num_sms = prop.multiProcessorCount;
@@ -297,6 +333,14 @@ extern "C" int b200r_set_id_base(b200r_index* ix, int64_t id_base) {
     return B200R_OK;
 }
 
+extern "C" int b200r_set_shadow_filter(b200r_index* ix, int32_t enabled) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_set_shadow_filter: null index");
+    if (!ix->cfg.shadow_bf16) return fail(B200R_E_INVALID, "index was created without shadow_bf16");
+    std::lock_guard<std::mutex> lk(ix->mu);
+    ix->shadow_on = enabled != 0;
+    return B200R_OK;
+}
+
 extern "C" int b200r_set_timing(b200r_index* ix, int32_t enabled) {
     if (!ix) return fail(B200R_E_INVALID, "b200r_set_timing: null index");
     ix->timing = enabled != 0;
@@ -343,6 +387,11 @@ extern "C" int b200r_add(b200r_index* ix, const void* x, int64_t n, int dtype, i
     if (mem_kind == B200R_DEVICE) {
         CU(launch_ingest((const float*)x, n, ix->d, ix->d_pad, norm, ix->bf16, dst, dstn, st));
         ix->st.n_kernel_launches++;
+        if (ix->shadow) {
+            CU(launch_ingest((const float*)x, n, ix->d, ix->d_pad, norm, true,
+                             ix->shadow + (size_t)ix->ntotal * ix->d_pad * 2, nullptr, st));
+            ix->st.n_kernel_launches++;
+        }
     } else {
         if (!ix->pin_add) {
             CU(cudaMallocHost(&ix->pin_add, 2 * kStageHalfBytes));
@@ -361,6 +410,11 @@ extern "C" int b200r_add(b200r_index* ix, const void* x, int64_t n, int dtype, i
             CU(cudaMemcpyAsync(dh, ph, (size_t)m * in_row, cudaMemcpyHostToDevice, st));
             CU(launch_ingest((const float*)dh, m, ix->d, ix->d_pad, norm, ix->bf16, dst + (size_t)r0 * ix->row_bytes,
                              dstn + r0, st));
+            if (ix->shadow) {
+                CU(launch_ingest((const float*)dh, m, ix->d, ix->d_pad, norm, true,
+                                 ix->shadow + (size_t)(ix->ntotal + r0) * ix->d_pad * 2, nullptr, st));
+                ix->st.n_kernel_launches++;
+            }
             CU(cudaEventRecord(ix->add_ev[half], st));
             used[half] = true;
             ix->st.n_kernel_launches++;
@@ -396,7 +450,7 @@ static int ensure_search_ws(b200r_index* ix, int64_t nq_slots, int64_t nq, int k
         CU(cudaMallocHost(&ix->q_pin, (size_t)cap * ix->d * sizeof(float)));
         CU(cudaMalloc(&ix->q_raw, (size_t)cap * ix->d * sizeof(float)));
         CU(cudaMalloc(&ix->q_dev, (size_t)cap * ix->d_pad * sizeof(float)));
-        if (ix->bf16) CU(cudaMalloc(&ix->q_bf16, (size_t)cap * ix->d_pad * 2));
+        if (ix->bf16 || ix->cfg.shadow_bf16) CU(cudaMalloc(&ix->q_bf16, (size_t)cap * ix->d_pad * 2));
         ix->q_cap = cap;
     }
     const int64_t need = nq * k;
@@ -418,7 +472,8 @@ static int ensure_search_ws(b200r_index* ix, int64_t nq_slots, int64_t nq, int k
 }
 
 static int ensure_gemm_ws(b200r_index* ix, int64_t nq, int k, cudaStream_t st) {
-    const size_t need = gemm_cand_bytes(ix->num_sms, kGemmMaxBlock, gemm_kp_cap(k));
+    const int filter = ix->bf16 ? kFilterBf16 : (ix->shadow && ix->shadow_on ? kFilterShadow : kFilterTf32);
+    const size_t need = gemm_cand_bytes(ix->num_sms, kGemmMaxBlock, gemm_kp_cap(k, filter, ix->kp_boost));
     if (need > ix->gemm_cand_bytes) {
         cudaFree(ix->gemm_cand);
         ix->gemm_cand = nullptr;
@@ -427,6 +482,9 @@ static int ensure_gemm_ws(b200r_index* ix, int64_t nq, int k, cudaStream_t st) {
         ix->gemm_cand_bytes = need;
     }
     if (!ix->max_norm_bits) {
+        CU(cudaMalloc(&ix->fb_q, (size_t)kScanMaxNQ * ix->d_pad * sizeof(float)));
+        CU(cudaMalloc(&ix->fb_d, (size_t)kScanMaxNQ * kScanMaxK * sizeof(float)));
+        CU(cudaMalloc(&ix->fb_i, (size_t)kScanMaxNQ * kScanMaxK * sizeof(int64_t)));
         CU(cudaMalloc(&ix->max_norm_bits, 256));
         CU(cudaMalloc(&ix->gemm_aux, gemm_aux_bytes()));
         ix->max_norm_dirty = true;
@@ -505,8 +563,9 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     float* od = out_mem_kind == B200R_DEVICE ? D : ix->out_d;
     int64_t* oi = out_mem_kind == B200R_DEVICE ? I : ix->out_i;
 
+    const bool use_shadow = use_gemm && ix->shadow && ix->shadow_on;
     if (use_gemm) {
-        if (ix->bf16) {
+        if (ix->bf16 || use_shadow) {
             CU(launch_f32_to_bf16(ix->q_dev, ix->q_bf16, nq_slots * ix->d_pad, st));
             ix->st.n_kernel_launches++;
         }
@@ -521,8 +580,10 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
             a.bf16 = ix->bf16;
             a.l2 = ix->l2;
             a.q_f32 = ix->q_dev + (size_t)q0 * ix->d_pad;
-            a.q_mma = ix->bf16 ? (const void*)((const uint8_t*)ix->q_bf16 + (size_t)q0 * ix->d_pad * 2)
-                               : (const void*)a.q_f32;
+            a.shadow = use_shadow ? ix->shadow : nullptr;
+            a.kp_boost_pct = ix->kp_boost;
+            a.q_mma = (ix->bf16 || use_shadow) ? (const void*)((const uint8_t*)ix->q_bf16 + (size_t)q0 * ix->d_pad * 2)
+                                               : (const void*)a.q_f32;
             a.nq = (int)std::min<int64_t>(kGemmMaxBlock, nq - q0);
             a.k = k;
             a.cand = ix->gemm_cand;
@@ -536,7 +597,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
             a.num_sms = std::min(ix->num_sms, kGemmMaxGrid);
             CU(launch_gemm_search(a, st));
             ix->st.n_kernel_launches += 3;
-            ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
+            ix->st.bytes_scanned += (int64_t)ix->ntotal * (use_shadow ? ix->d_pad * 2 : ix->row_bytes);
         }
         ix->st.last_path = B200R_PATH_GEMM;
         ix->st.last_grid = ix->num_sms;
@@ -545,6 +606,8 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
                            st));
         CU(cudaStreamSynchronize(st));
         ix->st.n_gemm_fallbacks += ix->fail_pin[ix->fail_cap];
+        if (ix->fail_pin[ix->fail_cap] > 0 && !getenv("B200R_GEMM_NOBOOST"))  // (tuning knob: keep K' fixed)
+            ix->kp_boost = std::min(400, ix->kp_boost * 3 / 2);
         if (getenv("B200R_DEBUG_FAILS") && ix->fail_pin[ix->fail_cap]) {
             int cause[4] = {0, 0, 0, 0};
             for (int64_t i = 0; i < nq; i++) cause[ix->fail_pin[i] & 3]++;
@@ -567,20 +630,57 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     p.scratch = ix->scratch;
     p.counter = ix->counter;
     p.id_base = ix->cfg.id_base;
-    // one query per launch after a GEMM pass (only the flagged ones) and for k > 128 (wide lists)
-    // ... and for rows so wide that four queries do not fit in shared memory beside the stages
-    const int scan_step = (use_gemm || k > kScanMaxK) ? 1 : scan_queries_per_launch(ix->d_pad, ix->row_bytes, ix->smem_optin);
-    for (int64_t q0 = 0; q0 < nq; q0 += scan_step) {
-        if (use_gemm && !ix->fail_pin[q0]) continue;  // only the queries whose check failed
-        const int nqg = (int)std::min<int64_t>(scan_step, nq - q0);
-        p.q = q_ready + (size_t)q0 * ix->d_pad;
-        p.out_d = od + (size_t)q0 * k;
-        p.out_i = oi + (size_t)q0 * k;
-        int grid = 0;
-        CU(launch_scan(p, nqg, ix->l2, ix->bf16, ix->num_sms, ix->smem_optin, st, &grid));
-        ix->st.n_kernel_launches++;
-        ix->st.last_grid = grid;
-        ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
+    // one query per launch for k > 128 (wide lists) and for rows so wide that four queries do not
+    // fit in shared memory beside the stages
+    const int scan_step = k > kScanMaxK ? 1 : scan_queries_per_launch(ix->d_pad, ix->row_bytes, ix->smem_optin);
+    if (!use_gemm) {
+        for (int64_t q0 = 0; q0 < nq; q0 += scan_step) {
+            const int nqg = (int)std::min<int64_t>(scan_step, nq - q0);
+            p.q = q_ready + (size_t)q0 * ix->d_pad;
+            p.out_d = od + (size_t)q0 * k;
+            p.out_i = oi + (size_t)q0 * k;
+            int grid = 0;
+            CU(launch_scan(p, nqg, ix->l2, ix->bf16, ix->num_sms, ix->smem_optin, st, &grid));
+            ix->st.n_kernel_launches++;
+            ix->st.last_grid = grid;
+            ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
+        }
+    } else if (ix->fail_pin[ix->fail_cap] > 0) {
+        // after a GEMM pass only the flagged queries are scanned: gathered scan_step at a time so
+        // that one corpus pass serves up to four of them
+        std::vector<int64_t> flagged;
+        for (int64_t i = 0; i < nq; i++)
+            if (ix->fail_pin[i]) flagged.push_back(i);
+        const size_t qb = (size_t)ix->d_pad * sizeof(float);
+        for (size_t f0 = 0; f0 < flagged.size(); f0 += scan_step) {
+            const int nqg = (int)std::min<size_t>(scan_step, flagged.size() - f0);
+            int grid = 0;
+            if (nqg == 1) {
+                const int64_t qi = flagged[f0];
+                p.q = q_ready + (size_t)qi * ix->d_pad;
+                p.out_d = od + (size_t)qi * k;
+                p.out_i = oi + (size_t)qi * k;
+                CU(launch_scan(p, 1, ix->l2, ix->bf16, ix->num_sms, ix->smem_optin, st, &grid));
+            } else {
+                for (int j = 0; j < nqg; j++)
+                    CU(cudaMemcpyAsync((uint8_t*)ix->fb_q + j * qb, (const uint8_t*)q_ready + (size_t)flagged[f0 + j] * qb, qb,
+                                       cudaMemcpyDeviceToDevice, st));
+                p.q = ix->fb_q;
+                p.out_d = ix->fb_d;
+                p.out_i = ix->fb_i;
+                CU(launch_scan(p, nqg, ix->l2, ix->bf16, ix->num_sms, ix->smem_optin, st, &grid));
+                for (int j = 0; j < nqg; j++) {
+                    const int64_t qi = flagged[f0 + j];
+                    CU(cudaMemcpyAsync(od + (size_t)qi * k, ix->fb_d + (size_t)j * k, (size_t)k * sizeof(float),
+                                       cudaMemcpyDeviceToDevice, st));
+                    CU(cudaMemcpyAsync(oi + (size_t)qi * k, ix->fb_i + (size_t)j * k, (size_t)k * sizeof(int64_t),
+                                       cudaMemcpyDeviceToDevice, st));
+                }
+            }
+            ix->st.n_kernel_launches++;
+            ix->st.last_grid = grid;
+            ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
+        }
     }
     if (!use_gemm) ix->st.last_path = B200R_PATH_SCAN;
     if (ix->timing) CU(cudaEventRecord(ix->t1, st));
@@ -705,6 +805,11 @@ extern "C" int b200r_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, 
             CU(launch_gather_rows(ix->rows, bounce, o0, o1, ix->row_bytes, adj_dev, m, st));
             CU(cudaMemcpyAsync(ix->rows + (size_t)o0 * ix->row_bytes, bounce, (size_t)(o1 - o0) * ix->row_bytes,
                                cudaMemcpyDeviceToDevice, st));
+            if (ix->shadow) {
+                CU(launch_gather_rows(ix->shadow, bounce, o0, o1, ix->d_pad * 2, adj_dev, m, st));
+                CU(cudaMemcpyAsync(ix->shadow + (size_t)o0 * ix->d_pad * 2, bounce, (size_t)(o1 - o0) * ix->d_pad * 2,
+                                   cudaMemcpyDeviceToDevice, st));
+            }
             CU(launch_gather_rows(ix->norms, bounce, o0, o1, (int)sizeof(float), adj_dev, m, st));
             CU(cudaMemcpyAsync(ix->norms + o0, bounce, (size_t)(o1 - o0) * sizeof(float), cudaMemcpyDeviceToDevice, st));
             ix->st.n_kernel_launches += 2;

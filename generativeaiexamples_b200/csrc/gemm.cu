@@ -268,6 +268,20 @@ __device__ __forceinline__ int enc_ordered(float f) {
 }
 __device__ __forceinline__ float dec_ordered(int o) { return __int_as_float(o >= 0 ? o : o ^ 0x7FFFFFFF); }
 
+// v[j] for a run-time j without sending v to local memory: a 5-level select tree (31 SELs)
+__device__ __forceinline__ float pick32(const float (&v)[32], int j) {
+    float a[16], b[8], c[4];
+#pragma unroll
+    for (int i = 0; i < 16; i++) a[i] = (j & 1) ? v[2 * i + 1] : v[2 * i];
+#pragma unroll
+    for (int i = 0; i < 8; i++) b[i] = (j & 2) ? a[2 * i + 1] : a[2 * i];
+#pragma unroll
+    for (int i = 0; i < 4; i++) c[i] = (j & 4) ? b[2 * i + 1] : b[2 * i];
+    const float d0 = (j & 8) ? c[1] : c[0];
+    const float d1 = (j & 8) ? c[3] : c[2];
+    return (j & 16) ? d1 : d0;
+}
+
 template <bool SMALL>
 __device__ __forceinline__ float better_of(float a, float b) {
     return SMALL ? fminf(a, b) : fmaxf(a, b);
@@ -620,23 +634,24 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                 }
                 if (active && p.debug_no_select == 0) {
                     float v[32];
-                    float best;
+                    const int64_t rbase = row0 + c * 32;
                     if (L2) {
                         // ||x||^2 - 2 q.x   (+ ||q||^2 is added at re-score time; order is unaffected)
 #pragma unroll
                         for (int j = 0; j < 32; j++) v[j] = fmaf(-2.f, __uint_as_float(r[j]), my_norms[c * 32 + j]);
-                        best = v[0];
-#pragma unroll
-                        for (int j = 1; j < 32; j++) best = fminf(best, v[j]);
                     } else {
 #pragma unroll
                         for (int j = 0; j < 32; j++) v[j] = __uint_as_float(r[j]);
-                        best = v[0];
-#pragma unroll
-                        for (int j = 1; j < 32; j++) best = fmaxf(best, v[j]);
                     }
+                    if (rbase + 32 > p.n_rows) {  // last tile only: rows past the end never win
+#pragma unroll
+                        for (int j = 0; j < 32; j++)
+                            if (rbase + j >= p.n_rows) v[j] = worst_val<L2>();
+                    }
+                    float best = v[0];
+#pragma unroll
+                    for (int j = 1; j < 32; j++) best = better_of<L2>(best, v[j]);
                     if (hist_only) {
-                        const int64_t rbase = row0 + c * 32;
 #pragma unroll
                         for (int j = 0; j < 32; j++)
                             if (rbase + j < p.n_rows) {
@@ -646,57 +661,64 @@ gemm_filter_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_const
                                 atomicAdd(my_hist + b, 1u);
                             }
                     } else if (better_val<L2>(best, thr)) {
-                        const int64_t rbase = row0 + c * 32;
+                        // A chunk with a survivor is rare.  The survivors' columns go into a bit mask and
+                        // ONE copy of the insert code walks it: unrolling the insert per column made
+                        // ~60 KB of code whose instruction-cache misses were the top stall (r01 notes).
+                        uint32_t hit = 0;
 #pragma unroll
-                        for (int j = 0; j < 32; j++)
-                            if (better_val<L2>(v[j], thr) && rbase + j < p.n_rows) {
-                                if (KP == 32) {
-                                    // compare-exchange chain over the 32 register slots (static indices)
-                                    float cv = v[j];
-                                    uint32_t ci = (uint32_t)(rbase + j);
+                        for (int j = 0; j < 32; j++) hit |= better_val<L2>(v[j], thr) ? (1u << j) : 0u;
+                        while (hit) {
+                            const int j = __ffs(hit) - 1;
+                            hit &= hit - 1;
+                            const float vj = pick32(v, j);
+                            if (!better_val<L2>(vj, thr)) continue;  // the threshold moved meanwhile
+                            if (KP == 32) {
+                                // compare-exchange chain over the 32 register slots (static indices)
+                                float cv = vj;
+                                uint32_t ci = (uint32_t)(rbase + j);
 #pragma unroll
-                                    for (int e = 0; e < 32; e++) {
-                                        const bool sw = better_val<L2>(cv, lv[e]);
-                                        const float tv = lv[e];
-                                        const uint32_t ti = li[e];
-                                        lv[e] = sw ? cv : tv;
-                                        li[e] = sw ? ci : ti;
-                                        cv = sw ? tv : cv;
-                                        ci = sw ? ti : ci;
-                                    }
-                                    lthr = lv[31];
-                                    count = 32;  // sentinel slots make the list "full" from the start
-                                } else {
-                                    if (count == KP) {
-                                        // slice full: entries admitted under an older, weaker threshold that
-                                        // the current one rules out can go (it is a lower bound of the final
-                                        // K'-th best, so they cannot be among the K' best)
-                                        g = better_of<L2>(g, dec_ordered(*reinterpret_cast<volatile int*>(gthr)));
-                                        int w = 0;
-                                        for (int e = 0; e < KP; e++) {
-                                            const Cand c2 = my_list[e];
-                                            if (better_val<L2>(c2.v, g)) my_list[w++] = c2;
-                                        }
-                                        count = w;
-                                    }
-                                    if (count < KP && better_val<L2>(v[j], g)) {
-                                        Cand cnd;
-                                        cnd.v = v[j];
-                                        cnd.id = (uint32_t)(rbase + j);
-                                        my_list[count++] = cnd;
-                                    } else if (count >= KP) {
-                                        count = KP + 1;  // still full after compaction: overflow
-                                    }
+                                for (int e = 0; e < 32; e++) {
+                                    const bool sw = better_val<L2>(cv, lv[e]);
+                                    const float tv = lv[e];
+                                    const uint32_t ti = li[e];
+                                    lv[e] = sw ? cv : tv;
+                                    li[e] = sw ? ci : ti;
+                                    cv = sw ? tv : cv;
+                                    ci = sw ? ti : ci;
                                 }
-                                thr = better_of<L2>(lthr, g);
-                                improved = true;
-                                if (!replay) {
-                                    const float good = L2 ? -v[j] : v[j];
-                                    int b = (int)((good - h_lo) * h_per_unit);
-                                    b = b < 0 ? 0 : (b > kGemmBuckets - 1 ? kGemmBuckets - 1 : b);
-                                    atomicAdd(my_hist + b, 1u);
+                                lthr = lv[31];
+                                count = 32;  // sentinel slots make the list "full" from the start
+                            } else {
+                                if (count == KP) {
+                                    // slice full: entries admitted under an older, weaker threshold that
+                                    // the current one rules out can go (it is a lower bound of the final
+                                    // K'-th best, so they cannot be among the K' best)
+                                    g = better_of<L2>(g, dec_ordered(*reinterpret_cast<volatile int*>(gthr)));
+                                    int w = 0;
+                                    for (int e = 0; e < KP; e++) {
+                                        const Cand c2 = my_list[e];
+                                        if (better_val<L2>(c2.v, g)) my_list[w++] = c2;
+                                    }
+                                    count = w;
+                                }
+                                if (count < KP && better_val<L2>(vj, g)) {
+                                    Cand cnd;
+                                    cnd.v = vj;
+                                    cnd.id = (uint32_t)(rbase + j);
+                                    my_list[count++] = cnd;
+                                } else if (count >= KP) {
+                                    count = KP + 1;  // still full after compaction: overflow
                                 }
                             }
+                            thr = better_of<L2>(lthr, g);
+                            improved = true;
+                            if (!replay) {
+                                const float good = L2 ? -vj : vj;
+                                int b = (int)((good - h_lo) * h_per_unit);
+                                b = b < 0 ? 0 : (b > kGemmBuckets - 1 ? kGemmBuckets - 1 : b);
+                                atomicAdd(my_hist + b, 1u);
+                            }
+                        }
                     }
                 }
             }
@@ -1158,11 +1180,32 @@ void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr, int
 
 // survivors kept per query: the slack beyond k must cover the rows whose approx score lies
 // within 2*eps of the k-th best; their number grows with k (and with N), so it scales with k
-int gemm_kp_cap(int k) { return (k + kGemmSlack <= 32) ? 32 : 256; }
-int gemm_kprime(int k) {
-    if (k + kGemmSlack <= 32) return 32;  // the register list below always holds 32
-    const int kp = 2 * k + 24;        // selection size K' (the per-thread slices stay at 256 entries:
-    const int cap = k + 512;          // with warm-up thresholds only ~K'/grid survivors reach a thread)
+// filter: kFilterTf32 (fp32 rows through tf32 MMA), kFilterBf16 (bf16 rows, bf16-rounded queries),
+// kFilterShadow (bf16 shadow of fp32 rows: both operands rounded).  The error bound grows in that
+// order (see launch_gemm_search), and so must the slack.  boost_pct (>= 100) widens the selection
+// after searches whose containment check failed (api.cu raises it; data with many near-ties).
+// Measured on 4M x 1024 unit-norm rows, 256 queries (r01 notes): the filter kernel slows by ~25%
+// per doubling of K' (more chunks take the append path), one scan-path fallback costs about as
+// much as the whole block, so K' is the smallest value that gave no fallback plus a margin.
+int gemm_kp_cap(int k, int filter, int boost_pct) {
+    if (const char* ev = getenv("B200R_GEMM_KPCAP")) {  // tuning knob
+        if (atoi(ev) == 256 || k + kGemmSlack > 32) return 256;
+        return 32;
+    }
+    if (filter != kFilterTf32 || boost_pct > 100) return 256;
+    return (k + kGemmSlack <= 32) ? 32 : 256;
+}
+int gemm_kprime(int k, int filter, int boost_pct) {
+    if (gemm_kp_cap(k, filter, boost_pct) == 32) return 32;  // the register list below always holds 32
+    // selection size K' (the per-thread slices stay at 256 entries: with warm-up thresholds only
+    // ~K'/grid survivors reach a thread)
+    int kp = 2 * k + 24;
+    if (k + kGemmSlack <= 32) kp = 32;
+    if (filter == kFilterBf16) kp = 3 * k + 34;
+    if (filter == kFilterShadow) kp = 4 * k + 72;
+    if (const char* ev = getenv("B200R_GEMM_KPRIME")) kp = atoi(ev) > k ? atoi(ev) : k + 1;  // tuning knob
+    if (boost_pct > 100) kp = (int)((int64_t)kp * boost_pct / 100);
+    const int cap = k + 512;
     return kp < cap ? kp : cap;
 }
 
@@ -1233,8 +1276,10 @@ static cudaError_t launch_rescore_bf(bool bf16, const RescoreParams& rp, int nq,
 cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     if (a.nq < 1 || a.nq > 2 * kGemmTileM || a.k < 1 || a.k > kMaxK) return cudaErrorInvalidValue;
     const int MT = a.nq <= kGemmTileM ? 1 : 2;
-    const int kp_cap = gemm_kp_cap(a.k);
-    const int kprime = gemm_kprime(a.k);
+    const int filter = a.shadow ? kFilterShadow : (a.bf16 ? kFilterBf16 : kFilterTf32);
+    const int boost = a.kp_boost_pct < 100 ? 100 : a.kp_boost_pct;
+    const int kp_cap = gemm_kp_cap(a.k, filter, boost);
+    const int kprime = gemm_kprime(a.k, filter, boost);
     const int64_t n_tiles_all = (a.n_rows + kGemmTileN - 1) / kGemmTileN;
     int cs = 2;  // query-operand multicast over CTA pairs
     if (const char* ev = getenv("B200R_GEMM_CLUSTER")) cs = atoi(ev) == 1 ? 1 : 2;
@@ -1243,21 +1288,25 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     bool pair = MT == 2 && cs == 2;
     if (const char* ev = getenv("B200R_GEMM_PAIR")) pair = pair && atoi(ev) != 0;
     if (pair) cs = 3;
+    // what the filter pass streams: the corpus itself, or its bf16 shadow
+    const bool fbf16 = a.bf16 || a.shadow != nullptr;
+    const void* fcorpus = a.shadow ? a.shadow : a.corpus;
+    if (a.shadow && (a.d_pad % 8) != 0) return cudaErrorInvalidValue;
     CUtensorMap mq, mx;
-    if (!make_map(&mq, a.q_mma, (int64_t)MT * kGemmTileM, a.d_pad, a.bf16, pair ? kGemmTileM : kGemmTileM / cs))
+    if (!make_map(&mq, a.q_mma, (int64_t)MT * kGemmTileM, a.d_pad, fbf16, pair ? kGemmTileM : kGemmTileM / cs))
         return cudaErrorNotSupported;
-    if (!make_map(&mx, a.corpus, a.n_rows, a.d_pad, a.bf16, pair ? kGemmTileN / 2 : kGemmTileN)) return cudaErrorNotSupported;
+    if (!make_map(&mx, fcorpus, a.n_rows, a.d_pad, fbf16, pair ? kGemmTileN / 2 : kGemmTileN)) return cudaErrorNotSupported;
     GemmParams p{};
     p.n_rows = a.n_rows;
     p.nq = a.nq;
     p.d_pad = a.d_pad;
     p.kprime = kprime;
-    p.num_kb = (a.d_pad * (a.bf16 ? 2 : 4) + kGemmKBytes - 1) / kGemmKBytes;
+    p.num_kb = (a.d_pad * (fbf16 ? 2 : 4) + kGemmKBytes - 1) / kGemmKBytes;
     p.n_tiles = (a.n_rows + kGemmTileN - 1) / kGemmTileN;
     p.norms = a.norms;
     p.cand = a.cand;
     p.gthr = a.gthr;
-    p.corpus = a.corpus;
+    p.corpus = fcorpus;
     {
         const char* ev = getenv("B200R_GEMM_PREFETCH");  // tuning knob
         p.prefetch_tiles = ev ? atoi(ev) : 0;
@@ -1270,7 +1319,7 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     p.qscale = a.qscale;
     gemm_prepare_kernel<<<MT * kGemmTileM, 32, 0, st>>>(a.q_f32, a.d_pad, a.nq, a.max_norm_bits, a.l2 ? 1 : 0, a.hist,
                                                         a.qscale, a.gthr, a.overflow);
-    p.evict_first = ((size_t)a.n_rows * a.d_pad * (a.bf16 ? 2 : 4) > ((size_t)96 << 20)) ? 1 : 0;
+    p.evict_first = ((size_t)a.n_rows * a.d_pad * (fbf16 ? 2 : 4) > ((size_t)96 << 20)) ? 1 : 0;
     int grid = (int)(p.n_tiles < a.num_sms ? p.n_tiles : a.num_sms);
     if (grid < 1) grid = 1;
     if (pair && grid < 2) grid = 2;
@@ -1285,7 +1334,7 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
         if (wv && kp_cap == 32) p.warmup = atoi(wv);
     }
     cudaError_t e;
-    if (a.bf16) {
+    if (fbf16) {
         if (MT == 1)
             e = kp_cap == 32 ? launch_filter_l2<true, 1, 32>(a.l2, cs, mq, mx, p, grid, st)
                              : launch_filter_l2<true, 1, 256>(a.l2, cs, mq, mx, p, grid, st);
@@ -1324,7 +1373,12 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     rp.kprime = kprime;
     rp.k = a.k;
     rp.max_norm_bits = a.max_norm_bits;
-    rp.err_coeff = 2.5e-3f;  // 2^-9 per product (two truncated tf32 / one bf16-rounded operand) + accumulation slack
+    // |q.x - (q.x)~| <= c * ||q|| * ||x|| (Cauchy-Schwarz over the per-product relative errors):
+    //   tf32: both operands truncated to 11 significant bits, 2 * 2^-10 = 1.95e-3
+    //   bf16 rows: the query is rounded to 8 significant bits, 2^-8 = 3.91e-3, the rows are exact
+    //   bf16 shadow of fp32 rows: both sides rounded, 2 * 2^-8 = 7.81e-3
+    // plus 5e-4 for the fp32 accumulation inside the tensor core.
+    rp.err_coeff = filter == kFilterShadow ? 8.4e-3f : (filter == kFilterBf16 ? 4.5e-3f : 2.5e-3f);
     rp.out_d = a.out_d;
     rp.out_i = a.out_i;
     rp.id_base = a.id_base;

@@ -85,9 +85,13 @@ struct GemmSearchArgs {
     int d_pad;
     bool bf16, l2;
     const float* q_f32;   // [128 or 256][d_pad] prepared queries, unused rows zero
-    const void* q_mma;    // same rows in the MMA input type (fp32 corpus: == q_f32; bf16 corpus: bf16 copy)
+    const void* q_mma;    // same rows in the filter's MMA input type (fp32: == q_f32; bf16: bf16 copy)
+    // optional bf16 shadow of an fp32 corpus ([n_rows][d_pad] bf16, d_pad % 8 == 0): the filter pass
+    // streams it instead of `corpus` (half the bytes, bf16 MMA rate); the re-score still reads `corpus`
+    const void* shadow;
+    int kp_boost_pct;     // >= 100: widens the selection size K' (raised after failed containment checks)
     int nq, k;
-    Cand* cand;           // >= gemm_cand_bytes(num_sms, 256, gemm_kp_cap(k))
+    Cand* cand;           // >= gemm_cand_bytes(num_sms, 256, gemm_kp_cap(k, filter, boost))
     int* gthr;            // [256] scratch: grid-wide per-query thresholds
     unsigned* hist;       // [256][512] scratch: score histograms
     float* qscale;        // [256][2] scratch: bucket maps
@@ -107,7 +111,8 @@ cudaError_t launch_f32_to_bf16(const float* src, void* dst, int64_t n, cudaStrea
 size_t gemm_cand_bytes(int grid, int nq_pad, int kp_cap);
 size_t gemm_aux_bytes();
 void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr, int** list_counts, int** overflow);
-int gemm_kp_cap(int k);
+enum { kFilterTf32 = 0, kFilterBf16 = 1, kFilterShadow = 2 };
+int gemm_kp_cap(int k, int filter, int boost_pct);
 
 // lets entry points outside api.cu fill b200r_last_error()
 void set_last_error(const char* msg);

@@ -42,9 +42,11 @@ class B200IndexFlat:
 
     def __init__(self, d: int, metric: int = METRIC_L2, *, storage: str = "f32", device: int = 0,
                  normalize_on_add: bool = False, normalize_queries: bool = False, reserve_rows: int = 0,
-                 id_base: int = 0, search_path: int = _lib.PATH_AUTO):
+                 id_base: int = 0, search_path: int = _lib.PATH_AUTO, shadow_bf16: bool = False):
         if storage not in ("f32", "bf16"):
             raise ValueError("storage must be 'f32' or 'bf16'")
+        if shadow_bf16 and storage != "f32":
+            raise ValueError("shadow_bf16 needs storage='f32'")
         self._h = None
         self._L = _lib.load()
         self.d = int(d)
@@ -54,8 +56,8 @@ class B200IndexFlat:
         self.device = int(device)
         cfg = _lib.Config(dim=self.d, metric=self.metric_type, storage=_lib.BF16 if storage == "bf16" else _lib.F32,
                           normalize_on_add=int(normalize_on_add), normalize_queries=int(normalize_queries),
-                          device=self.device, search_path=int(search_path), reserve_rows=int(reserve_rows),
-                          id_base=int(id_base))
+                          device=self.device, search_path=int(search_path), shadow_bf16=int(bool(shadow_bf16)),
+                          reserve_rows=int(reserve_rows), id_base=int(id_base))
         h = ctypes.c_void_p()
         _lib.check(self._L.b200r_create(ctypes.byref(cfg), ctypes.byref(h)))
         self._h = h
@@ -182,7 +184,8 @@ class B200IndexFlat:
         cfg = _lib.Config(dim=1, metric=METRIC_L2, storage=_lib.BF16 if storage == "bf16" else _lib.F32,
                           normalize_on_add=int(kw.get("normalize_on_add", False)),
                           normalize_queries=int(kw.get("normalize_queries", False)), device=int(device),
-                          search_path=int(kw.get("search_path", _lib.PATH_AUTO)), reserve_rows=0,
+                          search_path=int(kw.get("search_path", _lib.PATH_AUTO)),
+                          shadow_bf16=int(bool(kw.get("shadow_bf16", False))), reserve_rows=0,
                           id_base=int(kw.get("id_base", 0)))
         h = ctypes.c_void_p()
         _lib.check(L.b200r_load(str(path).encode(), ctypes.byref(cfg), ctypes.byref(h)))
@@ -197,6 +200,10 @@ class B200IndexFlat:
     # -- engine extras --------------------------------------------------------
     def set_id_base(self, base: int) -> None:
         _lib.check(self._L.b200r_set_id_base(self._h, int(base)))
+
+    def set_shadow_filter(self, enabled: bool) -> None:
+        """Index built with ``shadow_bf16=True``: filter batches on the bf16 shadow (default) or on the fp32 rows."""
+        _lib.check(self._L.b200r_set_shadow_filter(self._h, int(enabled)))
 
     def set_timing(self, enabled: bool) -> None:
         _lib.check(self._L.b200r_set_timing(self._h, int(enabled)))

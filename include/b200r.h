@@ -68,7 +68,11 @@ typedef struct b200r_config {
     int32_t normalize_queries; /* same for queries (rag_service.py:292) */
     int32_t device;            /* CUDA device ordinal */
     int32_t search_path;       /* B200R_PATH_* */
-    int32_t reserved0;
+    int32_t shadow_bf16;       /* fp32 storage only: also keep the rows rounded to bf16 (+50% HBM).
+                                  Batches on the GEMM path then filter on the shadow (half the bytes,
+                                  bf16 tensor-core rate) and re-score the survivors on the fp32 rows:
+                                  results stay exact, guarded by the same containment check.  No
+                                  faiss counterpart.  0 = off (default). */
     int64_t reserve_rows;      /* HBM reserved up front (0 = grow on demand) */
     int64_t id_base;           /* added to every returned id: global position of local row 0
                                   when the corpus is row-sharded over several GPUs */
@@ -191,6 +195,10 @@ int b200r_search_exchange(b200r_index* idx, const float* q, int64_t nq, int k, v
 
 /* row-sharding support: change the id offset after the shard layout moved */
 int b200r_set_id_base(b200r_index* idx, int64_t id_base);
+
+/* an index created with shadow_bf16 filters on the shadow by default; this turns that off/on at
+ * run time (no faiss counterpart) */
+int b200r_set_shadow_filter(b200r_index* idx, int32_t enabled);
 
 /* observability (no faiss counterpart) */
 int b200r_stats_get(b200r_index* idx, b200r_stats* out);

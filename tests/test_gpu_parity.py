@@ -563,3 +563,85 @@ def test_cross_stream_ordering(built_lib):
         assert I[0, 0] == n - 5 and D[0, 0] > 0.999
         np.testing.assert_array_equal(ix.reconstruct(n - 5), q[0])
         ix.close()
+
+
+# bf16 shadow of an fp32 corpus: the filter streams the shadow, the answers stay fp32-exact
+# ----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("metric", ["ip", "l2"])
+@pytest.mark.parametrize("d,n", [(1024, 40000), (100, 9001), (388, 20011)])
+def test_shadow_filter_parity(built_lib, metric, d, n):
+    from generativeaiexamples_b200 import _lib
+
+    rng = np.random.default_rng(4000 + d)
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    if metric == "l2":
+        x *= rng.uniform(0.5, 1.5, (n, 1)).astype(np.float32)
+    q = rng.standard_normal((260, d), dtype=np.float32)
+    q[::2] = x[rng.integers(0, n, 130)] + 0.05 * q[::2]
+    ix = _mk(metric, d, shadow_bf16=True)
+    plain = _mk(metric, d)
+    half = n // 2
+    ix.add(x[:half])
+    ix.add(x[half:])  # the shadow follows growth
+    plain.add(x)
+    for nq, k in ((5, 10), (64, 4), (129, 1), (260, 10), (33, 100), (200, 128)):
+        b0 = ix.stats()["bytes_scanned"]
+        D, I = ix.search(q[:nq], k)
+        st = ix.stats()
+        assert st["last_path"] == _lib.PATH_GEMM
+        # the filter pass streamed 2-byte elements (fallback scans, if any, add 4-byte passes)
+        d_pad = (d + 7) // 8 * 8
+        blocks = (nq + 255) // 256
+        assert (st["bytes_scanned"] - b0 - blocks * n * d_pad * 2) % (n * d_pad * 4) == 0
+        _check(metric, D, I, q[:nq], x, k, f"shadow {metric} d={d} nq={nq} k={k}")
+        Dp, Ip = plain.search(q[:nq], k)
+        np.testing.assert_array_equal(I, Ip)
+        np.testing.assert_array_equal(D, Dp)  # same fp32 re-score either way
+    # small batches still take the fp32 scan
+    D4, I4 = ix.search(q[:4], 10)
+    assert ix.stats()["last_path"] == _lib.PATH_SCAN
+    Dp, Ip = plain.search(q[:4], 10)
+    np.testing.assert_array_equal(I4, Ip)
+    np.testing.assert_array_equal(D4, Dp)
+    # run-time switch: filter on the fp32 rows instead
+    ix.set_shadow_filter(False)
+    b0 = ix.stats()["bytes_scanned"]
+    D, I = ix.search(q[:64], 10)
+    assert ix.stats()["bytes_scanned"] - b0 >= n * ((d + 7) // 8 * 8) * 4
+    Dp, Ip = plain.search(q[:64], 10)
+    np.testing.assert_array_equal(I, Ip)
+    np.testing.assert_array_equal(D, Dp)
+    ix.close()
+    plain.close()
+
+
+def test_shadow_filter_remove_and_fallback(built_lib):
+    from generativeaiexamples_b200 import B200IndexFlat, B200IndexFlatIP
+
+    rng = np.random.default_rng(41)
+    n, d = 20000, 1024
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    centre = x[123].copy()
+    # 600 rows closer together than bf16 can tell apart: the filter cannot rank them
+    x[1000:1600] = centre + 1e-4 * rng.standard_normal((600, d), dtype=np.float32)
+    q = np.repeat(centre[None, :], 24, axis=0) + 1e-3 * rng.standard_normal((24, d), dtype=np.float32)
+    ix = B200IndexFlatIP(d, shadow_bf16=True)
+    ix.add(x)
+    D, I = ix.search(q, 10)
+    assert ix.stats()["n_gemm_fallbacks"] > 0
+    _check("ip", D, I, q, x, 10, "shadow fallback")
+    # delete: rows, norms and shadow must move together
+    gone = np.unique(np.concatenate([rng.integers(0, n, 3000), np.arange(1000, 1590)]))
+    assert ix.remove_ids(gone) == len(gone)
+    keep = np.setdiff1d(np.arange(n), gone)
+    qq = x[keep[rng.integers(0, len(keep), 48)]] + 0.02 * rng.standard_normal((48, d), dtype=np.float32)
+    D, I = ix.search(qq, 10)
+    _check("ip", D, I, qq, x[keep], 10, "shadow after remove_ids")
+    ix.close()
+    with pytest.raises(Exception):
+        B200IndexFlat(d, 0, storage="bf16", shadow_bf16=True)
+    plain = B200IndexFlatIP(d)
+    with pytest.raises(Exception):
+        plain.set_shadow_filter(True)
+    plain.close()
