@@ -385,6 +385,32 @@ def main_gpu(args):
             if not same:
                 raise SystemExit("bench: shadow-filter results differ from the fp32-filter results")
 
+    # ---- batch-1 on the bf16 shadow (opt-in index mode; secondary) ---------------------------------
+    b1s = None
+    if use_shadow:
+        ref = [index.search(Q[i: i + 1], TOPK) for i in range(8)]
+        ref = [(d_.clone(), i_.clone()) for d_, i_ in ref]
+        index.local.set_shadow_filter(True)
+        fb0 = index.local.stats()["n_gemm_fallbacks"]
+        same = True
+        for i in range(8):
+            d_, i_ = index.search(Q[i: i + 1], TOPK)
+            same = same and bool(torch.equal(i_, ref[i][1]) and torch.equal(d_, ref[i][0]))
+        steps1 = max(20, args.steps // 2)
+        ms_s, _ = timed(dev_step, steps1, 5)
+        _, ms_s_wall = timed(e2e_step, steps1, 5)
+        fbs = index.local.stats()["n_gemm_fallbacks"] - fb0
+        index.local.set_shadow_filter(False)
+        b1s = {"value": steps1 * 1000.0 / ms_s, "unit": "queries/s", "ms_per_step": ms_s / steps1,
+               "e2e": {"value": steps1 * 1000.0 / ms_s_wall, "unit": "queries/s"},
+               "hbm_frac_bf16_bytes": (max_rows * DIM * 2 / (ms_s / steps1 * 1e-3) / 1e9) / peak,
+               "identical_to_fp32_scan": same, "path": "tcgen05 bf16 GEMM filter on the shadow + exact fp32 re-score", "gemm_fallbacks": fbs, "steps": steps1,
+               "note": "opt-in index mode (shadow_bf16=True, +50% HBM): the tcgen05 filter streams N*d*2 bytes of bf16 "
+                       "rows for the K'=112 best approximate scores, which are re-scored on the fp32 rows and checked "
+                       "for containment; not used for `value`/`e2e`/`roofline`"}
+        if not same:
+            raise SystemExit("bench: shadow-scan results differ from the fp32-scan results")
+
     # ---- service view: 64 concurrent single-query callers through the coalescer (N=1 only) -------
     conc = None
     if world == 1 and args.concurrent > 0:
@@ -440,6 +466,7 @@ def main_gpu(args):
                          "note": "kernel_ms = prep_queries + scan launch, CUDA events on the launching stream"},
             "cpu_baseline": cb,
             "batch256": b256,
+            "batch1_shadow_bf16": b1s,
             "concurrent_callers": conc,
             "clocks": clocks,
         }

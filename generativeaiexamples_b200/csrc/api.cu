@@ -61,6 +61,10 @@ struct DeviceGuard {
 // ---------------------------------------------------------------------------
 constexpr size_t kStageHalfBytes = 32u << 20;  // pinned / device staging, per half
 constexpr int64_t kMaxRows = 0xFFFFFFFEll;     // ids are 32-bit inside the kernels
+// corpus sizes from which small batches go to the GEMM path (measured crossovers, tools/perf_small_nq.py:
+// 2..4 queries from ~200k x 1024 fp32 rows; a single query on the bf16 shadow from ~375k rows)
+constexpr int64_t kGemmSmallBatchBytes = 768ll << 20;
+constexpr int64_t kGemmShadowSingleBytes = 1536ll << 20;
 
 struct b200r_index {
     b200r_config cfg{};
@@ -525,17 +529,27 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     const bool any_dev = q_mem_kind == B200R_DEVICE || out_mem_kind == B200R_DEVICE;
     cudaStream_t st = (any_dev || stream) ? (cudaStream_t)stream : ix->stream;
     // Two-way dispatch like faiss (scan for small batches, GEMM for large ones).  faiss switches
-    // at nq = 20 (distance_compute_blas_threshold); here the scan serves 4 queries per corpus pass
-    // and one GEMM pass costs about one scan pass, so the GEMM path wins from nq = 5.  Both paths
-    // end in the same fp32 scoring code, so the choice never changes a result.
+    // at nq = 20 (distance_compute_blas_threshold).  Here one GEMM pass streams the corpus at
+    // ~6.9 TB/s whatever nq <= 128 is, while the scan kernel is FMA-bound beyond one query
+    // (10M x 1024 fp32: 5.7 ms for nq = 1, 9.5-10.1 ms for nq = 2..4; GEMM 5.9-6.2 ms), so on a
+    // corpus large enough to hide the GEMM path's extra launches and its flag read-back the GEMM
+    // takes over at nq = 2 -- and at nq = 1 when it can filter on the bf16 shadow (3.0 ms).
+    // Small corpora keep the scan up to nq = 4.  Both paths end in the same fp32 scoring code, so
+    // the choice never changes a result.
     const char* env_thr = getenv("B200R_GEMM_MIN_NQ");
-    const int64_t gemm_min = env_thr ? atoll(env_thr) : 5;
+    const char* env_bytes = getenv("B200R_GEMM_MIN_BYTES");
+    const int64_t corpus_bytes = (int64_t)ix->ntotal * ix->row_bytes;
+    int64_t gemm_min = 5;
+    if (corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmSmallBatchBytes)) gemm_min = 2;
+    if (ix->shadow && ix->shadow_on && corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmShadowSingleBytes)) gemm_min = 1;
+    if (env_thr) gemm_min = atoll(env_thr);
     const bool use_gemm = ix->ntotal > 0 && (ix->cfg.search_path == B200R_PATH_GEMM ||
                                              (ix->cfg.search_path == B200R_PATH_AUTO && nq >= gemm_min));
     const int64_t nq_slots = use_gemm ? round_up(nq, 128) : round_up(nq, kScanMaxNQ);
+    const bool filtered = use_gemm;  // answers come from a filter + re-score + check
     int rc = ensure_search_ws(ix, nq_slots, nq, k);
     if (rc != B200R_OK) return rc;
-    if (use_gemm) {
+    if (filtered) {
         rc = ensure_gemm_ws(ix, nq, k, st);
         if (rc != B200R_OK) return rc;
     }
@@ -564,13 +578,13 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     int64_t* oi = out_mem_kind == B200R_DEVICE ? I : ix->out_i;
 
     const bool use_shadow = use_gemm && ix->shadow && ix->shadow_on;
+    int* fail_count = filtered ? ix->fail_dev + ix->fail_cap : nullptr;
+    if (filtered) CU(cudaMemsetAsync(fail_count, 0, sizeof(int), st));
     if (use_gemm) {
         if (ix->bf16 || use_shadow) {
             CU(launch_f32_to_bf16(ix->q_dev, ix->q_bf16, nq_slots * ix->d_pad, st));
             ix->st.n_kernel_launches++;
         }
-        int* fail_count = ix->fail_dev + ix->fail_cap;
-        CU(cudaMemsetAsync(fail_count, 0, sizeof(int), st));
         for (int64_t q0 = 0; q0 < nq; q0 += kGemmMaxBlock) {
             GemmSearchArgs a{};
             a.corpus = ix->rows;
@@ -601,6 +615,8 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
         }
         ix->st.last_path = B200R_PATH_GEMM;
         ix->st.last_grid = ix->num_sms;
+    }
+    if (filtered) {
         // the containment check is read back: one small D2H + sync per search
         CU(cudaMemcpyAsync(ix->fail_pin, ix->fail_dev, (size_t)(ix->fail_cap + 1) * sizeof(int), cudaMemcpyDeviceToHost,
                            st));
@@ -633,7 +649,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     // one query per launch for k > 128 (wide lists) and for rows so wide that four queries do not
     // fit in shared memory beside the stages
     const int scan_step = k > kScanMaxK ? 1 : scan_queries_per_launch(ix->d_pad, ix->row_bytes, ix->smem_optin);
-    if (!use_gemm) {
+    if (!filtered) {
         for (int64_t q0 = 0; q0 < nq; q0 += scan_step) {
             const int nqg = (int)std::min<int64_t>(scan_step, nq - q0);
             p.q = q_ready + (size_t)q0 * ix->d_pad;
@@ -682,7 +698,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
             ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
         }
     }
-    if (!use_gemm) ix->st.last_path = B200R_PATH_SCAN;
+    if (!filtered) ix->st.last_path = B200R_PATH_SCAN;
     if (ix->timing) CU(cudaEventRecord(ix->t1, st));
 
     if (out_mem_kind == B200R_HOST) {

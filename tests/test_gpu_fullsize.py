@@ -119,9 +119,14 @@ def test_c3_full_size_both_paths(built_lib):
     torch.cuda.synchronize()
     assert ix.ntotal == n
     Dt, It = best_s.cpu().numpy(), best_i.cpu().numpy()
+    # the scan path one query at a time (a corpus this large sends 2..4 queries to the GEMM path)
+    for i in range(4):
+        D1, I1 = ix.search(q[i: i + 1].contiguous(), k)
+        assert ix.stats()["last_path"] == 1
+        assert_topk_parity(D1.cpu().numpy(), I1.cpu().numpy(), Dt[i: i + 1], It[i: i + 1], what="C3 full size, scan path")
     D4, I4 = ix.search(q[:4].contiguous(), k)
-    assert ix.stats()["last_path"] == 1
-    assert_topk_parity(D4.cpu().numpy(), I4.cpu().numpy(), Dt[:4], It[:4], what="C3 full size, scan path")
+    assert ix.stats()["last_path"] == 2
+    assert_topk_parity(D4.cpu().numpy(), I4.cpu().numpy(), Dt[:4], It[:4], what="C3 full size, 4 queries")
     D32, I32 = ix.search(q, k)
     assert ix.stats()["last_path"] == 2
     assert_topk_parity(D32.cpu().numpy(), I32.cpu().numpy(), Dt, It, what="C3 full size, GEMM path")

@@ -645,3 +645,97 @@ def test_shadow_filter_remove_and_fallback(built_lib):
     with pytest.raises(Exception):
         plain.set_shadow_filter(True)
     plain.close()
+
+
+@pytest.mark.parametrize("metric", ["ip", "l2"])
+def test_shadow_small_batches(built_lib, metric, monkeypatch):
+    """nq <= 4 on a shadow index: the scan on small corpora, the shadow GEMM filter on large ones (forced here
+    through the size knob); the answers equal the plain index's bit for bit either way."""
+    from generativeaiexamples_b200 import _lib
+
+    rng = np.random.default_rng(77)
+    for d, n in ((1024, 30000), (100, 9001), (384, 50), (64, 7)):
+        x = rng.standard_normal((n, d), dtype=np.float32)
+        if metric == "l2":
+            x *= rng.uniform(0.5, 1.5, (n, 1)).astype(np.float32)
+        q = rng.standard_normal((4, d), dtype=np.float32)
+        q[::2] = x[rng.integers(0, n, 2)] + 0.05 * q[::2]
+        ix = _mk(metric, d, shadow_bf16=True)
+        plain = _mk(metric, d)
+        ix.add(x)
+        plain.add(x)
+        d_pad = (d + 7) // 8 * 8
+        for big in (False, True):
+            if big:
+                monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")  # treat this corpus as a large one
+            else:
+                monkeypatch.delenv("B200R_GEMM_MIN_BYTES", raising=False)
+            for nq, k in ((1, 10), (4, 10), (3, 1), (2, 14), (1, 100), (2, 200)):
+                b0 = ix.stats()["bytes_scanned"]
+                D, I = ix.search(q[:nq], k)
+                st = ix.stats()
+                if big:
+                    assert st["last_path"] == _lib.PATH_GEMM
+                    assert (st["bytes_scanned"] - b0 - n * d_pad * 2) % (n * d_pad * 4) == 0, (d, n, nq, k)
+                else:
+                    assert st["last_path"] == _lib.PATH_SCAN
+                kk = min(k, n)
+                assert (I[:, kk:] == -1).all()
+                _check(metric, D[:, :kk], I[:, :kk], q[:nq], x, kk, f"shadow small {metric} d={d} n={n} nq={nq} k={k}")
+                Dp, Ip = plain.search(q[:nq], k)
+                np.testing.assert_array_equal(I, Ip)
+                np.testing.assert_array_equal(D, Dp)
+        ix.close()
+        plain.close()
+
+
+def test_small_batch_dispatch_by_corpus_size(built_lib, monkeypatch):
+    """2..4 queries: scan on a small corpus, GEMM from ~200k rows (here: via the size knob); same answers."""
+    from generativeaiexamples_b200 import B200IndexFlatL2, _lib
+
+    rng = np.random.default_rng(79)
+    n, d = 20000, 256
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    q = x[:4] + 0.1 * rng.standard_normal((4, d), dtype=np.float32)
+    ix = B200IndexFlatL2(d)
+    ix.add(x)
+    D0, I0 = ix.search(q, 10)
+    assert ix.stats()["last_path"] == _lib.PATH_SCAN
+    monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
+    for nq in (2, 3, 4):
+        D1, I1 = ix.search(q[:nq], 10)
+        assert ix.stats()["last_path"] == _lib.PATH_GEMM
+        np.testing.assert_array_equal(I1, I0[:nq])
+        np.testing.assert_array_equal(D1, D0[:nq])
+    D1, I1 = ix.search(q[:1], 10)
+    assert ix.stats()["last_path"] == _lib.PATH_SCAN  # a single query without a shadow always scans
+    np.testing.assert_array_equal(I1, I0[:1])
+    _check("l2", D0, I0, q, x, 10, "dispatch")
+    ix.close()
+
+
+def test_shadow_single_query_fallback(built_lib, monkeypatch):
+    from generativeaiexamples_b200 import B200IndexFlatIP, _lib
+
+    monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
+    rng = np.random.default_rng(78)
+    n, d = 20000, 1024
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    centre = x[123].copy()
+    x[1000:1600] = centre + 1e-4 * rng.standard_normal((600, d), dtype=np.float32)
+    q = np.repeat(centre[None, :], 3, axis=0) + 1e-3 * rng.standard_normal((3, d), dtype=np.float32)
+    ix = B200IndexFlatIP(d, shadow_bf16=True)
+    ix.add(x)
+    for nq in (1, 3):
+        f0 = ix.stats()["n_gemm_fallbacks"]
+        D, I = ix.search(q[:nq], 10)
+        assert ix.stats()["last_path"] == _lib.PATH_GEMM
+        assert ix.stats()["n_gemm_fallbacks"] > f0
+        _check("ip", D, I, q[:nq], x, 10, "shadow single-query fallback")
+    f0 = ix.stats()["n_gemm_fallbacks"]
+    q2 = x[5000:5001] + 0.05 * rng.standard_normal((1, d), dtype=np.float32)
+    D, I = ix.search(q2, 10)
+    assert ix.stats()["n_gemm_fallbacks"] == f0  # an ordinary query needs none
+    _check("ip", D, I, q2, x, 10, "shadow single query")
+    ix.close()
