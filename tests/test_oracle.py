@@ -168,3 +168,19 @@ def test_shim_threshold_and_delete():
 def test_oracle_build_is_loadable():
     lib = load_flat_ref()
     assert lib.oracle_max_threads() >= 1
+
+
+@pytest.mark.parametrize("nq", [3, 40])
+def test_restatement_matches_independent_bruteforce(nq):
+    """Third-party cross-check (not the reference: faiss is absent from this image): scikit-learn's brute-force
+    k-NN must agree with the restatement on ids, and on distances after squaring (faiss returns squared L2)."""
+    sk = pytest.importorskip("sklearn.neighbors")
+    rng = np.random.default_rng(2024 + nq)
+    x = rng.standard_normal((3000, 96)).astype(np.float32)
+    q = rng.standard_normal((nq, 96)).astype(np.float32)
+    nn = sk.NearestNeighbors(n_neighbors=12, algorithm="brute", metric="euclidean").fit(x.astype(np.float64))
+    dist, ids = nn.kneighbors(q.astype(np.float64))
+    D, I = FlatRef.knn(METRIC_L2, q, x, 12)
+    scale = float((q.astype(np.float64) ** 2).sum(1).max() + (x.astype(np.float64) ** 2).sum(1).max()) if nq >= 20 else 1.0
+    assert_topk_parity(D, I, (dist ** 2).astype(np.float32), ids.astype(np.int64), what="restatement vs sklearn brute force",
+                       scale=scale)
