@@ -65,6 +65,8 @@ constexpr int64_t kMaxRows = 0xFFFFFFFEll;     // ids are 32-bit inside the kern
 // 2..4 queries from ~200k x 1024 fp32 rows; a single query on the bf16 shadow from ~375k rows)
 constexpr int64_t kGemmSmallBatchBytes = 768ll << 20;
 constexpr int64_t kGemmShadowSingleBytes = 1536ll << 20;
+constexpr int64_t kGemmBf16SmallBatchBytes = 100ll << 20;  // bf16 storage: 2..4 queries from ~50k x 1024 rows
+constexpr int64_t kGemmBf16SingleBytes = 2048ll << 20;     // bf16 storage: one query from ~1M x 1024 rows
 
 struct b200r_index {
     b200r_config cfg{};
@@ -542,6 +544,12 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     int64_t gemm_min = 5;
     if (corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmSmallBatchBytes)) gemm_min = 2;
     if (ix->shadow && ix->shadow_on && corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmShadowSingleBytes)) gemm_min = 1;
+    if (ix->bf16) {
+        // bf16 rows: the scan unpacks every element (5.5 TB/s for one query, 1.5 TB/s for four),
+        // the tensor cores take bf16 as it is (6.8 TB/s)
+        if (corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmBf16SmallBatchBytes)) gemm_min = 2;
+        if (corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmBf16SingleBytes)) gemm_min = 1;
+    }
     if (env_thr) gemm_min = atoll(env_thr);
     const bool use_gemm = ix->ntotal > 0 && (ix->cfg.search_path == B200R_PATH_GEMM ||
                                              (ix->cfg.search_path == B200R_PATH_AUTO && nq >= gemm_min));
