@@ -739,3 +739,27 @@ def test_shadow_single_query_fallback(built_lib, monkeypatch):
     assert ix.stats()["n_gemm_fallbacks"] == f0  # an ordinary query needs none
     _check("ip", D, I, q2, x, 10, "shadow single query")
     ix.close()
+
+
+@pytest.mark.parametrize("shadow", [False, True])
+def test_gemm_massive_ties(built_lib, shadow):
+    """Thousands of identical rows: whatever the filter keeps, the answer is the lowest ids (faiss keeps the
+    first-seen on ties) with exactly equal scores; the check must send these queries to the scan path."""
+    from generativeaiexamples_b200 import B200IndexFlat
+
+    rng = np.random.default_rng(91)
+    n, d, k = 12000, 256, 10
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    x[2000:9000] = x[2000]  # 7000 copies of one row
+    q = np.repeat(x[2000][None, :], 8, axis=0)
+    q[4:] = rng.standard_normal((4, d), dtype=np.float32)  # and four ordinary queries
+    for metric in (0, 1):
+        ix = B200IndexFlat(d, metric, shadow_bf16=shadow)
+        ix.add(x)
+        D, I = ix.search(q, k)
+        assert ix.stats()["last_path"] == 2
+        for i in range(4):
+            np.testing.assert_array_equal(I[i], np.arange(2000, 2000 + k))
+            assert (D[i] == D[i, 0]).all()
+        _check("l2" if metric == 1 else "ip", D[4:], I[4:], q[4:], x, k, f"ties metric={metric} shadow={shadow}")
+        ix.close()
