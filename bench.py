@@ -152,6 +152,25 @@ def cpu_reference(steps: int, warmup: int, sample_rows: int = 400_000, budget_s:
         return done / (time.perf_counter() - t0), done
 
     scale = sample_rows / N_TOTAL
+    # Opportunistic: a real faiss on the box (never seen on this pool) is timed as the
+    # reference proper and checked against the restatement; its absence is the expected case.
+    live = {"faiss_importable": False}
+    try:
+        ref_dir = os.path.join(ROOT, "baseline", "_ref")
+        if os.path.isdir(ref_dir) and ref_dir not in sys.path:
+            sys.path.append(ref_dir)
+        import faiss  # noqa: F401
+
+        fidx = faiss.IndexFlatIP(DIM)
+        fidx.add(x)
+        qps_faiss, nf = run(lambda v: fidx.search(v, TOPK), min(warmup, 2), steps, budget_s * 0.3)
+        Df, If = fidx.search(q[:8], TOPK)
+        Dr, Ir = FlatRef.knn(0, q[:8], x, TOPK)
+        live = {"faiss_importable": True, "faiss_version": getattr(faiss, "__version__", "?"),
+                "value": qps_faiss * scale, "steps": nf, "ids_equal_to_restatement": bool((If == Ir).all()),
+                "max_abs_score_diff_vs_restatement": float(np.abs(Df - Dr).max())}
+    except ImportError:
+        pass
     # (i) faithful: faiss 1.7.4 runs nq < 20 on ONE thread (OpenMP over queries only)
     qps_faithful, n1 = run(lambda v: FlatRef.knn(0, v, x, TOPK), min(warmup, 2), steps, budget_s * 0.4)
     # (ii) the same scan row-parallel over all cores (not a faiss code path; stronger baseline)
@@ -164,6 +183,11 @@ def cpu_reference(steps: int, warmup: int, sample_rows: int = 400_000, budget_s:
                 break
     except OSError:
         pass
+    if live["faiss_importable"]:  # the real thing: report it, keep the restatement's numbers beside it
+        return {"value": live["value"], "unit": "queries/s", "cores": threads, "kind": "reference", "cpu_model": cpu_model,
+                "sample": f"faiss.IndexFlatIP.search, nq=1 top-{TOPK} over a {sample_rows} x {DIM} slice, scaled to {N_TOTAL} rows",
+                "port_allcores_value": qps_all * scale, "faithful_1thread_value": qps_faithful * scale,
+                "host_cores_visible": len(os.sched_getaffinity(0)), "live_faiss": live}
     return {
         "value": qps_all * scale, "unit": "queries/s", "cores": threads, "kind": "port", "cpu_model": cpu_model,
         "omp_num_threads": os.environ.get("OMP_NUM_THREADS", "unset (OpenMP default = all cores)"),
@@ -173,6 +197,7 @@ def cpu_reference(steps: int, warmup: int, sample_rows: int = 400_000, budget_s:
         "faithful_1thread_value": qps_faithful * scale,
         "note": "value = all-cores row-parallel scan; faithful_1thread_value = faiss 1.7.4's own nq<20 path (1 thread)",
         "host_cores_visible": len(os.sched_getaffinity(0)),
+        "live_faiss": live,
     }
 
 
