@@ -190,7 +190,8 @@ class ShardedFlatIndex:
                 qd = q
                 mine = torch.empty(block, dtype=torch.uint8, device=dev)
                 out = torch.empty(block, dtype=torch.uint8, device=dev) if self.world > 1 else mine
-            xchg = self._exchange() if (self.world > 1 and nq <= 4 and k <= 128) else None
+            # single queries only: batches of 2..4 are better served by the local GEMM route + NCCL
+            xchg = self._exchange() if (self.world > 1 and nq == 1 and k <= 128) else None
             if xchg is not None:
                 # scan kernel -> NVLink stores into every rank's buffer -> waiting select kernel
                 if not as_numpy:
