@@ -36,8 +36,11 @@ def create_vectorstore_langchain(document_embedder, collection_name: str = "", *
     if name not in SUPPORTED_NAMES:
         raise ValueError(f"{name} vector database is not supported")
     d = int(dimensions if dimensions is not None else os.getenv("APP_EMBEDDINGS_DIMENSIONS", "1024"))
-    index = B200IndexFlatL2(d, device=int(os.getenv("B200R_DEVICE", "0")), storage=os.getenv("B200R_STORAGE", "f32"),
-                            reserve_rows=int(os.getenv("B200R_RESERVE_ROWS", "0")))
+    storage = os.getenv("B200R_STORAGE", "f32")
+    index = B200IndexFlatL2(d, device=int(os.getenv("B200R_DEVICE", "0")), storage=storage,
+                            reserve_rows=int(os.getenv("B200R_RESERVE_ROWS", "0")),
+                            # opt-in bf16 copy of the fp32 rows for the filter pass (+50 % HBM, same answers)
+                            shadow_bf16=storage == "f32" and os.getenv("B200R_SHADOW_BF16", "0") == "1")
     vectorstore = B200FlatVectorStore(document_embedder, index, InMemoryDocstore(), {})
     logger.info("Vector store created and saved.")
     return vectorstore
