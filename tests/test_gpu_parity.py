@@ -763,3 +763,33 @@ def test_gemm_massive_ties(built_lib, shadow):
             assert (D[i] == D[i, 0]).all()
         _check("l2" if metric == 1 else "ip", D[4:], I[4:], q[4:], x, k, f"ties metric={metric} shadow={shadow}")
         ix.close()
+
+
+def test_shadow_survives_load_and_reset(built_lib, tmp_path, monkeypatch):
+    from generativeaiexamples_b200 import B200IndexFlat, B200IndexFlatIP, _lib
+
+    monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
+    rng = np.random.default_rng(93)
+    n, d = 9000, 200
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    q = x[:6] + 0.05 * rng.standard_normal((6, d), dtype=np.float32)
+    plain = B200IndexFlatIP(d)
+    plain.add(x)
+    path = str(tmp_path / "index.faiss")
+    plain.write(path)
+    ix = B200IndexFlat.read(path, shadow_bf16=True)  # the shadow is rebuilt while the file streams in
+    assert ix.ntotal == n
+    b0 = ix.stats()["bytes_scanned"]
+    D, I = ix.search(q, 10)
+    assert ix.stats()["last_path"] == _lib.PATH_GEMM
+    assert (ix.stats()["bytes_scanned"] - b0) % (n * 200 * 4) == n * 200 * 2  # the filter streamed 2-byte rows
+    Dp, Ip = plain.search(q, 10)
+    np.testing.assert_array_equal(I, Ip)
+    np.testing.assert_array_equal(D, Dp)
+    ix.reset()
+    assert ix.ntotal == 0
+    ix.add(x[:500])
+    D, I = ix.search(q, 10)
+    _check("ip", D, I, q, x[:500], 10, "shadow after reset")
+    ix.close()
+    plain.close()
