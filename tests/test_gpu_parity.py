@@ -793,3 +793,53 @@ def test_shadow_survives_load_and_reset(built_lib, tmp_path, monkeypatch):
     _check("ip", D, I, q, x[:500], 10, "shadow after reset")
     ix.close()
     plain.close()
+
+
+@pytest.mark.parametrize("seed", range(64))
+def test_randomised_differential(built_lib, seed, monkeypatch):
+    """Random shapes, metrics, routes and index options against the float64 truth: whatever the dispatch picks
+    (scan, tf32 / bf16-shadow GEMM filter, fallbacks), ids and scores must satisfy the north-star tolerance."""
+    from generativeaiexamples_b200 import B200IndexFlat, _lib
+    from oracle import assert_topk_parity, truth_topk
+
+    rng = np.random.default_rng(5000 + seed)
+    d = int(rng.choice([1, 3, 4, 7, 8, 31, 64, 100, 257, 384, 768, 1024, 1100]))
+    n = int(rng.choice([1, 2, 31, 255, 256, 257, 1000, 4099, 12000, 20000]))
+    nq = int(rng.choice([1, 2, 3, 4, 5, 19, 20, 64, 129, 200]))
+    k = int(rng.choice([1, 2, 4, 10, 32, 33, 100, 128, 129, 300]))
+    metric = "l2" if rng.random() < 0.5 else "ip"
+    shadow = bool(rng.random() < 0.4)
+    path = int(rng.choice([_lib.PATH_AUTO, _lib.PATH_AUTO, _lib.PATH_SCAN, _lib.PATH_GEMM]))
+    norm_add = bool(rng.random() < 0.3)
+    norm_q = bool(rng.random() < 0.3)
+    if rng.random() < 0.5:
+        monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
+    x = rng.standard_normal((n, d), dtype=np.float32) * rng.uniform(0.3, 3.0, (n, 1)).astype(np.float32)
+    q = rng.standard_normal((nq, d), dtype=np.float32)
+    src = rng.integers(0, n, nq)
+    near = rng.random(nq) < 0.5
+    q[near] = x[src[near]] + 0.05 * q[near]
+    ix = B200IndexFlat(d, 1 if metric == "l2" else 0, shadow_bf16=shadow, search_path=path,
+                       normalize_on_add=norm_add, normalize_queries=norm_q)
+    cut = int(rng.integers(0, n + 1))
+    ix.add(x[:cut])
+    ix.add(x[cut:])
+    D, I = ix.search(q, k)
+
+    def unit(a):
+        nrm = np.sqrt((a.astype(np.float32) ** 2).sum(1, keepdims=True, dtype=np.float32))
+        return np.where(nrm > 0, a / np.where(nrm > 0, nrm, 1), a).astype(np.float32)
+
+    xe = unit(x) if norm_add else x
+    qe = unit(q) if norm_q else q
+    kk = min(k, n)
+    what = f"seed={seed} d={d} n={n} nq={nq} k={k} {metric} shadow={shadow} path={path} norm={norm_add},{norm_q}"
+    assert (I[:, kk:] == -1).all(), what
+    Dt, It = truth_topk(metric, qe, xe, min(n, kk + 8))
+    # normalisation happens in fp32 on the device: compare with a tolerance scaled by the magnitudes involved
+    scale = float(max(1.0, (qe.astype(np.float64) ** 2).sum(1).max() + (xe.astype(np.float64) ** 2).sum(1).max())) \
+        if (norm_add or norm_q or metric == "l2") else 1.0
+    assert_topk_parity(D[:, :kk], I[:, :kk], Dt, It, what=what, scale=scale if (norm_add or norm_q) else 1.0)
+    s = D[:, :kk] if metric == "l2" else -D[:, :kk]
+    assert (np.diff(s, axis=1) >= 0).all(), what + ": not sorted"
+    ix.close()
