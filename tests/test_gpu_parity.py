@@ -811,6 +811,7 @@ def test_randomised_differential(built_lib, seed, monkeypatch):
     shadow = bool(rng.random() < 0.4)
     path = int(rng.choice([_lib.PATH_AUTO, _lib.PATH_AUTO, _lib.PATH_SCAN, _lib.PATH_GEMM]))
     norm_add = bool(rng.random() < 0.3)
+    bf16 = bool(not shadow and not norm_add and rng.random() < 0.3)  # stored rows = bf16(x): compare with those
     norm_q = bool(rng.random() < 0.3)
     if rng.random() < 0.5:
         monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
@@ -819,8 +820,12 @@ def test_randomised_differential(built_lib, seed, monkeypatch):
     src = rng.integers(0, n, nq)
     near = rng.random(nq) < 0.5
     q[near] = x[src[near]] + 0.05 * q[near]
+    if bf16:
+        import torch
+
+        x = torch.from_numpy(x).to(torch.bfloat16).to(torch.float32).numpy()
     ix = B200IndexFlat(d, 1 if metric == "l2" else 0, shadow_bf16=shadow, search_path=path,
-                       normalize_on_add=norm_add, normalize_queries=norm_q)
+                       normalize_on_add=norm_add, normalize_queries=norm_q, storage="bf16" if bf16 else "f32")
     cut = int(rng.integers(0, n + 1))
     ix.add(x[:cut])
     ix.add(x[cut:])
@@ -833,7 +838,7 @@ def test_randomised_differential(built_lib, seed, monkeypatch):
     xe = unit(x) if norm_add else x
     qe = unit(q) if norm_q else q
     kk = min(k, n)
-    what = f"seed={seed} d={d} n={n} nq={nq} k={k} {metric} shadow={shadow} path={path} norm={norm_add},{norm_q}"
+    what = f"seed={seed} d={d} n={n} nq={nq} k={k} {metric} shadow={shadow} bf16={bf16} path={path} norm={norm_add},{norm_q}"
     assert (I[:, kk:] == -1).all(), what
     Dt, It = truth_topk(metric, qe, xe, min(n, kk + 8))
     # normalisation happens in fp32 on the device: compare with a tolerance scaled by the magnitudes involved
