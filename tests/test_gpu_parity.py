@@ -848,3 +848,53 @@ def test_randomised_differential(built_lib, seed, monkeypatch):
     s = D[:, :kk] if metric == "l2" else -D[:, :kk]
     assert (np.diff(s, axis=1) >= 0).all(), what + ": not sorted"
     ix.close()
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_randomised_mutation_sequences(built_lib, seed, monkeypatch):
+    """add / remove_ids / reset / search in random order against a numpy model of faiss's semantics
+    (positions are ids; remove_ids compacts and shifts later ids down)."""
+    from generativeaiexamples_b200 import B200IndexFlat
+    from oracle import assert_topk_parity, truth_topk
+
+    rng = np.random.default_rng(7000 + seed)
+    d = int(rng.choice([8, 100, 256, 1024]))
+    metric = "l2" if seed % 2 else "ip"
+    shadow = bool(seed % 3 == 0)
+    if seed % 4 < 2:
+        monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
+    ix = B200IndexFlat(d, 1 if metric == "l2" else 0, shadow_bf16=shadow)
+    model = np.zeros((0, d), dtype=np.float32)
+    for step in range(14):
+        op = rng.choice(["add", "add", "remove", "search", "search", "reset"], p=[0.3, 0.2, 0.2, 0.15, 0.1, 0.05])
+        if op == "add" or model.shape[0] == 0:
+            m = int(rng.choice([1, 5, 300, 3000]))
+            x = rng.standard_normal((m, d), dtype=np.float32)
+            ix.add(x)
+            model = np.concatenate([model, x])
+        elif op == "remove":
+            ids = rng.integers(-5, model.shape[0] + 5, int(rng.choice([1, 10, 500])))
+            valid = np.unique(ids[(ids >= 0) & (ids < model.shape[0])])
+            assert ix.remove_ids(ids.astype(np.int64)) == len(valid)
+            model = np.delete(model, valid, axis=0)
+        elif op == "reset":
+            ix.reset()
+            model = np.zeros((0, d), dtype=np.float32)
+        assert ix.ntotal == model.shape[0]
+        if model.shape[0] == 0:
+            D, I = ix.search(rng.standard_normal((2, d), dtype=np.float32), 3)
+            assert (I == -1).all()
+            continue
+        nq = int(rng.choice([1, 3, 8, 40]))
+        k = int(rng.choice([1, 10, 50]))
+        q = rng.standard_normal((nq, d), dtype=np.float32)
+        pick = rng.integers(0, model.shape[0], nq)
+        q[::2] = model[pick[::2]] + 0.05 * q[::2]
+        D, I = ix.search(q, k)
+        kk = min(k, model.shape[0])
+        assert (I[:, kk:] == -1).all()
+        Dt, It = truth_topk(metric, q, model, min(model.shape[0], kk + 8))
+        assert_topk_parity(D[:, :kk], I[:, :kk], Dt, It, what=f"seed={seed} step={step} op={op} n={model.shape[0]} nq={nq} k={k}")
+        j = int(rng.integers(0, model.shape[0]))
+        np.testing.assert_array_equal(ix.reconstruct(j), model[j])
+    ix.close()
