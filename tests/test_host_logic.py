@@ -272,3 +272,19 @@ def test_multi_turn_rag_surface():
         thr = conv_store.as_retriever(search_type="similarity_score_threshold",
                                       search_kwargs={"score_threshold": 0.25, "k": 40})
         assert [d.page_content for d in thr.get_relevant_documents("user said 3")] == ["user said 3"]
+
+
+def test_to_matrix_fast_paths_match_numpy():
+    from generativeaiexamples_b200.vectorstore import _to_matrix
+
+    rng = np.random.default_rng(3)
+    rows = (rng.standard_normal((5, 37)) * 1e3).tolist()
+    for inp in (rows[0], tuple(rows[0]), rows, [tuple(r) for r in rows], np.asarray(rows), np.asarray(rows, dtype=np.float32)):
+        got = _to_matrix(inp)
+        want = np.asarray(inp, dtype=np.float32)
+        want = want[None, :] if want.ndim == 1 else want
+        assert got.dtype == np.float32 and got.flags["C_CONTIGUOUS"] and got.shape == want.shape
+        np.testing.assert_array_equal(got, want)
+    with pytest.raises(ValueError):
+        _to_matrix([[1.0, 2.0], [3.0]])
+    np.testing.assert_array_equal(_to_matrix([[1, 2], [3, 4]]), np.array([[1, 2], [3, 4]], dtype=np.float32))
