@@ -100,8 +100,9 @@ struct b200r_index {
     int64_t q_cap = 0;        // query slots allocated
     Cand* scratch = nullptr;
     unsigned* counter = nullptr;
-    float* out_d = nullptr;
-    int64_t* out_i = nullptr;
+    uint8_t* out_buf = nullptr;  // host-output searches: [scores | pad to 16 B | ids], one D2H per search
+    float* out_d = nullptr;      // = out_buf
+    int64_t* out_i = nullptr;    // ids of a full-capacity result (only a placeholder target otherwise)
     uint8_t* out_pin = nullptr;
     int64_t out_cap = 0;  // nq*k entries allocated
     cudaEvent_t t0 = nullptr, t1 = nullptr;
@@ -223,8 +224,7 @@ static void free_index(b200r_index* ix) {
     cudaFree(ix->q_dev);
     cudaFree(ix->scratch);
     cudaFree(ix->counter);
-    cudaFree(ix->out_d);
-    cudaFree(ix->out_i);
+    cudaFree(ix->out_buf);
     cudaFreeHost(ix->out_pin);
     cudaFree(ix->q_bf16);
     cudaFree(ix->gemm_cand);
@@ -465,16 +465,17 @@ static int ensure_search_ws(b200r_index* ix, int64_t nq_slots, int64_t nq, int k
     }
     const int64_t need = nq * k;
     if (need > ix->out_cap) {
-        cudaFree(ix->out_d);
-        cudaFree(ix->out_i);
+        cudaFree(ix->out_buf);
         cudaFreeHost(ix->out_pin);
+        ix->out_buf = nullptr;
         ix->out_d = nullptr;
         ix->out_i = nullptr;
         ix->out_pin = nullptr;
         ix->out_cap = 0;
         const int64_t cap = std::max<int64_t>(need, 4096);
-        CU(cudaMalloc(&ix->out_d, (size_t)cap * sizeof(float)));
-        CU(cudaMalloc(&ix->out_i, (size_t)cap * sizeof(int64_t)));
+        CU(cudaMalloc(&ix->out_buf, (size_t)cap * (sizeof(float) + sizeof(int64_t)) + 64));
+        ix->out_d = reinterpret_cast<float*>(ix->out_buf);
+        ix->out_i = reinterpret_cast<int64_t*>(ix->out_buf + round_up((size_t)cap * sizeof(float), 16));
         CU(cudaMallocHost(&ix->out_pin, (size_t)cap * (sizeof(float) + sizeof(int64_t)) + 64));
         ix->out_cap = cap;
     }
@@ -569,25 +570,32 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     if (ix->data_ev_set && ix->data_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->data_ev, 0));
     if (ix->timing) CU(cudaEventRecord(ix->t0, st));
     const float* q_src = (const float*)q;
+    // queries that need no padding, normalisation or zero-filled spare slots skip the prep kernel:
+    // device ones are used in place, host ones are copied straight into the prepared-query buffer
+    const bool q_plain = !use_gemm && ix->d == ix->d_pad && !ix->cfg.normalize_queries &&
+                         (nq == 1 || nq % kScanMaxNQ == 0);
+    const bool q_in_place = q_plain && q_mem_kind == B200R_DEVICE && (reinterpret_cast<uintptr_t>(q) & 15) == 0;
+    const bool q_direct = q_plain && q_mem_kind == B200R_HOST;
     if (q_mem_kind == B200R_HOST) {
         memcpy(ix->q_pin, q, (size_t)nq * ix->d * sizeof(float));
-        CU(cudaMemcpyAsync(ix->q_raw, ix->q_pin, (size_t)nq * ix->d * sizeof(float), cudaMemcpyHostToDevice, st));
-        q_src = ix->q_raw;
+        float* dst = q_direct ? ix->q_dev : ix->q_raw;
+        CU(cudaMemcpyAsync(dst, ix->q_pin, (size_t)nq * ix->d * sizeof(float), cudaMemcpyHostToDevice, st));
+        q_src = dst;
     }
-    // device queries that need no padding, normalisation or zero-filled spare slots are used in place
-    const bool q_in_place = !use_gemm && q_mem_kind == B200R_DEVICE && ix->d == ix->d_pad &&
-                            !ix->cfg.normalize_queries && (nq == 1 || nq % kScanMaxNQ == 0) &&
-                            (reinterpret_cast<uintptr_t>(q) & 15) == 0;
     const float* q_ready = ix->q_dev;
     if (q_in_place) {
         q_ready = (const float*)q;
+    } else if (q_direct) {
+        // nothing to do: q_dev holds the queries
     } else {
         CU(launch_prep_queries(q_src, nq, ix->d, ix->d_pad, nq_slots, ix->cfg.normalize_queries != 0, ix->q_dev, st));
         ix->st.n_kernel_launches++;
     }
 
-    float* od = out_mem_kind == B200R_DEVICE ? D : ix->out_d;
-    int64_t* oi = out_mem_kind == B200R_DEVICE ? I : ix->out_i;
+    // host outputs: scores and ids packed for this nq*k so that one copy brings both back
+    const size_t ids_off = round_up((size_t)nq * k * sizeof(float), 16);
+    float* od = out_mem_kind == B200R_DEVICE ? D : reinterpret_cast<float*>(ix->out_buf);
+    int64_t* oi = out_mem_kind == B200R_DEVICE ? I : reinterpret_cast<int64_t*>(ix->out_buf + ids_off);
 
     const bool use_shadow = use_gemm && ix->shadow && ix->shadow_on;
     int* fail_count = filtered ? ix->fail_dev + ix->fail_cap : nullptr;
@@ -715,10 +723,9 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
 
     if (out_mem_kind == B200R_HOST) {
         float* pd = (float*)ix->out_pin;
-        int64_t* pi = (int64_t*)(ix->out_pin + round_up((size_t)nq * k * sizeof(float), 16));
-        // out_pin holds cap*(4+8)+64 bytes, so the 16-byte rounding always fits
-        CU(cudaMemcpyAsync(pd, ix->out_d, (size_t)nq * k * sizeof(float), cudaMemcpyDeviceToHost, st));
-        CU(cudaMemcpyAsync(pi, ix->out_i, (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        int64_t* pi = (int64_t*)(ix->out_pin + ids_off);
+        // out_buf / out_pin hold cap*(4+8)+64 bytes, so the 16-byte rounding always fits
+        CU(cudaMemcpyAsync(ix->out_pin, ix->out_buf, ids_off + (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
         memcpy(D, pd, (size_t)nq * k * sizeof(float));
         memcpy(I, pi, (size_t)nq * k * sizeof(int64_t));
