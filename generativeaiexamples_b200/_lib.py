@@ -63,6 +63,7 @@ SIGNATURES = {
                                      _vp]),
     "b200r_set_id_base": (_int, [_vp, _i64]),
     "b200r_stats_get": (_int, [_vp, ctypes.POINTER(Stats)]),
+    "b200r_merge_from": (_int, [_vp, _vp]),
     "b200r_set_shadow_filter": (_int, [_vp, _i32]),
     "b200r_set_timing": (_int, [_vp, _i32]),
     "b200r_last_error": (ctypes.c_char_p, []),

@@ -914,6 +914,64 @@ extern "C" int b200r_reconstruct_batch(b200r_index* ix, const int64_t* keys, int
 }
 
 // ---------------------------------------------------------------------------
+// merge_from: append another index's rows, empty the other index
+// ---------------------------------------------------------------------------
+extern "C" int b200r_merge_from(b200r_index* dst, b200r_index* src) {
+    if (!dst || !src) return fail(B200R_E_INVALID, "b200r_merge_from: null index");
+    if (dst == src) return fail(B200R_E_INVALID, "b200r_merge_from: an index cannot be merged into itself");
+    // faiss check_compatible_for_merge: same d, metric and index type (here also the storage and the GPU)
+    if (dst->d != src->d || dst->l2 != src->l2 || dst->bf16 != src->bf16)
+        return fail(B200R_E_INVALID, "b200r_merge_from: indexes are not compatible (dim %d/%d, metric or storage differ)",
+                    dst->d, src->d);
+    if (dst->device != src->device)
+        return fail(B200R_E_UNSUPPORTED, "b200r_merge_from: indexes live on different GPUs (%d, %d)", dst->device, src->device);
+    std::scoped_lock lk(dst->mu, src->mu);
+    const int64_t n = src->ntotal;
+    if (n == 0) return B200R_OK;
+    DeviceGuard g(dst->device);
+    cudaStream_t st = dst->stream;
+    if (src->data_ev_set) CU(cudaStreamWaitEvent(st, src->data_ev, 0));
+    if (dst->data_ev_set) CU(cudaStreamWaitEvent(st, dst->data_ev, 0));
+    int rc = ensure_capacity(dst, dst->ntotal + n, st);
+    if (rc != B200R_OK) return rc;
+    // The stored rows go through fp32 and the ingest kernel again (without normalisation): exact
+    // for both storages (bf16 -> fp32 -> bf16 is the identity), it re-pads rows whose padding
+    // differs between the two indexes and fills the norms and the bf16 shadow in the same pass.
+    const int64_t chunk = std::max<int64_t>(1, (int64_t)((64u << 20) / ((size_t)dst->d * sizeof(float))));
+    float* tmp = nullptr;
+    cudaError_t e = cudaMalloc(&tmp, (size_t)std::min(chunk, n) * dst->d * sizeof(float));
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(B200R_E_NOMEM, "b200r_merge_from: staging buffer: %s", cudaGetErrorString(e));
+    }
+    for (int64_t r0 = 0; r0 < n && e == cudaSuccess; r0 += chunk) {
+        const int64_t m = std::min(chunk, n - r0);
+        e = launch_rows_to_f32(src->rows + (size_t)r0 * src->row_bytes, src->row_bytes, src->d, src->bf16, nullptr, m, tmp, st);
+        if (e == cudaSuccess)
+            e = launch_ingest(tmp, m, dst->d, dst->d_pad, false, dst->bf16,
+                              dst->rows + (size_t)(dst->ntotal + r0) * dst->row_bytes, dst->norms + dst->ntotal + r0, st);
+        if (e == cudaSuccess && dst->shadow)
+            e = launch_ingest(tmp, m, dst->d, dst->d_pad, false, true,
+                              dst->shadow + (size_t)(dst->ntotal + r0) * dst->d_pad * 2, nullptr, st);
+        dst->st.n_kernel_launches += dst->shadow ? 3 : 2;
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(tmp);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(B200R_E_CUDA, "b200r_merge_from: %s", cudaGetErrorString(e));
+    }
+    dst->ntotal += n;
+    dst->max_norm_dirty = true;
+    dst->st.n_rows_added += n;
+    dst->data_ev_set = false;
+    src->ntotal = 0;  // faiss: the other index is reset
+    src->max_norm_dirty = true;
+    src->data_ev_set = false;
+    return B200R_OK;
+}
+
+// ---------------------------------------------------------------------------
 // stand-alone normalise and merge
 // ---------------------------------------------------------------------------
 extern "C" int b200r_normalize_l2(float* x, int64_t n, int32_t d, int mem_kind, int32_t device, void* stream) {

@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(kRowWarps * 32) rows_to_f32_kernel(const uint8
     const int lane = threadIdx.x & 31;
     const int64_t i = (int64_t)blockIdx.x * kRowWarps + (threadIdx.x >> 5);
     if (i >= n) return;
-    const uint8_t* r = rows + ids[i] * (int64_t)row_bytes;
+    const uint8_t* r = rows + (ids ? ids[i] : i) * (int64_t)row_bytes;  // no id list: rows 0..n-1 in order
     for (int j = lane; j < d; j += 32)
         out[i * d + j] = bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(r)[j])
                               : reinterpret_cast<const float*>(r)[j];

@@ -197,6 +197,13 @@ class B200IndexFlat:
         assert st["ntotal"] >= 0
         return self
 
+    def merge_from(self, other: "B200IndexFlat", add_id: int = 0) -> None:
+        """faiss ``index.merge_from(other)``: append ``other``'s vectors and empty ``other`` (``add_id`` is
+        unused by flat indexes, as in faiss)."""
+        if not isinstance(other, B200IndexFlat):
+            raise TypeError("merge_from needs another B200IndexFlat")
+        _lib.check(self._L.b200r_merge_from(self._h, other._h))
+
     # -- engine extras --------------------------------------------------------
     def set_id_base(self, base: int) -> None:
         _lib.check(self._L.b200r_set_id_base(self._h, int(base)))

@@ -503,6 +503,24 @@ class B200FlatVectorStore(_VSBase):
         return True
 
     # -- constructors ---------------------------------------------------------------------
+    def merge_from(self, target: "B200FlatVectorStore") -> None:
+        """LangChain ``FAISS.merge_from`` (reference caller: community/oran-chatbot-multimodal/vectorstore/
+        vectorstore_updater.py:217): the target's vectors and documents are appended; its index is left empty."""
+        if target.index is None or target.index.ntotal == 0:
+            return
+        if self.index is None:
+            self.index = self._new_index(int(target.index.d))
+        starting_len = len(self.index_to_docstore_id)
+        self.index.merge_from(target.index)
+        full_info = []
+        for i, target_id in target.index_to_docstore_id.items():
+            doc = target.docstore.search(target_id)
+            if not isinstance(doc, Document):
+                raise ValueError("Document should be returned")
+            full_info.append((starting_len + i, target_id, doc))
+        self.docstore.add({_id: doc for _, _id, doc in full_info})
+        self.index_to_docstore_id.update({index: _id for index, _id, _ in full_info})
+
     @classmethod
     def from_embeddings(cls, text_embeddings: Iterable[Tuple[str, List[float]]], embedding,
                         metadatas: Optional[List[dict]] = None, ids: Optional[List[str]] = None,

@@ -193,6 +193,12 @@ int64_t b200r_exchange_buffer_bytes(void);
 int b200r_search_exchange(b200r_index* idx, const float* q, int64_t nq, int k, void* const* peer_bufs, int32_t world,
                           int32_t rank, uint32_t epoch, float* D, int64_t* I, void* stream);
 
+/* index.merge_from(other)   [faiss 1.7.4 IndexFlatCodes::merge_from, reached through LangChain's
+ * FAISS.merge_from: community/oran-chatbot-multimodal/vectorstore/vectorstore_updater.py:217]
+ * Appends src's rows to dst (positions dst.ntotal ...) and empties src.  Both must have the same
+ * dim, metric and storage (faiss: check_compatible_for_merge) and live on the same GPU. */
+int b200r_merge_from(b200r_index* dst, b200r_index* src);
+
 /* row-sharding support: change the id offset after the shard layout moved */
 int b200r_set_id_base(b200r_index* idx, int64_t id_base);
 

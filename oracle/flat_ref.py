@@ -161,6 +161,14 @@ class IndexFlatRef:
     def reset(self):
         self._codes = np.empty((0, self.d), dtype=np.float32)
 
+    def merge_from(self, other, add_id=0):
+        """faiss 1.7.4 IndexFlatCodes::merge_from (check_compatible_for_merge: same d, metric, type): the other
+        index's codes are appended and the other index is emptied; add_id is unused by flat indexes."""
+        if not isinstance(other, IndexFlatRef) or other.d != self.d or other.metric_type != self.metric_type:
+            raise RuntimeError("merge_from: indexes are not compatible")
+        self._codes = np.concatenate([self._codes, other._codes], axis=0)
+        other.reset()
+
 
 def IndexFlatL2Ref(d):
     return IndexFlatRef(d, METRIC_L2)

@@ -230,6 +230,20 @@ class RefFAISS:
         self.index_to_docstore_id = {i: id_ for i, id_ in enumerate(remaining_ids)}
         return True
 
+    # -- merge_from (langchain_community FAISS.merge_from; reference caller:
+    #    community/oran-chatbot-multimodal/vectorstore/vectorstore_updater.py:217) --------------------
+    def merge_from(self, target: "RefFAISS") -> None:
+        starting_len = len(self.index_to_docstore_id)
+        self.index.merge_from(target.index)
+        full_info = []
+        for i, target_id in target.index_to_docstore_id.items():
+            doc = target.docstore.search(target_id)
+            if not isinstance(doc, RefDocument):
+                raise ValueError("Document should be returned")
+            full_info.append((starting_len + i, target_id, doc))
+        self.docstore.add({_id: doc for _, _id, doc in full_info})
+        self.index_to_docstore_id.update({index: _id for index, _id, _ in full_info})
+
     # -- retriever ------------------------------------------------------------
     def retrieve(self, query, search_type="similarity", search_kwargs=None):
         """VectorStoreRetriever._get_relevant_documents"""

@@ -898,3 +898,74 @@ def test_randomised_mutation_sequences(built_lib, seed, monkeypatch):
         j = int(rng.integers(0, model.shape[0]))
         np.testing.assert_array_equal(ix.reconstruct(j), model[j])
     ix.close()
+
+
+def test_merge_from(built_lib, monkeypatch):
+    """index.merge_from / FAISS.merge_from (vectorstore_updater.py:217) against the restatement."""
+    import zlib
+
+    from generativeaiexamples_b200 import B200FlatVectorStore, B200IndexFlat
+    from oracle import IndexFlatRef
+    from oracle.lc_faiss_shim import RefDocstore, RefFAISS
+
+    rng = np.random.default_rng(95)
+    for d, kw_dst, kw_src in ((100, dict(shadow_bf16=True), dict()), (64, dict(), dict(shadow_bf16=True)),
+                              (257, dict(storage="bf16"), dict(storage="bf16")), (1024, dict(), dict())):
+        xa = rng.standard_normal((3000, d), dtype=np.float32)
+        xb = rng.standard_normal((1234, d), dtype=np.float32)
+        if kw_dst.get("storage") == "bf16":
+            import torch
+
+            xa = torch.from_numpy(xa).to(torch.bfloat16).to(torch.float32).numpy()
+            xb = torch.from_numpy(xb).to(torch.bfloat16).to(torch.float32).numpy()
+        for metric in (0, 1):
+            a, b = B200IndexFlat(d, metric, **kw_dst), B200IndexFlat(d, metric, **kw_src)
+            ra, rb = IndexFlatRef(d, metric), IndexFlatRef(d, metric)
+            for ix, x in ((a, xa), (ra, xa), (b, xb), (rb, xb)):
+                ix.add(x)
+            a.merge_from(b)
+            ra.merge_from(rb)
+            assert a.ntotal == ra.ntotal == 4234 and b.ntotal == rb.ntotal == 0
+            np.testing.assert_array_equal(a.reconstruct(3000 + 77), xb[77])
+            q = np.concatenate([xa[:3], xb[:3]]) + 0.01 * rng.standard_normal((6, d), dtype=np.float32)
+            for nq in (1, 6):  # scan and GEMM routes
+                D, I = a.search(q[:nq], 5)
+                _check("l2" if metric == 1 else "ip", D, I, q[:nq], np.concatenate([xa, xb]), 5, f"merge_from d={d} {kw_dst}")
+            b.add(xa[:10])  # the emptied index stays usable
+            assert b.search(xa[:1], 1)[1][0, 0] == 0
+            a.close()
+            b.close()
+    x = B200IndexFlat(16, 1)
+    with pytest.raises(RuntimeError):
+        x.merge_from(B200IndexFlat(16, 0))
+    with pytest.raises(RuntimeError):
+        x.merge_from(B200IndexFlat(17, 1))
+    with pytest.raises(RuntimeError):
+        x.merge_from(B200IndexFlat(16, 1, storage="bf16"))
+    with pytest.raises(RuntimeError):
+        x.merge_from(x)
+
+    # the LangChain surface
+    def emb(t):
+        return np.random.default_rng(zlib.crc32(t.encode())).standard_normal(64).astype(np.float32).tolist()
+
+    class E:
+        def embed_documents(self, ts):
+            return [emb(t) for t in ts]
+
+        def embed_query(self, t):
+            return emb(t)
+
+    s1, s2 = B200FlatVectorStore(E(), 64), B200FlatVectorStore(E(), 64)
+    r1, r2 = RefFAISS(emb, IndexFlatRef(64), RefDocstore(), {}), RefFAISS(emb, IndexFlatRef(64), RefDocstore(), {})
+    t1, t2 = [f"first {i}" for i in range(40)], [f"second {i}" for i in range(25)]
+    for s, t in ((s1, t1), (r1, t1), (s2, t2), (r2, t2)):
+        s.add_texts(t)
+    s1.merge_from(s2)
+    r1.merge_from(r2)
+    assert s1.index.ntotal == 65 and sorted(s1.index_to_docstore_id) == list(range(65))
+    for qt in ("second 7", "first 3", "something else"):
+        got = [(d_.page_content, float(sc)) for d_, sc in s1.similarity_search_with_score(qt, k=4)]
+        want = [(d_.page_content, float(sc)) for d_, sc in r1.similarity_search_with_score(qt, k=4)]
+        assert [g[0] for g in got] == [w[0] for w in want]
+        np.testing.assert_allclose([g[1] for g in got], [w[1] for w in want], rtol=1e-5, atol=1e-5)

@@ -184,3 +184,36 @@ def test_restatement_matches_independent_bruteforce(nq):
     scale = float((q.astype(np.float64) ** 2).sum(1).max() + (x.astype(np.float64) ** 2).sum(1).max()) if nq >= 20 else 1.0
     assert_topk_parity(D, I, (dist ** 2).astype(np.float32), ids.astype(np.int64), what="restatement vs sklearn brute force",
                        scale=scale)
+
+
+def test_merge_from_restatement():
+    """faiss IndexFlatCodes::merge_from + LangChain FAISS.merge_from (vectorstore_updater.py:217)."""
+    rng = np.random.default_rng(12)
+    a, b = IndexFlatRef(8, METRIC_L2), IndexFlatRef(8, METRIC_L2)
+    xa, xb = rng.standard_normal((5, 8)).astype(np.float32), rng.standard_normal((3, 8)).astype(np.float32)
+    a.add(xa)
+    b.add(xb)
+    a.merge_from(b)
+    assert a.ntotal == 8 and b.ntotal == 0
+    np.testing.assert_array_equal(a.reconstruct(6), xb[1])
+    with pytest.raises(RuntimeError):
+        a.merge_from(IndexFlatRef(8, METRIC_INNER_PRODUCT))
+    with pytest.raises(RuntimeError):
+        a.merge_from(IndexFlatRef(9, METRIC_L2))
+
+    def emb(t):
+        return np.random.default_rng(zlib_crc(t)).standard_normal(8).astype(np.float32).tolist()
+
+    import zlib
+
+    def zlib_crc(t):
+        return zlib.crc32(t.encode())
+
+    s1 = RefFAISS(emb, IndexFlatRef(8), RefDocstore(), {})
+    s2 = RefFAISS(emb, IndexFlatRef(8), RefDocstore(), {})
+    s1.add_texts(["a", "b", "c"])
+    s2.add_texts(["d", "e"])
+    s1.merge_from(s2)
+    assert s1.index.ntotal == 5 and sorted(s1.index_to_docstore_id) == [0, 1, 2, 3, 4]
+    assert s1.similarity_search("e", k=1)[0].page_content == "e"
+    assert s1.similarity_search("a", k=1)[0].page_content == "a"
