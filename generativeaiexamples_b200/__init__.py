@@ -15,5 +15,6 @@ from .vectorstore import (  # noqa: F401
     B200FlatVectorStore, DistanceStrategy, Document, InMemoryDocstore, VectorStoreRetriever,
 )
 from .factory import create_vectorstore_langchain, get_vectorstore  # noqa: F401
+from .service import B200VectorDBResourceService  # noqa: F401
 
 __version__ = "0.1.0"

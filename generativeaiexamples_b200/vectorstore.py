@@ -78,6 +78,10 @@ except Exception:
         def __repr__(self):
             return f"Document(page_content={self.page_content!r}, metadata={self.metadata!r})"
 
+        def dict(self) -> dict:
+            """pydantic's ``Document.dict()`` (used by faiss_vdb_service.py:172)."""
+            return {"page_content": self.page_content, "metadata": self.metadata, "type": "Document"}
+
     class _VSBase:
         pass
 

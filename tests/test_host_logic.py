@@ -288,3 +288,31 @@ def test_to_matrix_fast_paths_match_numpy():
     with pytest.raises(ValueError):
         _to_matrix([[1.0, 2.0], [3.0]])
     np.testing.assert_array_equal(_to_matrix([[1, 2], [3, 4]]), np.array([[1, 2], [3, 4]], dtype=np.float32))
+
+
+def test_morpheus_service_mirror(tmp_path):
+    """faiss_vdb_service.py:147-174: async similarity_search(embeddings, k) -> list[list[Document.dict()]];
+    every other operation raises NotImplementedError, as in the reference."""
+    from generativeaiexamples_b200 import B200VectorDBResourceService
+
+    ours, ref = _pair()
+    e = Emb()
+    pairs = [(f"t{i}", e._v(f"t{i}")) for i in range(30)]
+    ours.add_embeddings(pairs, metadatas=[{"n": i} for i in range(30)])
+    ref.add_embeddings(pairs, metadatas=[{"n": i} for i in range(30)])
+    svc = B200VectorDBResourceService(ours)
+    embs = [e._v(f"t{i}") for i in (3, 7, 11)] + [e._v("unseen")]
+    got = asyncio.run(svc.similarity_search(embs, k=3))
+    want = [[{"page_content": d.page_content, "metadata": d.metadata, "type": "Document"}
+             for d in ref.similarity_search_by_vector(v, k=3)] for v in embs]
+    assert got == want
+    assert got[0][0]["page_content"] == "t3" and got[1][0]["metadata"] == {"n": 7}
+    assert asyncio.run(svc.similarity_search([], k=3)) == []
+    assert svc.ntotal == 30
+    for call in (lambda: svc.insert([[0.0]]), lambda: svc.insert_dataframe(None), svc.describe, lambda: svc.query("x"),
+                 lambda: svc.update([]), lambda: svc.delete_by_keys(1), lambda: svc.delete("x"),
+                 lambda: svc.retrieve_by_keys(1), svc.count, svc.drop):
+        with pytest.raises(NotImplementedError, match="not supported in FAISS"):
+            call()
+    empty = B200VectorDBResourceService(B200FlatVectorStore(Emb(), None))
+    assert asyncio.run(empty.similarity_search(embs[:2], k=3)) == [[], []]
