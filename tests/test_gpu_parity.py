@@ -969,3 +969,32 @@ def test_merge_from(built_lib, monkeypatch):
         want = [(d_.page_content, float(sc)) for d_, sc in r1.similarity_search_with_score(qt, k=4)]
         assert [g[0] for g in got] == [w[0] for w in want]
         np.testing.assert_allclose([g[1] for g in got], [w[1] for w in want], rtol=1e-5, atol=1e-5)
+
+
+def test_service_mirror_on_engine(built_lib, tmp_path):
+    """faiss_vdb_service.py:63-66,147-174 on the real engine: load_local, then one batched launch per call."""
+    import asyncio
+    import zlib
+
+    from generativeaiexamples_b200 import B200FlatVectorStore, B200VectorDBResourceService
+
+    def emb(t):
+        v = np.random.default_rng(zlib.crc32(t.encode())).standard_normal(96)
+        return (v / np.linalg.norm(v)).tolist()
+
+    class E:
+        def embed_documents(self, ts):
+            return [emb(t) for t in ts]
+
+        def embed_query(self, t):
+            return emb(t)
+
+    vs = B200FlatVectorStore.from_texts([f"doc {i}" for i in range(500)], E(), metadatas=[{"i": i} for i in range(500)])
+    vs.save_local(str(tmp_path), index_name="code")
+    svc = B200VectorDBResourceService.load(str(tmp_path), E(), name="code")
+    assert svc.ntotal == 500
+    res = asyncio.run(svc.similarity_search([emb(f"doc {i}") for i in (5, 250, 499)] + [emb("nothing like it")], k=4))
+    assert [r[0]["page_content"] for r in res[:3]] == ["doc 5", "doc 250", "doc 499"]
+    assert res[1][0]["metadata"] == {"i": 250} and all(len(r) == 4 for r in res)
+    single = [d.page_content for d in vs.similarity_search_by_vector(emb("nothing like it"), k=4)]
+    assert [d["page_content"] for d in res[3]] == single
