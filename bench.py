@@ -450,7 +450,7 @@ def main_gpu(args):
         from generativeaiexamples_b200.batching import SearchCoalescer
 
         co = SearchCoalescer(index.local)
-        nreq = args.concurrent * 8
+        nreq = args.concurrent * 24
 
         def one(i):
             return co.search(Qh[i % pool: i % pool + 1], TOPK)

@@ -8,11 +8,15 @@ i.e. B threads each running an nq=1 ``index.search``.  On a CPU that is how fais
 parallelism; on the GPU it would serialise B full corpus scans.  ``SearchCoalescer`` sits between
 the store and the index: while one search is in flight the requests that arrive are queued, and
 the next launch serves all of them as ONE nq=B search (the tensor-core path from B >= 5).  An idle
-coalescer adds no waiting: the first request starts immediately.
+coalescer adds no waiting: the first request starts immediately.  After a batch that served several
+callers the drain loop lingers for a few per cent of that batch's duration (at most 0.5 ms) before it
+forms the next one: the callers it has just released are about to come back, and without the pause
+they alternate between two half-size batches (64 callers: 2 x 32 per corpus pass instead of 64).
 """
 from __future__ import annotations
 
 import threading
+import time
 from typing import List, Optional, Tuple
 
 import numpy as np
@@ -28,9 +32,11 @@ class _Request:
 
 
 class SearchCoalescer:
-    def __init__(self, index, max_batch: int = 256):
+    def __init__(self, index, max_batch: int = 256, linger_frac: float = 0.03, max_linger_s: float = 5e-4):
         self.index = index
         self.max_batch = int(max_batch)
+        self.linger_frac = float(linger_frac)
+        self.max_linger_s = float(max_linger_s)
         self._lock = threading.Lock()
         self._pending: List[_Request] = []
         self._busy = False
@@ -64,6 +70,7 @@ class SearchCoalescer:
                 batch = [r for r in self._pending if r.k == k][: self.max_batch]
                 taken = set(map(id, batch))
                 self._pending = [r for r in self._pending if id(r) not in taken]
+            t0 = time.perf_counter()
             try:
                 Q = np.concatenate([r.vec for r in batch], axis=0)
                 D, I = self.index.search(Q, k)
@@ -76,3 +83,5 @@ class SearchCoalescer:
             finally:
                 for r in batch:
                     r.done.set()
+            if len(batch) > 1 and self.linger_frac > 0:
+                time.sleep(min(self.max_linger_s, self.linger_frac * (time.perf_counter() - t0)))
