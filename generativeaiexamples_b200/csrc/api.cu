@@ -61,12 +61,13 @@ struct DeviceGuard {
 // ---------------------------------------------------------------------------
 constexpr size_t kStageHalfBytes = 32u << 20;  // pinned / device staging, per half
 constexpr int64_t kMaxRows = 0xFFFFFFFEll;     // ids are 32-bit inside the kernels
-// corpus sizes from which small batches go to the GEMM path (measured crossovers, tools/perf_small_nq.py:
-// 2..4 queries from ~200k x 1024 fp32 rows; a single query on the bf16 shadow from ~375k rows)
-constexpr int64_t kGemmSmallBatchBytes = 768ll << 20;
-constexpr int64_t kGemmShadowSingleBytes = 1536ll << 20;
-constexpr int64_t kGemmBf16SmallBatchBytes = 100ll << 20;  // bf16 storage: 2..4 queries from ~50k x 1024 rows
-constexpr int64_t kGemmBf16SingleBytes = 2048ll << 20;     // bf16 storage: one query from ~1M x 1024 rows
+// corpus sizes from which small batches go to the GEMM path (measured crossovers with the device-side
+// fallback in place, tools/perf_small_nq.py / perf_bf16_small.py: 2..4 queries from ~110k x 1024 fp32 rows;
+// a single query on the bf16 shadow or on bf16 rows from ~250k / ~500k rows)
+constexpr int64_t kGemmSmallBatchBytes = 448ll << 20;
+constexpr int64_t kGemmShadowSingleBytes = 1024ll << 20;
+constexpr int64_t kGemmBf16SmallBatchBytes = 64ll << 20;
+constexpr int64_t kGemmBf16SingleBytes = 1024ll << 20;
 
 struct b200r_index {
     b200r_config cfg{};
@@ -89,6 +90,12 @@ struct b200r_index {
     cudaEvent_t data_ev = nullptr;
     bool data_ev_set = false;
     cudaStream_t data_ev_stream = nullptr;
+    // last user of the search workspace (query slots, candidate scratch, tickets, ...): a search
+    // enqueued on another stream waits for it, so asynchronous searches on different streams
+    // never overlap on the shared buffers
+    cudaEvent_t ws_ev = nullptr;
+    bool ws_ev_set = false;
+    cudaStream_t ws_ev_stream = nullptr;
     // add(): double-buffered host->device staging
     uint8_t* pin_add = nullptr;
     uint8_t* dev_add = nullptr;
@@ -120,16 +127,24 @@ struct b200r_index {
     // K' multiplier in percent: raised after a search whose containment check failed for some
     // query (corpus with many near-ties), so the next batches filter with more slack
     int kp_boost = 100;
-    // scan-path fallback of flagged queries, four per corpus pass: gathered queries / their results
-    float* fb_q = nullptr;
-    float* fb_d = nullptr;
-    int64_t* fb_i = nullptr;
+    // device-side fallback of flagged queries (launch_scan_flagged): compacted positions + their number
+    int* flag_dev = nullptr;       // [fail_cap] list + 1 count at the end
+    // the number of flagged queries of recent searches comes back asynchronously (statistics and the
+    // K' boost only): a small ring of pinned words, each with the event that says it has landed
+    static constexpr int kFbRing = 8;
+    int* fb_pin = nullptr;         // [kFbRing]
+    cudaEvent_t fb_ev[kFbRing] = {};
+    bool fb_pending[kFbRing] = {};
+    int64_t fb_pass_bytes[kFbRing] = {};  // corpus bytes one fallback pass streams
+    int fb_per_pass[kFbRing] = {};        // flagged queries one pass serves
+    int fb_next = 0;
 
     std::mutex mu;
     b200r_stats st{};
 };
 
 static int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+static void fold_fallback_counts(b200r_index* ix, bool wait);
 
 // pageable -> pinned staging copy; one core moves ~12 GB/s, PCIe Gen5 takes ~50, so large
 // copies are split over a few threads (at most half the cores)
@@ -232,12 +247,14 @@ static void free_index(b200r_index* ix) {
     cudaFree(ix->gemm_aux);
     cudaFree(ix->fail_dev);
     cudaFreeHost(ix->fail_pin);
-    cudaFree(ix->fb_q);
-    cudaFree(ix->fb_d);
-    cudaFree(ix->fb_i);
+    cudaFree(ix->flag_dev);
+    cudaFreeHost(ix->fb_pin);
+    for (auto& e : ix->fb_ev)
+        if (e) cudaEventDestroy(e);
     for (auto& e : ix->add_ev)
         if (e) cudaEventDestroy(e);
     if (ix->data_ev) cudaEventDestroy(ix->data_ev);
+    if (ix->ws_ev) cudaEventDestroy(ix->ws_ev);
     if (ix->t0) cudaEventDestroy(ix->t0);
     if (ix->t1) cudaEventDestroy(ix->t1);
     if (ix->stream) cudaStreamDestroy(ix->stream);
@@ -308,6 +325,7 @@ extern "C" int b200r_create(const b200r_config* cfg, b200r_index** out) {
     CU_OR_FREE(cudaEventCreateWithFlags(&ix->add_ev[0], cudaEventDisableTiming));
     CU_OR_FREE(cudaEventCreateWithFlags(&ix->add_ev[1], cudaEventDisableTiming));
     CU_OR_FREE(cudaEventCreateWithFlags(&ix->data_ev, cudaEventDisableTiming));
+    CU_OR_FREE(cudaEventCreateWithFlags(&ix->ws_ev, cudaEventDisableTiming));
     CU_OR_FREE(cudaEventCreate(&ix->t0));
     CU_OR_FREE(cudaEventCreate(&ix->t1));
     CU_OR_FREE(cudaMalloc(&ix->scratch, scan_scratch_bytes(ix->num_sms)));
@@ -360,6 +378,10 @@ extern "C" int b200r_set_timing(b200r_index* ix, int32_t enabled) {
 extern "C" int b200r_stats_get(b200r_index* ix, b200r_stats* out) {
     if (!ix || !out) return fail(B200R_E_INVALID, "b200r_stats_get: null argument");
     std::lock_guard<std::mutex> lk(ix->mu);
+    {
+        DeviceGuard g(ix->device);
+        fold_fallback_counts(ix, true);
+    }
     ix->st.ntotal = ix->ntotal;
     ix->st.capacity_rows = ix->capacity;
     *out = ix->st;
@@ -493,9 +515,8 @@ static int ensure_gemm_ws(b200r_index* ix, int64_t nq, int k, cudaStream_t st) {
         ix->gemm_cand_bytes = need;
     }
     if (!ix->max_norm_bits) {
-        CU(cudaMalloc(&ix->fb_q, (size_t)kScanMaxNQ * ix->d_pad * sizeof(float)));
-        CU(cudaMalloc(&ix->fb_d, (size_t)kScanMaxNQ * kScanMaxK * sizeof(float)));
-        CU(cudaMalloc(&ix->fb_i, (size_t)kScanMaxNQ * kScanMaxK * sizeof(int64_t)));
+        CU(cudaMallocHost(&ix->fb_pin, b200r_index::kFbRing * sizeof(int)));
+        for (auto& e : ix->fb_ev) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         CU(cudaMalloc(&ix->max_norm_bits, 256));
         CU(cudaMalloc(&ix->gemm_aux, gemm_aux_bytes()));
         ix->max_norm_dirty = true;
@@ -507,16 +528,41 @@ static int ensure_gemm_ws(b200r_index* ix, int64_t nq, int k, cudaStream_t st) {
     }
     if (nq > ix->fail_cap) {
         cudaFree(ix->fail_dev);
+        cudaFree(ix->flag_dev);
         cudaFreeHost(ix->fail_pin);
         ix->fail_dev = nullptr;
+        ix->flag_dev = nullptr;
         ix->fail_pin = nullptr;
         ix->fail_cap = 0;
         const int64_t cap = std::max<int64_t>(nq, 1024);
         CU(cudaMalloc(&ix->fail_dev, (size_t)(cap + 1) * sizeof(int)));
+        CU(cudaMalloc(&ix->flag_dev, (size_t)(cap + 1) * sizeof(int)));
         CU(cudaMallocHost(&ix->fail_pin, (size_t)(cap + 1) * sizeof(int)));
         ix->fail_cap = cap;
     }
     return B200R_OK;
+}
+
+// Flagged-query counts of earlier searches that have arrived by now (or all of them, waiting):
+// statistics, and the K' boost for the searches that follow.
+static void fold_fallback_counts(b200r_index* ix, bool wait) {
+    for (int sl = 0; sl < b200r_index::kFbRing; sl++) {
+        if (!ix->fb_pending[sl]) continue;
+        if (wait) {
+            cudaEventSynchronize(ix->fb_ev[sl]);
+        } else if (cudaEventQuery(ix->fb_ev[sl]) != cudaSuccess) {
+            cudaGetLastError();  // cudaErrorNotReady is not an error
+            continue;
+        }
+        const int cnt = ix->fb_pin[sl];
+        ix->fb_pending[sl] = false;
+        if (cnt <= 0) continue;
+        ix->st.n_gemm_fallbacks += cnt;
+        const int per = std::max(1, ix->fb_per_pass[sl]);
+        ix->st.bytes_scanned += (int64_t)((cnt + per - 1) / per) * ix->fb_pass_bytes[sl];
+        if (!getenv("B200R_GEMM_NOBOOST"))  // (tuning knob: keep K' fixed)
+            ix->kp_boost = std::min(400, ix->kp_boost * 3 / 2);
+    }
 }
 
 extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
@@ -539,7 +585,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     // at nq = 20 (distance_compute_blas_threshold).  Here one GEMM pass streams the corpus at
     // ~6.9 TB/s whatever nq <= 128 is, while the scan kernel is FMA-bound beyond one query
     // (10M x 1024 fp32: 5.7 ms for nq = 1, 9.5-10.1 ms for nq = 2..4; GEMM 5.9-6.2 ms), so on a
-    // corpus large enough to hide the GEMM path's extra launches and its flag read-back the GEMM
+    // corpus large enough to hide the GEMM path's extra launches the GEMM
     // takes over at nq = 2 -- and at nq = 1 when it can filter on the bf16 shadow (3.0 ms).
     // Small corpora keep the scan up to nq = 4.  Both paths end in the same fp32 scoring code, so
     // the choice never changes a result.
@@ -556,6 +602,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
         if (corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmBf16SingleBytes)) gemm_min = 1;
     }
     if (env_thr) gemm_min = atoll(env_thr);
+    fold_fallback_counts(ix, false);  // may raise the K' boost used below
     const bool use_gemm = ix->ntotal > 0 && (ix->cfg.search_path == B200R_PATH_GEMM ||
                                              (ix->cfg.search_path == B200R_PATH_AUTO && nq >= gemm_min));
     const int64_t nq_slots = use_gemm ? round_up(nq, 128) : round_up(nq, kScanMaxNQ);
@@ -568,6 +615,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     }
 
     if (ix->data_ev_set && ix->data_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->data_ev, 0));
+    if (ix->ws_ev_set && ix->ws_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->ws_ev, 0));
     if (ix->timing) CU(cudaEventRecord(ix->t0, st));
     const float* q_src = (const float*)q;
     // queries that need no padding, normalisation or zero-filled spare slots skip the prep kernel:
@@ -636,25 +684,6 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
         ix->st.last_path = B200R_PATH_GEMM;
         ix->st.last_grid = ix->num_sms;
     }
-    if (filtered) {
-        // the containment check is read back: one small D2H + sync per search
-        CU(cudaMemcpyAsync(ix->fail_pin, ix->fail_dev, (size_t)(ix->fail_cap + 1) * sizeof(int), cudaMemcpyDeviceToHost,
-                           st));
-        CU(cudaStreamSynchronize(st));
-        ix->st.n_gemm_fallbacks += ix->fail_pin[ix->fail_cap];
-        if (ix->fail_pin[ix->fail_cap] > 0 && !getenv("B200R_GEMM_NOBOOST"))  // (tuning knob: keep K' fixed)
-            ix->kp_boost = std::min(400, ix->kp_boost * 3 / 2);
-        if (getenv("B200R_DEBUG_FAILS") && ix->fail_pin[ix->fail_cap]) {
-            int cause[4] = {0, 0, 0, 0};
-            for (int64_t i = 0; i < nq; i++) cause[ix->fail_pin[i] & 3]++;
-            fprintf(stderr, "[b200r] gemm fallbacks: check=%d bucket=%d slice=%d; first failing queries:", cause[1], cause[2], cause[3]);
-            int shown = 0;
-            for (int64_t i = 0; i < nq && shown < 40; i++)
-                if (ix->fail_pin[i]) { fprintf(stderr, " %lld", (long long)i); shown++; }
-            fprintf(stderr, "\n");
-        }
-    }
-
     ScanParams p{};
     p.corpus = ix->rows;
     p.n_rows = ix->ntotal;
@@ -681,41 +710,45 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
             ix->st.last_grid = grid;
             ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
         }
-    } else if (ix->fail_pin[ix->fail_cap] > 0) {
-        // after a GEMM pass only the flagged queries are scanned: gathered scan_step at a time so
-        // that one corpus pass serves up to four of them
-        std::vector<int64_t> flagged;
-        for (int64_t i = 0; i < nq; i++)
-            if (ix->fail_pin[i]) flagged.push_back(i);
-        const size_t qb = (size_t)ix->d_pad * sizeof(float);
-        for (size_t f0 = 0; f0 < flagged.size(); f0 += scan_step) {
-            const int nqg = (int)std::min<size_t>(scan_step, flagged.size() - f0);
-            int grid = 0;
-            if (nqg == 1) {
-                const int64_t qi = flagged[f0];
-                p.q = q_ready + (size_t)qi * ix->d_pad;
-                p.out_d = od + (size_t)qi * k;
-                p.out_i = oi + (size_t)qi * k;
-                CU(launch_scan(p, 1, ix->l2, ix->bf16, ix->num_sms, ix->smem_optin, st, &grid));
-            } else {
-                for (int j = 0; j < nqg; j++)
-                    CU(cudaMemcpyAsync((uint8_t*)ix->fb_q + j * qb, (const uint8_t*)q_ready + (size_t)flagged[f0 + j] * qb, qb,
-                                       cudaMemcpyDeviceToDevice, st));
-                p.q = ix->fb_q;
-                p.out_d = ix->fb_d;
-                p.out_i = ix->fb_i;
-                CU(launch_scan(p, nqg, ix->l2, ix->bf16, ix->num_sms, ix->smem_optin, st, &grid));
-                for (int j = 0; j < nqg; j++) {
-                    const int64_t qi = flagged[f0 + j];
-                    CU(cudaMemcpyAsync(od + (size_t)qi * k, ix->fb_d + (size_t)j * k, (size_t)k * sizeof(float),
-                                       cudaMemcpyDeviceToDevice, st));
-                    CU(cudaMemcpyAsync(oi + (size_t)qi * k, ix->fb_i + (size_t)j * k, (size_t)k * sizeof(int64_t),
-                                       cudaMemcpyDeviceToDevice, st));
-                }
+    } else {
+        // Queries whose containment check failed are re-run on the scan kernel WITHOUT a trip to the
+        // host: a compaction kernel lists them and one cooperative launch serves them scan_step per
+        // corpus pass (it returns at once when the list is empty, the common case).  How many there
+        // were comes back asynchronously, for the statistics and the K' boost only.
+        p.q = q_ready;
+        p.out_d = od;
+        p.out_i = oi;
+        CU(launch_scan_flagged(p, ix->fail_dev, nq, ix->flag_dev, ix->flag_dev + ix->fail_cap, ix->l2, ix->bf16,
+                               ix->num_sms, ix->smem_optin, st));
+        ix->st.n_kernel_launches += 2;
+        int sl = ix->fb_next;
+        ix->fb_next = (sl + 1) % b200r_index::kFbRing;
+        if (ix->fb_pending[sl]) {  // the ring is full of unread counts: take the oldest now
+            cudaEventSynchronize(ix->fb_ev[sl]);
+            fold_fallback_counts(ix, false);
+        }
+        CU(cudaMemcpyAsync(ix->fb_pin + sl, fail_count, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CU(cudaEventRecord(ix->fb_ev[sl], st));
+        ix->fb_pending[sl] = true;
+        ix->fb_pass_bytes[sl] = (int64_t)ix->ntotal * ix->row_bytes;
+        ix->fb_per_pass[sl] = scan_step;
+        if (getenv("B200R_DEBUG_FAILS")) {  // diagnosis: read the per-query flags back (synchronises)
+            CU(cudaMemcpyAsync(ix->fail_pin, ix->fail_dev, (size_t)(ix->fail_cap + 1) * sizeof(int), cudaMemcpyDeviceToHost,
+                               st));
+            CU(cudaStreamSynchronize(st));
+            if (ix->fail_pin[ix->fail_cap]) {
+                int cause[4] = {0, 0, 0, 0};
+                for (int64_t i = 0; i < nq; i++) cause[ix->fail_pin[i] & 3]++;
+                fprintf(stderr, "[b200r] gemm fallbacks: check=%d bucket=%d slice=%d; first failing queries:", cause[1],
+                        cause[2], cause[3]);
+                int shown = 0;
+                for (int64_t i = 0; i < nq && shown < 40; i++)
+                    if (ix->fail_pin[i]) {
+                        fprintf(stderr, " %lld", (long long)i);
+                        shown++;
+                    }
+                fprintf(stderr, "\n");
             }
-            ix->st.n_kernel_launches++;
-            ix->st.last_grid = grid;
-            ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
         }
     }
     if (!filtered) ix->st.last_path = B200R_PATH_SCAN;
@@ -735,6 +768,15 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
         float ms = 0.f;
         CU(cudaEventElapsedTime(&ms, ix->t0, ix->t1));
         ix->st.last_search_ms = ms;
+    }
+    if (out_mem_kind == B200R_DEVICE) {  // still in flight on the caller's stream
+        // (host queries were staged through the index's pinned buffer: it must be free before the next call)
+        if (q_mem_kind == B200R_HOST) CU(cudaStreamSynchronize(st));
+        CU(cudaEventRecord(ix->ws_ev, st));
+        ix->ws_ev_set = true;
+        ix->ws_ev_stream = st;
+    } else {
+        ix->ws_ev_set = false;  // host results: the stream was synchronised above
     }
     ix->st.n_search_calls++;
     ix->st.n_queries += nq;
@@ -765,6 +807,7 @@ extern "C" int b200r_search_exchange(b200r_index* ix, const float* q, int64_t nq
     int rc = ensure_search_ws(ix, nq_slots, nq, k);
     if (rc != B200R_OK) return rc;
     if (ix->data_ev_set && ix->data_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->data_ev, 0));
+    if (ix->ws_ev_set && ix->ws_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->ws_ev, 0));
     CU(launch_prep_queries(q, nq, ix->d, ix->d_pad, nq_slots, ix->cfg.normalize_queries != 0, ix->q_dev, st));
     ScanParams p{};
     p.corpus = ix->rows;
@@ -786,6 +829,9 @@ extern "C" int b200r_search_exchange(b200r_index* ix, const float* q, int64_t nq
     int grid = 0;
     CU(launch_scan(p, (int)nq, ix->l2, ix->bf16, ix->num_sms, ix->smem_optin, st, &grid));
     CU(launch_merge_wait(ix->l2, reinterpret_cast<uint8_t*>(peer_bufs[rank]), world, (int)nq, k, epoch, D, I, st));
+    CU(cudaEventRecord(ix->ws_ev, st));
+    ix->ws_ev_set = true;
+    ix->ws_ev_stream = st;
     ix->st.n_kernel_launches += 3;
     ix->st.last_grid = grid;
     ix->st.last_path = B200R_PATH_SCAN;

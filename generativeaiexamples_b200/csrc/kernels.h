@@ -33,6 +33,10 @@ struct ScanParams {
     int xchg_world, xchg_rank;
     uint32_t xchg_epoch;
     uint8_t* xchg_peer[8];  // peer-mapped base of each rank's exchange buffer (layout below)
+    // flagged re-run (launch_scan_flagged): the queries to serve are q[flag_list[0..*flag_count)], their
+    // results go to row flag_list[i] of out_d / out_i; the launch is cooperative and loops over them
+    const int* flag_list;
+    const int* flag_count;
 };
 
 // Exchange buffer of one rank (symmetric: same layout on every rank, peer-mapped over NVLink):
@@ -51,6 +55,11 @@ cudaError_t launch_merge_wait(bool l2, uint8_t* my_buf, int world, int nq, int k
 
 size_t scan_scratch_bytes(int max_grid);
 int scan_queries_per_launch(int d_pad, int row_bytes, size_t smem_limit);
+// Device-side fallback of the GEMM route: compacts fail_flags[0..nq_total) into flag_list / flag_count and
+// re-runs exactly those queries through the scan kernel in ONE cooperative launch (which returns at
+// once when nothing is flagged), so the host never has to read the flags back.
+cudaError_t launch_scan_flagged(ScanParams p, const int* fail_flags, int64_t nq_total, int* flag_list, int* flag_count,
+                                bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st);
 cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st,
                         int* grid_out);
 

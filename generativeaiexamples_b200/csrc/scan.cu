@@ -21,6 +21,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <cooperative_groups.h>
+
 #include <cstdlib>
 
 namespace b200r {
@@ -28,7 +30,11 @@ namespace b200r {
 constexpr int kScanConsumerWarps = 16;
 constexpr int kScanThreads = 32 * (1 + kScanConsumerWarps);
 
-template <int NQ, int KPL, bool L2, bool BF16>
+// FLAGGED: the cooperative re-run of the queries that failed the GEMM route's containment check.
+// The same body runs once per group of NQ flagged queries, with a grid-wide barrier between groups
+// (the candidate scratch, the ticket and the shared-memory ring are reused); the pipeline position
+// (stage, phase) simply carries on from one group to the next.
+template <int NQ, int KPL, bool L2, bool BF16, bool FLAGGED>
 __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int NCW = kScanConsumerWarps;
@@ -44,6 +50,13 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
     uint64_t* empty_bar = full_bar + nst;
     __shared__ int s_is_last;
 
+    int n_groups = 1, n_flagged = 0;
+    if constexpr (FLAGGED) {
+        n_flagged = *p.flag_count;
+        if (n_flagged == 0) return;  // the common case: every query passed its check
+        n_groups = (n_flagged + NQ - 1) / NQ;
+    }
+
     // ---- set-up ---------------------------------------------------------
     if (threadIdx.x == 0) {
         for (int s = 0; s < nst; s++) {
@@ -52,8 +65,22 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
         }
         fence_mbar_init();
     }
+    // position in the stage ring: the producer lane and every consumer warp advance it identically
+    int s = 0;
+    uint32_t ph = 0;
+  for (int grp = 0; grp < n_groups; grp++) {
+    const int nq_active = FLAGGED ? (n_flagged - grp * NQ < NQ ? n_flagged - grp * NQ : NQ) : p.nq_active;
     // queries -> shared memory (fp32, zero padded to NQ rows by the host)
-    {
+    if constexpr (FLAGGED) {
+        float4* q4 = reinterpret_cast<float4*>(qs);
+        const int d4 = p.d / 4;
+        for (int qi = 0; qi < NQ; qi++) {
+            const bool have = qi < nq_active;
+            const float4* qg = reinterpret_cast<const float4*>(p.q + (size_t)(have ? p.flag_list[grp * NQ + qi] : 0) * p.d);
+            for (int i = threadIdx.x; i < d4; i += blockDim.x)
+                q4[(size_t)qi * d4 + i] = have ? qg[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    } else {
         const float4* qg = reinterpret_cast<const float4*>(p.q);
         float4* q4 = reinterpret_cast<float4*>(qs);
         const int n4 = NQ * p.d / 4;
@@ -83,8 +110,6 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
         if (lane == 0) {
             const uint64_t pol = policy_evict_first();
             const uint8_t* g = reinterpret_cast<const uint8_t*>(p.corpus);
-            int s = 0;
-            uint32_t ph = 0;
             for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
                 mbar_wait(&empty_bar[s], ph ^ 1);
                 const int64_t row0 = t * R;
@@ -108,8 +133,6 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
     } else {
         // ---- consumers --------------------------------------------------
         const int cw = warp - 1;
-        int s = 0;
-        uint32_t ph = 0;
         int64_t seq = 0;  // rows this CTA has streamed before the current tile
         const int nvec = BF16 ? (p.d >> 3) : (p.d >> 2);  // 16-byte vectors per row
         for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
@@ -239,7 +262,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
         s_is_last = (ticket == gridDim.x - 1);
     }
     __syncthreads();
-    if (!s_is_last) return;
+    if (s_is_last) {
     __threadfence();
 
     // phase A: every warp folds a strided subset of the CTA lists, per query
@@ -252,17 +275,19 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
     }
     __syncthreads();
     // phase B: one warp per query folds the NW partial lists and writes the result
-    if (warp < NQ && warp < p.nq_active) {
+    if (warp < NQ && warp < nq_active) {
         WarpTopK<KPL, L2> m;
         m.init(p.k);
         m.template merge_from<false>(sm_lists + (size_t)warp * NW * KCAP, 0, NW, 1, KCAP);
-        if (p.xchg_world == 0) {
+        if (FLAGGED || p.xchg_world == 0) {
+            // result row: the query's own position (flagged re-run) or its slot in this launch
+            const size_t orow = FLAGGED ? (size_t)p.flag_list[grp * NQ + warp] : (size_t)warp;
 #pragma unroll
             for (int j = 0; j < KPL; j++) {
                 const int e = j * 32 + lane;
                 if (e < p.k) {
-                    p.out_d[(size_t)warp * p.k + e] = m.v[j];
-                    p.out_i[(size_t)warp * p.k + e] = (m.id[j] == kEmptyId) ? -1 : (int64_t)m.id[j] + p.id_base;
+                    p.out_d[orow * p.k + e] = m.v[j];
+                    p.out_i[orow * p.k + e] = (m.id[j] == kEmptyId) ? -1 : (int64_t)m.id[j] + p.id_base;
                 }
             }
         } else {
@@ -284,7 +309,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
             __threadfence_system();
         }
     }
-    if (p.xchg_world > 0) {
+    if (!FLAGGED && p.xchg_world > 0) {
         __syncthreads();  // every result store of this CTA is fenced; now raise the flags
         if (threadIdx.x < p.xchg_world) {
             uint32_t* flag = reinterpret_cast<uint32_t*>(p.xchg_peer[threadIdx.x] + kXchgFlagOffset +
@@ -292,13 +317,29 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
             asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(p.xchg_epoch) : "memory");
         }
     }
-    if (threadIdx.x == 0) *p.counter = 0;  // ready for the next launch on this stream
+    if (threadIdx.x == 0) *p.counter = 0;  // ready for the next group / the next launch on this stream
+    }  // s_is_last
+    if constexpr (FLAGGED) {
+        __threadfence();
+        fence_proxy_async();  // the ring held candidate lists (generic stores); the next group's bulk copies write it again
+        cooperative_groups::this_grid().sync();  // scratch, ticket and the shared-memory ring are free again
+    }
+  }  // groups
 }
 
 // ---------------------------------------------------------------------------
 template <int NQ, int KPL, bool L2, bool BF16>
-static cudaError_t launch_one(const ScanParams& p, int grid, size_t smem, cudaStream_t st) {
-    auto kern = scan_topk_kernel<NQ, KPL, L2, BF16>;
+static cudaError_t launch_one(const ScanParams& p, int grid, size_t smem, cudaStream_t st, bool flagged) {
+    if (flagged) {
+        // cooperative: the kernel loops over the flagged queries with grid-wide barriers in between
+        auto kern = scan_topk_kernel<NQ, KPL, L2, BF16, true>;
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        ScanParams pc = p;
+        void* args[] = {&pc};
+        return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(grid), dim3(kScanThreads), args, smem, st);
+    }
+    auto kern = scan_topk_kernel<NQ, KPL, L2, BF16, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     kern<<<grid, kScanThreads, smem, st>>>(p);
@@ -306,11 +347,12 @@ static cudaError_t launch_one(const ScanParams& p, int grid, size_t smem, cudaSt
 }
 
 template <int NQ, int KPL>
-static cudaError_t launch_mk(const ScanParams& p, bool l2, bool bf16, int grid, size_t smem, cudaStream_t st) {
-    if (l2) return bf16 ? launch_one<NQ, KPL, true, true>(p, grid, smem, st)
-                        : launch_one<NQ, KPL, true, false>(p, grid, smem, st);
-    return bf16 ? launch_one<NQ, KPL, false, true>(p, grid, smem, st)
-                : launch_one<NQ, KPL, false, false>(p, grid, smem, st);
+static cudaError_t launch_mk(const ScanParams& p, bool l2, bool bf16, int grid, size_t smem, cudaStream_t st,
+                             bool flagged) {
+    if (l2) return bf16 ? launch_one<NQ, KPL, true, true>(p, grid, smem, st, flagged)
+                        : launch_one<NQ, KPL, true, false>(p, grid, smem, st, flagged);
+    return bf16 ? launch_one<NQ, KPL, false, true>(p, grid, smem, st, flagged)
+                : launch_one<NQ, KPL, false, false>(p, grid, smem, st, flagged);
 }
 
 size_t scan_scratch_bytes(int max_grid) {
@@ -327,8 +369,8 @@ int scan_queries_per_launch(int d_pad, int row_bytes, size_t smem_limit) {
     return (fixed + (size_t)kScanMaxNQ * d_pad * sizeof(float) <= smem_limit) ? kScanMaxNQ : 1;
 }
 
-cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st,
-                        int* grid_out) {
+static cudaError_t launch_scan_impl(ScanParams p, int nq, bool l2, bool bf16, int num_sms, size_t smem_limit,
+                                    cudaStream_t st, int* grid_out, bool flagged) {
     const int NQ = nq <= 1 ? 1 : 4;
     // list slots per lane: 32*KPL >= k.  Above 128 only the single-query variants exist.
     const int KPL = p.k <= 32 ? 1 : p.k <= 128 ? 4 : p.k <= 256 ? 8 : p.k <= 512 ? 16 : 32;
@@ -362,11 +404,60 @@ cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, s
     if (grid < 1) grid = 1;
     if (grid_out) *grid_out = grid;
     const size_t smem = (size_t)nst * stage_bytes + q_bytes + bar_bytes;
-    if (KPL == 8) return launch_mk<1, 8>(p, l2, bf16, grid, smem, st);
-    if (KPL == 16) return launch_mk<1, 16>(p, l2, bf16, grid, smem, st);
-    if (KPL == 32) return launch_mk<1, 32>(p, l2, bf16, grid, smem, st);
-    if (NQ == 1) return KPL == 1 ? launch_mk<1, 1>(p, l2, bf16, grid, smem, st) : launch_mk<1, 4>(p, l2, bf16, grid, smem, st);
-    return KPL == 1 ? launch_mk<4, 1>(p, l2, bf16, grid, smem, st) : launch_mk<4, 4>(p, l2, bf16, grid, smem, st);
+    if (KPL == 8) return launch_mk<1, 8>(p, l2, bf16, grid, smem, st, flagged);
+    if (KPL == 16) return launch_mk<1, 16>(p, l2, bf16, grid, smem, st, flagged);
+    if (KPL == 32) return launch_mk<1, 32>(p, l2, bf16, grid, smem, st, flagged);
+    if (NQ == 1)
+        return KPL == 1 ? launch_mk<1, 1>(p, l2, bf16, grid, smem, st, flagged) : launch_mk<1, 4>(p, l2, bf16, grid, smem, st, flagged);
+    return KPL == 1 ? launch_mk<4, 1>(p, l2, bf16, grid, smem, st, flagged) : launch_mk<4, 4>(p, l2, bf16, grid, smem, st, flagged);
+}
+
+cudaError_t launch_scan(ScanParams p, int nq, bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st,
+                        int* grid_out) {
+    p.flag_list = nullptr;
+    p.flag_count = nullptr;
+    return launch_scan_impl(p, nq, l2, bf16, num_sms, smem_limit, st, grid_out, false);
+}
+
+// fail_flags[0..n) (non-zero = flagged) -> ascending list of flagged positions + their number
+__global__ void compact_flags_kernel(const int* __restrict__ fail_flags, int64_t n, int* flag_list, int* flag_count) {
+    __shared__ int s_base;
+    __shared__ int s_warp[32];
+    if (threadIdx.x == 0) s_base = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int64_t i0 = 0; i0 < n; i0 += blockDim.x) {
+        const int64_t i = i0 + threadIdx.x;
+        const bool f = i < n && fail_flags[i] != 0;
+        const unsigned m = __ballot_sync(0xffffffffu, f);
+        if (lane == 0) s_warp[warp] = __popc(m);
+        __syncthreads();
+        int off = s_base;
+        for (int w = 0; w < warp; w++) off += s_warp[w];
+        if (f) flag_list[off + __popc(m & ((1u << lane) - 1u))] = (int)i;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int t = 0;
+            for (int w = 0; w < nw; w++) t += s_warp[w];
+            s_base += t;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *flag_count = s_base;
+}
+
+cudaError_t launch_scan_flagged(ScanParams p, const int* fail_flags, int64_t nq_total, int* flag_list, int* flag_count,
+                                bool l2, bool bf16, int num_sms, size_t smem_limit, cudaStream_t st) {
+    if (nq_total < 1 || nq_total > 0x7fffffff) return cudaErrorInvalidValue;
+    compact_flags_kernel<<<1, 256, 0, st>>>(fail_flags, nq_total, flag_list, flag_count);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    p.flag_list = flag_list;
+    p.flag_count = flag_count;
+    p.xchg_world = 0;
+    // four flagged queries per corpus pass where the four-query variants exist and fit
+    const int per_pass = p.k > kScanMaxK ? 1 : scan_queries_per_launch(p.d, p.row_bytes, smem_limit);
+    return launch_scan_impl(p, per_pass, l2, bf16, num_sms, smem_limit, st, nullptr, true);
 }
 
 }  // namespace b200r

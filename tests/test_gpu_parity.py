@@ -998,3 +998,31 @@ def test_service_mirror_on_engine(built_lib, tmp_path):
     assert res[1][0]["metadata"] == {"i": 250} and all(len(r) == 4 for r in res)
     single = [d.page_content for d in vs.similarity_search_by_vector(emb("nothing like it"), k=4)]
     assert [d["page_content"] for d in res[3]] == single
+
+
+def test_async_searches_on_different_streams(built_lib):
+    """Device-tensor searches return before the kernels run; issued on several streams they share the index's
+    workspace (query slots, candidate scratch, tickets), so the library must order them."""
+    import torch
+
+    d, n = 512, 300_000
+    ix = _mk("ip", d, reserve_rows=n)
+    x = torch.randn((n, d), device="cuda")
+    x /= x.norm(dim=1, keepdim=True)
+    ix.add(x)
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream() for _ in range(4)]
+    outs = []
+    for rep in range(24):
+        s = streams[rep % 4]
+        nq = (1, 3, 4, 16)[rep % 4]  # scan and GEMM routes interleaved
+        with torch.cuda.stream(s):
+            rows = torch.arange(rep * 100, rep * 100 + nq, device="cuda")
+            q = x[rows] + 0.01 * torch.randn((nq, d), device="cuda")
+            D, I = ix.search(q, 5)
+            outs.append((rows, I, D))
+    torch.cuda.synchronize()
+    for rows, I, D in outs:
+        assert (I[:, 0] == rows).all(), (rows.tolist(), I[:, 0].tolist())
+        assert (D[:, 0] > 0.9).all()
+    ix.close()
