@@ -115,8 +115,13 @@ int b200r_add(b200r_index* idx, const void* x, int64_t n, int dtype, int mem_kin
  * +FLT_MAX (L2) / -FLT_MAX (IP).  Ties are broken by lowest id.
  * [langchain FAISS.similarity_search_with_score_by_vector -> chains.py:163,211;
  * rag_service.py:301].  q and D/I may independently live on the host or the device;
- * with device outputs the call is asynchronous on `stream`.  Stream rule as for add():
- * if any buffer is DEVICE memory the given stream is used as is (NULL = default stream). */
+ * with device q AND device outputs the call returns without waiting for the GPU, on every
+ * route (queries whose tensor-core filter could not be proven exact are re-run by a
+ * device-side loop, not by the host); host q with device outputs waits once, because the
+ * queries pass through the index's own pinned buffer.  Searches issued on different streams
+ * are ordered after one another on the GPU (they share the index's workspace).  Stream rule
+ * as for add(): if any buffer is DEVICE memory the given stream is used as is (NULL = default
+ * stream). */
 int b200r_search(b200r_index* idx, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
                  int out_mem_kind, void* stream);
 
