@@ -795,7 +795,7 @@ def test_shadow_survives_load_and_reset(built_lib, tmp_path, monkeypatch):
     plain.close()
 
 
-@pytest.mark.parametrize("seed", range(64))
+@pytest.mark.parametrize("seed", range(128))
 def test_randomised_differential(built_lib, seed, monkeypatch):
     """Random shapes, metrics, routes and index options against the float64 truth: whatever the dispatch picks
     (scan, tf32 / bf16-shadow GEMM filter, fallbacks), ids and scores must satisfy the north-star tolerance."""
@@ -841,10 +841,13 @@ def test_randomised_differential(built_lib, seed, monkeypatch):
     what = f"seed={seed} d={d} n={n} nq={nq} k={k} {metric} shadow={shadow} bf16={bf16} path={path} norm={norm_add},{norm_q}"
     assert (I[:, kk:] == -1).all(), what
     Dt, It = truth_topk(metric, qe, xe, min(n, kk + 8))
-    # normalisation happens in fp32 on the device: compare with a tolerance scaled by the magnitudes involved
-    scale = float(max(1.0, (qe.astype(np.float64) ** 2).sum(1).max() + (xe.astype(np.float64) ** 2).sum(1).max())) \
-        if (norm_add or norm_q or metric == "l2") else 1.0
-    assert_topk_parity(D[:, :kk], I[:, :kk], Dt, It, what=what, scale=scale if (norm_add or norm_q) else 1.0)
+    # fp32 rounding is relative to the magnitude of the operands, not of the result: a mid-ranked inner product
+    # of two long vectors can be ~0 while carrying ~1e-7 * |q| * |x| of rounding.  The tolerance floor is
+    # therefore |q|*|x| (the reference's own fp32 kernels are no closer to the float64 truth than that).
+    qn = float(np.sqrt((qe.astype(np.float64) ** 2).sum(1).max()))
+    xn = float(np.sqrt((xe.astype(np.float64) ** 2).sum(1).max())) if n else 0.0
+    scale = max(1.0, qn * xn) if metric == "ip" else max(1.0, qn * qn + xn * xn)
+    assert_topk_parity(D[:, :kk], I[:, :kk], Dt, It, what=what, scale=scale)
     s = D[:, :kk] if metric == "l2" else -D[:, :kk]
     assert (np.diff(s, axis=1) >= 0).all(), what + ": not sorted"
     ix.close()
