@@ -205,7 +205,7 @@ def main_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0  # rank 0 alone runs the CPU arm
-    cb = cpu_reference(args.steps, args.warmup)
+    cb = cpu_reference(args.steps, args.warmup, sample_rows=args.cpu_sample_rows)
     line = {
         "impl": "reference", "metric": METRIC_NAME, "value": cb["value"], "unit": "queries/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1000.0 / cb["value"], "higher_is_better": True,
@@ -469,7 +469,7 @@ def main_gpu(args):
     if rank == 0:
         qps = args.steps * 1000.0 / ms_dev
         e2e_qps = args.steps * 1000.0 / ms_e2e_wall
-        cb = cpu_reference(20, 2) if (world == 1 and not args.no_cpu_baseline) else None
+        cb = cpu_reference(20, 2, sample_rows=args.cpu_sample_rows) if (world == 1 and not args.no_cpu_baseline) else None
         line = {
             "metric": METRIC_NAME, "value": qps, "unit": "queries/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "strong",
@@ -518,6 +518,8 @@ if __name__ == "__main__":
     ap.add_argument("--batch256-steps", type=int, default=20)
     ap.add_argument("--no-shadow", action="store_true", help="skip the bf16-shadow batch-256 line (saves 50%% HBM)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample-rows", type=int, default=400_000,
+                    help="rows of the bounded sample the CPU arm / cpu_baseline scans (scaled linearly to --rows)")
     ap.add_argument("--concurrent", type=int, default=64, help="callers for the coalesced service-view number (0 = skip)")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
