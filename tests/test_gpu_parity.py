@@ -1029,3 +1029,38 @@ def test_async_searches_on_different_streams(built_lib):
         assert (I[:, 0] == rows).all(), (rows.tolist(), I[:, 0].tolist())
         assert (D[:, 0] > 0.9).all()
     ix.close()
+
+
+def test_many_queries_and_many_flagged(built_lib):
+    """Thousands of queries in one call (many 256-query blocks), hundreds of which fail the containment check:
+    the device-side fallback loops over all of them in one cooperative launch."""
+    from generativeaiexamples_b200 import B200IndexFlatIP, _lib
+
+    rng = np.random.default_rng(97)
+    n, d = 30000, 256
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    centre = x[77].copy()
+    x[5000:5800] = centre + 1e-4 * rng.standard_normal((800, d), dtype=np.float32)  # 800 near-duplicates
+    nq = 3001
+    q = rng.standard_normal((nq, d), dtype=np.float32)
+    q[::5] = centre + 1e-3 * rng.standard_normal((len(q[::5]), d), dtype=np.float32)  # 601 queries that must fall back
+    ix = B200IndexFlatIP(d)
+    ix.add(x)
+    f0 = ix.stats()["n_gemm_fallbacks"]
+    D, I = ix.search(q, 10)
+    st = ix.stats()
+    assert st["last_path"] == _lib.PATH_GEMM
+    assert st["n_gemm_fallbacks"] - f0 >= 500
+    _check("ip", D, I, q, x, 10, "3001 queries, ~600 flagged")
+    # and again with device tensors, twice in a row without synchronising in between
+    import torch
+
+    qd = torch.from_numpy(q).cuda()
+    D1, I1 = ix.search(qd, 10)
+    D2, I2 = ix.search(qd[:1500], 10)
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(I1.cpu().numpy(), I)
+    np.testing.assert_array_equal(I2.cpu().numpy(), I[:1500])
+    np.testing.assert_array_equal(D1.cpu().numpy(), D)
+    ix.close()
