@@ -1327,6 +1327,19 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     int cs = 2;  // query-operand multicast over CTA pairs
     if (const char* ev = getenv("B200R_GEMM_CLUSTER")) cs = atoi(ev) == 1 ? 1 : 2;
     if (n_tiles_all < 2 || a.num_sms < 2) cs = 1;
+    if (cs == 2) {
+        // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load
+        // from another GPU's memory hung the GPU.  The multicast operand is the index's own query
+        // buffer; anything that is not plain device memory of the current GPU takes the
+        // non-multicast variant.
+        cudaPointerAttributes pa{};
+        int cur = -1;
+        if (cudaGetDevice(&cur) != cudaSuccess || cudaPointerGetAttributes(&pa, a.q_mma) != cudaSuccess ||
+            pa.type != cudaMemoryTypeDevice || pa.device != cur) {
+            cudaGetLastError();
+            cs = 1;
+        }
+    }
     // more than 128 queries: 2-CTA MMA over CTA pairs (double-buffered accumulators) unless turned off
     bool pair = MT == 2 && cs == 2;
     if (const char* ev = getenv("B200R_GEMM_PAIR")) pair = pair && atoi(ev) != 0;
