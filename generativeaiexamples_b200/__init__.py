@@ -14,7 +14,9 @@ from .flat_index import (  # noqa: F401
 from .vectorstore import (  # noqa: F401
     B200FlatVectorStore, DistanceStrategy, Document, InMemoryDocstore, VectorStoreRetriever,
 )
-from .factory import create_vectorstore_langchain, get_vectorstore  # noqa: F401
+from .factory import (  # noqa: F401
+    create_vectorstore_langchain, del_docs_vectorstore_langchain, get_docs_vectorstore_langchain, get_vectorstore,
+)
 from .service import B200VectorDBResourceService  # noqa: F401
 
-__version__ = "0.1.0"
+__version__ = "0.2.0"

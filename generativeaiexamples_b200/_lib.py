@@ -17,6 +17,7 @@ OK, E_INVALID, E_CUDA, E_UNSUPPORTED, E_NOMEM, E_IO = range(6)
 F32, BF16 = 0, 1
 HOST, DEVICE = 0, 1
 PATH_AUTO, PATH_SCAN, PATH_GEMM = 0, 1, 2
+MAX_DEVICES = 8
 
 
 class Config(ctypes.Structure):
@@ -25,6 +26,7 @@ class Config(ctypes.Structure):
         ("normalize_on_add", ctypes.c_int32), ("normalize_queries", ctypes.c_int32),
         ("device", ctypes.c_int32), ("search_path", ctypes.c_int32), ("shadow_bf16", ctypes.c_int32),
         ("reserve_rows", ctypes.c_int64), ("id_base", ctypes.c_int64),
+        ("n_devices", ctypes.c_int32), ("device_ids", ctypes.c_int32 * MAX_DEVICES),
     ]
 
 
@@ -35,6 +37,8 @@ class Stats(ctypes.Structure):
         ("n_rows_added", ctypes.c_int64), ("n_rows_removed", ctypes.c_int64), ("last_grid", ctypes.c_int32),
         ("last_path", ctypes.c_int32), ("num_sms", ctypes.c_int32), ("reserved0", ctypes.c_int32),
         ("last_search_ms", ctypes.c_double), ("n_gemm_fallbacks", ctypes.c_int64),
+        ("last_kernel_us", ctypes.c_double), ("last_exchange_us", ctypes.c_double),
+        ("n_devices", ctypes.c_int32), ("n_segments", ctypes.c_int32),
     ]
 
     def as_dict(self):
@@ -61,6 +65,8 @@ SIGNATURES = {
     "b200r_exchange_buffer_bytes": (_i64, []),
     "b200r_search_exchange": (_int, [_vp, _vp, _i64, _int, ctypes.POINTER(_vp), _i32, _i32, ctypes.c_uint32, _vp, _vp,
                                      _vp]),
+    "b200r_exchange_status": (_int, [_vp, _i32, _vp, ctypes.POINTER(_i32)]),
+    "b200r_reload_env": (_int, []),
     "b200r_set_id_base": (_int, [_vp, _i64]),
     "b200r_stats_get": (_int, [_vp, ctypes.POINTER(Stats)]),
     "b200r_merge_from": (_int, [_vp, _vp]),
@@ -106,3 +112,29 @@ def check(rc):
         if rc == E_NOMEM:
             raise MemoryError(f"libb200r: {msg}")
         raise B200RError(rc, msg)
+
+
+def make_config(*, dim, metric, storage=F32, normalize_on_add=False, normalize_queries=False, device=0,
+                search_path=PATH_AUTO, shadow_bf16=False, reserve_rows=0, id_base=0, devices=None) -> Config:
+    """``b200r_config`` from keyword arguments; ``devices`` (a list of 2..8 CUDA ordinals) makes a
+    multi-GPU index inside this process."""
+    cfg = Config(dim=int(dim), metric=int(metric), storage=int(storage), normalize_on_add=int(bool(normalize_on_add)),
+                 normalize_queries=int(bool(normalize_queries)), device=int(device), search_path=int(search_path),
+                 shadow_bf16=int(bool(shadow_bf16)), reserve_rows=int(reserve_rows), id_base=int(id_base))
+    devs = [int(d) for d in devices] if devices else []
+    if len(devs) > MAX_DEVICES:
+        raise ValueError(f"at most {MAX_DEVICES} devices, got {len(devs)}")
+    if len(devs) == 1:
+        cfg.device = devs[0]
+        devs = []
+    cfg.n_devices = len(devs)
+    for i, d in enumerate(devs):
+        cfg.device_ids[i] = d
+    if devs:
+        cfg.device = devs[0]
+    return cfg
+
+
+def reload_env() -> None:
+    """Make libb200r read its ``B200R_*`` environment switches again (it reads them once per process)."""
+    check(load().b200r_reload_env())

@@ -1,9 +1,7 @@
-// C ABI of libb200r.so (see include/b200r.h for the reference call each entry
-// point replaces).  Host-side runtime: HBM corpus buffer, pinned staging rings,
-// per-index search workspace, error plumbing.  No CPU compute path exists here.
-#include "../../include/b200r.h"
-#include "common.cuh"
-#include "kernels.h"
+// The single-GPU index ("leaf") behind the C ABI of libb200r.so: HBM corpus buffer, pinned
+// staging rings, per-index search workspace, error plumbing.  include/b200r.h names the reference
+// call each operation replaces; abi.cu exports them.  No CPU compute path exists here.
+#include "index.h"
 
 #include <algorithm>
 #include <cstdarg>
@@ -22,7 +20,8 @@ using namespace b200r;
 // ---------------------------------------------------------------------------
 static thread_local std::string g_err;
 
-static int fail(int code, const char* fmt, ...) {
+namespace b200r {
+int fail(int code, const char* fmt, ...) {
     char buf[1024];
     va_list ap;
     va_start(ap, fmt);
@@ -31,36 +30,58 @@ static int fail(int code, const char* fmt, ...) {
     g_err = buf;
     return code;
 }
-
-namespace b200r {
 void set_last_error(const char* msg) { g_err = msg ? msg : ""; }
+const char* last_error_cstr() { return g_err.c_str(); }
+
+// ---------------------------------------------------------------------------
+// environment switches
+// ---------------------------------------------------------------------------
+static Knobs g_knobs;
+static std::once_flag g_knobs_once;
+static std::mutex g_knobs_mu;
+
+static void read_knobs_locked() {
+    Knobs k;
+    auto geti = [](const char* name, long long dflt) -> long long {
+        const char* ev = getenv(name);
+        return (ev && *ev) ? atoll(ev) : dflt;
+    };
+    k.stage_threads = (int)std::max<long long>(1, geti("B200R_STAGE_THREADS", 8));
+    k.gemm_min_nq = geti("B200R_GEMM_MIN_NQ", -1);
+    k.gemm_min_bytes = geti("B200R_GEMM_MIN_BYTES", -1);
+    k.evict_first = (int)geti("B200R_EVICT_FIRST", -1);
+    k.gemm_noboost = getenv("B200R_GEMM_NOBOOST") != nullptr;
+    k.debug_fails = getenv("B200R_DEBUG_FAILS") != nullptr;
+    k.scan_stage_kb = (int)geti("B200R_SCAN_STAGE_KB", 0);
+    k.scan_stages = (int)geti("B200R_SCAN_STAGES", 0);
+    k.scan_dynamic = (int)geti("B200R_SCAN_DYNAMIC", -1);
+    k.gemm_kpcap = (int)geti("B200R_GEMM_KPCAP", 0);
+    k.gemm_kprime = (int)geti("B200R_GEMM_KPRIME", 0);
+    k.gemm_cluster = (int)geti("B200R_GEMM_CLUSTER", 0);
+    k.gemm_pair = (int)geti("B200R_GEMM_PAIR", -1);
+    k.gemm_prefetch = (int)geti("B200R_GEMM_PREFETCH", 0);
+    k.gemm_noselect = (int)geti("B200R_GEMM_DEBUG_NOSELECT", 0);
+    k.gemm_warmup = (int)geti("B200R_GEMM_WARMUP", -1);
+    k.small_gemm = (int)geti("B200R_SMALL_GEMM", -1);
+    k.multi_workers = (int)geti("B200R_MULTI_WORKERS", -1);
+    k.multi_spin_us = (int)geti("B200R_MULTI_SPIN_US", 200);
+    k.multi_fused = (int)geti("B200R_MULTI_FUSED", -1);
+    g_knobs = k;
+}
+const Knobs& knobs() {
+    std::call_once(g_knobs_once, [] {
+        std::lock_guard<std::mutex> lk(g_knobs_mu);
+        read_knobs_locked();
+    });
+    return g_knobs;
+}
+void reload_knobs() {
+    knobs();
+    std::lock_guard<std::mutex> lk(g_knobs_mu);
+    read_knobs_locked();
+}
 }  // namespace b200r
 
-#define CU(call)                                                                                     \
-    do {                                                                                             \
-        cudaError_t e__ = (call);                                                                    \
-        if (e__ != cudaSuccess)                                                                      \
-            return fail(e__ == cudaErrorMemoryAllocation ? B200R_E_NOMEM : B200R_E_CUDA, "%s: %s (%s:%d)", #call, \
-                        cudaGetErrorString(e__), __FILE__, __LINE__);                                \
-    } while (0)
-
-struct DeviceGuard {
-    int prev = -1;
-    bool ok = true;
-    explicit DeviceGuard(int dev) {
-        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
-        if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
-    }
-    ~DeviceGuard() {
-        if (prev >= 0) cudaSetDevice(prev);
-    }
-};
-
-// ---------------------------------------------------------------------------
-// the index
-// ---------------------------------------------------------------------------
-constexpr size_t kStageHalfBytes = 32u << 20;  // pinned / device staging, per half
-constexpr int64_t kMaxRows = 0xFFFFFFFEll;     // ids are 32-bit inside the kernels
 // corpus sizes from which small batches go to the GEMM path (measured crossovers with the device-side
 // fallback in place, tools/perf_small_nq.py / perf_bf16_small.py: 2..4 queries from ~110k x 1024 fp32 rows;
 // a single query on the bf16 shadow or on bf16 rows from ~250k / ~500k rows)
@@ -69,79 +90,7 @@ constexpr int64_t kGemmShadowSingleBytes = 1024ll << 20;
 constexpr int64_t kGemmBf16SmallBatchBytes = 64ll << 20;
 constexpr int64_t kGemmBf16SingleBytes = 1024ll << 20;
 
-struct b200r_index {
-    b200r_config cfg{};
-    int d = 0, d_pad = 0, row_bytes = 0;
-    bool bf16 = false, l2 = false;
-    int device = 0, num_sms = 0;
-    size_t smem_optin = 0;
-
-    uint8_t* rows = nullptr;  // [capacity][row_bytes]
-    float* norms = nullptr;   // [capacity] squared norms of the stored rows
-    // optional (cfg.shadow_bf16, fp32 storage): the same rows rounded to bf16, [capacity][d_pad];
-    // batches on the GEMM path filter on it (half the bytes, bf16 MMA rate) and re-score on `rows`
-    uint8_t* shadow = nullptr;
-    bool shadow_on = false;   // b200r_set_shadow_filter
-    int64_t ntotal = 0, capacity = 0;
-
-    cudaStream_t stream = nullptr;  // the index's own stream
-    // last writer of rows/norms: searches on another stream wait for it (add() with a device tensor
-    // runs asynchronously on the caller's stream)
-    cudaEvent_t data_ev = nullptr;
-    bool data_ev_set = false;
-    cudaStream_t data_ev_stream = nullptr;
-    // last user of the search workspace (query slots, candidate scratch, tickets, ...): a search
-    // enqueued on another stream waits for it, so asynchronous searches on different streams
-    // never overlap on the shared buffers
-    cudaEvent_t ws_ev = nullptr;
-    bool ws_ev_set = false;
-    cudaStream_t ws_ev_stream = nullptr;
-    // add(): double-buffered host->device staging
-    uint8_t* pin_add = nullptr;
-    uint8_t* dev_add = nullptr;
-    cudaEvent_t add_ev[2] = {nullptr, nullptr};
-    // search(): workspace
-    float* q_pin = nullptr;
-    float* q_raw = nullptr;   // device, as given
-    float* q_dev = nullptr;   // device, padded / normalised
-    int64_t q_cap = 0;        // query slots allocated
-    Cand* scratch = nullptr;
-    unsigned* counter = nullptr;
-    uint8_t* out_buf = nullptr;  // host-output searches: [scores | pad to 16 B | ids], one D2H per search
-    float* out_d = nullptr;      // = out_buf
-    int64_t* out_i = nullptr;    // ids of a full-capacity result (only a placeholder target otherwise)
-    uint8_t* out_pin = nullptr;
-    int64_t out_cap = 0;  // nq*k entries allocated
-    cudaEvent_t t0 = nullptr, t1 = nullptr;
-    bool timing = false;
-    // GEMM path workspace
-    void* q_bf16 = nullptr;        // bf16 copy of q_dev (bf16 corpus only), q_cap rows
-    Cand* gemm_cand = nullptr;
-    size_t gemm_cand_bytes = 0;
-    unsigned* max_norm_bits = nullptr;
-    void* gemm_aux = nullptr;      // histograms, bucket maps, grid-wide thresholds
-    bool max_norm_dirty = true;
-    int* fail_dev = nullptr;       // [fail_cap] flags + 1 counter at the end
-    int* fail_pin = nullptr;
-    int64_t fail_cap = 0;
-    // K' multiplier in percent: raised after a search whose containment check failed for some
-    // query (corpus with many near-ties), so the next batches filter with more slack
-    int kp_boost = 100;
-    // device-side fallback of flagged queries (launch_scan_flagged): compacted positions + their number
-    int* flag_dev = nullptr;       // [fail_cap] list + 1 count at the end
-    // the number of flagged queries of recent searches comes back asynchronously (statistics and the
-    // K' boost only): a small ring of pinned words, each with the event that says it has landed
-    static constexpr int kFbRing = 8;
-    int* fb_pin = nullptr;         // [kFbRing]
-    cudaEvent_t fb_ev[kFbRing] = {};
-    bool fb_pending[kFbRing] = {};
-    int64_t fb_pass_bytes[kFbRing] = {};  // corpus bytes one fallback pass streams
-    int fb_per_pass[kFbRing] = {};        // flagged queries one pass serves
-    int fb_next = 0;
-
-    std::mutex mu;
-    b200r_stats st{};
-};
+namespace b200r {
 
 static int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
 static void fold_fallback_counts(b200r_index* ix, bool wait);
@@ -151,10 +100,7 @@ static void fold_fallback_counts(b200r_index* ix, bool wait);
 static void staged_memcpy(void* dst, const void* src, size_t bytes) {
     constexpr size_t kMinPerThread = 4u << 20;
     unsigned hw = std::thread::hardware_concurrency();
-    static const int max_threads = [] {
-        const char* ev = getenv("B200R_STAGE_THREADS");  // tuning knob
-        return ev ? std::max(1, atoi(ev)) : 8;  // measured on the 16-core GPU box: 18 GB/s with 4, 24 with 8, 21 with 12
-    }();
+    const int max_threads = knobs().stage_threads;  // measured on the 16-core GPU box: 18 GB/s with 4, 24 with 8, 21 with 12
     int nt = (int)std::min<size_t>(std::min<unsigned>(hw ? std::max(1u, hw / 2) : 1, (unsigned)max_threads), bytes / kMinPerThread);
     if (nt <= 1) {
         memcpy(dst, src, bytes);
@@ -225,7 +171,7 @@ static int ensure_capacity(b200r_index* ix, int64_t need, cudaStream_t st) {
     return B200R_OK;
 }
 
-static void free_index(b200r_index* ix) {
+void leaf_free(b200r_index* ix) {
     if (!ix) return;
     DeviceGuard g(ix->device);
     if (ix->stream) cudaStreamSynchronize(ix->stream);
@@ -249,6 +195,10 @@ static void free_index(b200r_index* ix) {
     cudaFreeHost(ix->fail_pin);
     cudaFree(ix->flag_dev);
     cudaFreeHost(ix->fb_pin);
+    cudaFree(ix->recon_dev);
+    cudaFreeHost(ix->recon_pin);
+    cudaFree(ix->bounce);
+    cudaFree(ix->adj_dev);
     for (auto& e : ix->fb_ev)
         if (e) cudaEventDestroy(e);
     for (auto& e : ix->add_ev)
@@ -262,10 +212,7 @@ static void free_index(b200r_index* ix) {
     delete ix;
 }
 
-extern "C" int b200r_version(void) { return B200R_VERSION; }
-extern "C" const char* b200r_last_error(void) { return g_err.c_str(); }
-
-extern "C" int b200r_create(const b200r_config* cfg, b200r_index** out) {
+int leaf_create(const b200r_config* cfg, b200r_index** out) {
     if (!cfg || !out) return fail(B200R_E_INVALID, "b200r_create: null argument");
     *out = nullptr;
     if (cfg->dim <= 0) return fail(B200R_E_INVALID, "dim must be positive, got %d", cfg->dim);
@@ -315,7 +262,7 @@ extern "C" int b200r_create(const b200r_config* cfg, b200r_index** out) {
     do {                                                                                          \
         cudaError_t e__ = (call);                                                                 \
         if (e__ != cudaSuccess) {                                                                 \
-            free_index(ix);                                                                       \
+            leaf_free(ix);                                                                       \
             cudaGetLastError();                                                                   \
             return fail(e__ == cudaErrorMemoryAllocation ? B200R_E_NOMEM : B200R_E_CUDA, "%s: %s", #call, \
                         cudaGetErrorString(e__));                                                 \
@@ -335,7 +282,7 @@ extern "C" int b200r_create(const b200r_config* cfg, b200r_index** out) {
     if (cfg->reserve_rows > 0) {
         int rc = ensure_capacity(ix, cfg->reserve_rows, ix->stream);
         if (rc != B200R_OK) {
-            free_index(ix);
+            leaf_free(ix);
             return rc;
         }
     }
@@ -343,40 +290,7 @@ extern "C" int b200r_create(const b200r_config* cfg, b200r_index** out) {
     return B200R_OK;
 }
 
-extern "C" int b200r_destroy(b200r_index* ix) {
-    free_index(ix);
-    return B200R_OK;
-}
-
-extern "C" int b200r_ntotal(const b200r_index* ix, int64_t* out) {
-    if (!ix || !out) return fail(B200R_E_INVALID, "b200r_ntotal: null argument");
-    *out = ix->ntotal;
-    return B200R_OK;
-}
-
-extern "C" int b200r_set_id_base(b200r_index* ix, int64_t id_base) {
-    if (!ix) return fail(B200R_E_INVALID, "b200r_set_id_base: null index");
-    std::lock_guard<std::mutex> lk(ix->mu);
-    ix->cfg.id_base = id_base;
-    return B200R_OK;
-}
-
-extern "C" int b200r_set_shadow_filter(b200r_index* ix, int32_t enabled) {
-    if (!ix) return fail(B200R_E_INVALID, "b200r_set_shadow_filter: null index");
-    if (!ix->cfg.shadow_bf16) return fail(B200R_E_INVALID, "index was created without shadow_bf16");
-    std::lock_guard<std::mutex> lk(ix->mu);
-    ix->shadow_on = enabled != 0;
-    return B200R_OK;
-}
-
-extern "C" int b200r_set_timing(b200r_index* ix, int32_t enabled) {
-    if (!ix) return fail(B200R_E_INVALID, "b200r_set_timing: null index");
-    ix->timing = enabled != 0;
-    return B200R_OK;
-}
-
-extern "C" int b200r_stats_get(b200r_index* ix, b200r_stats* out) {
-    if (!ix || !out) return fail(B200R_E_INVALID, "b200r_stats_get: null argument");
+int leaf_stats(b200r_index* ix, b200r_stats* out) {
     std::lock_guard<std::mutex> lk(ix->mu);
     {
         DeviceGuard g(ix->device);
@@ -384,12 +298,14 @@ extern "C" int b200r_stats_get(b200r_index* ix, b200r_stats* out) {
     }
     ix->st.ntotal = ix->ntotal;
     ix->st.capacity_rows = ix->capacity;
+    ix->st.last_kernel_us = ix->st.last_search_ms * 1000.0;
+    ix->st.last_exchange_us = 0.0;
+    ix->st.n_devices = 1;
     *out = ix->st;
     return B200R_OK;
 }
 
-extern "C" int b200r_reset(b200r_index* ix) {
-    if (!ix) return fail(B200R_E_INVALID, "b200r_reset: null index");
+int leaf_reset(b200r_index* ix) {
     std::lock_guard<std::mutex> lk(ix->mu);
     ix->ntotal = 0;
     ix->max_norm_dirty = true;
@@ -399,8 +315,7 @@ extern "C" int b200r_reset(b200r_index* ix) {
 // ---------------------------------------------------------------------------
 // add
 // ---------------------------------------------------------------------------
-extern "C" int b200r_add(b200r_index* ix, const void* x, int64_t n, int dtype, int mem_kind, void* stream) {
-    if (!ix) return fail(B200R_E_INVALID, "b200r_add: null index");
+int leaf_add(b200r_index* ix, const void* x, int64_t n, int dtype, int mem_kind, void* stream, bool allow_normalize) {
     if (n < 0) return fail(B200R_E_INVALID, "b200r_add: n = %lld", (long long)n);
     if (n == 0) return B200R_OK;
     if (!x) return fail(B200R_E_INVALID, "b200r_add: null data");
@@ -411,9 +326,12 @@ extern "C" int b200r_add(b200r_index* ix, const void* x, int64_t n, int dtype, i
     // device input: ordered on the caller's stream exactly as given (NULL is CUDA's default
     // stream, e.g. torch's); host input: the index's own non-blocking stream unless told otherwise
     cudaStream_t st = (mem_kind == B200R_DEVICE || stream) ? (cudaStream_t)stream : ix->stream;
+    // an earlier device add may still be writing rows on another stream: this add is ordered after it
+    // (a growth below copies those rows, and data_ev is about to be re-recorded on `st` alone)
+    if (ix->data_ev_set && ix->data_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->data_ev, 0));
     int rc = ensure_capacity(ix, ix->ntotal + n, st);
     if (rc != B200R_OK) return rc;
-    const bool norm = ix->cfg.normalize_on_add != 0;
+    const bool norm = allow_normalize && ix->cfg.normalize_on_add != 0;
     uint8_t* dst = ix->rows + (size_t)ix->ntotal * ix->row_bytes;
     float* dstn = ix->norms + ix->ntotal;
     if (mem_kind == B200R_DEVICE) {
@@ -560,62 +478,77 @@ static void fold_fallback_counts(b200r_index* ix, bool wait) {
         ix->st.n_gemm_fallbacks += cnt;
         const int per = std::max(1, ix->fb_per_pass[sl]);
         ix->st.bytes_scanned += (int64_t)((cnt + per - 1) / per) * ix->fb_pass_bytes[sl];
-        if (!getenv("B200R_GEMM_NOBOOST"))  // (tuning knob: keep K' fixed)
+        if (!knobs().gemm_noboost)  // (tuning knob: keep K' fixed)
             ix->kp_boost = std::min(400, ix->kp_boost * 3 / 2);
     }
 }
 
-extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
-                            int out_mem_kind, void* stream) {
-    if (!ix) return fail(B200R_E_INVALID, "b200r_search: null index");
+// Two-way dispatch like faiss (scan for small batches, GEMM for large ones).  faiss switches
+// at nq = 20 (distance_compute_blas_threshold).  Here one GEMM pass streams the corpus at
+// ~6.9 TB/s whatever nq <= 128 is, while the scan kernel is FMA-bound beyond one query
+// (10M x 1024 fp32: 5.7 ms for nq = 1, 9.5-10.1 ms for nq = 2..4; GEMM 5.9-6.2 ms), so on a
+// corpus large enough to hide the GEMM path's extra launches the GEMM
+// takes over at nq = 2 -- and at nq = 1 when it can filter on the bf16 shadow (3.0 ms).
+// Small corpora keep the scan up to nq = 4.  Both paths end in the same fp32 scoring code, so
+// the choice never changes a result.
+static bool auto_uses_gemm(const b200r_index* ix, int64_t nq) {
+    const Knobs& kn = knobs();
+    const int64_t corpus_bytes = (int64_t)ix->ntotal * ix->row_bytes;
+    const bool eb = kn.gemm_min_bytes >= 0;
+    int64_t gemm_min = 5;
+    if (corpus_bytes >= (eb ? kn.gemm_min_bytes : kGemmSmallBatchBytes)) gemm_min = 2;
+    if (ix->shadow && ix->shadow_on && corpus_bytes >= (eb ? kn.gemm_min_bytes : kGemmShadowSingleBytes)) gemm_min = 1;
+    if (ix->bf16) {
+        // bf16 rows: the scan unpacks every element (5.5 TB/s for one query, 1.5 TB/s for four),
+        // the tensor cores take bf16 as it is (6.8 TB/s)
+        if (corpus_bytes >= (eb ? kn.gemm_min_bytes : kGemmBf16SmallBatchBytes)) gemm_min = 2;
+        if (corpus_bytes >= (eb ? kn.gemm_min_bytes : kGemmBf16SingleBytes)) gemm_min = 1;
+    }
+    if (kn.gemm_min_nq >= 0) gemm_min = kn.gemm_min_nq;
+    return ix->ntotal > 0 && (ix->cfg.search_path == B200R_PATH_GEMM ||
+                              (ix->cfg.search_path == B200R_PATH_AUTO && nq >= gemm_min));
+}
+
+int leaf_route(b200r_index* ix, int64_t nq) {
+    std::lock_guard<std::mutex> lk(ix->mu);
+    return auto_uses_gemm(ix, nq) ? B200R_PATH_GEMM : B200R_PATH_SCAN;
+}
+
+int leaf_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
+                int out_mem_kind, void* stream, int route, const ScanExchange* xchg) {
     if (nq < 0) return fail(B200R_E_INVALID, "b200r_search: nq = %lld", (long long)nq);
     if (k <= 0) return fail(B200R_E_INVALID, "b200r_search: k must be > 0, got %d", k);  // faiss: assert k > 0
     if (nq == 0) return B200R_OK;
-    if (!q || !D || !I) return fail(B200R_E_INVALID, "b200r_search: null buffer");
+    if (!q || ((!D || !I) && !xchg)) return fail(B200R_E_INVALID, "b200r_search: null buffer");
     if ((q_mem_kind != B200R_HOST && q_mem_kind != B200R_DEVICE) ||
         (out_mem_kind != B200R_HOST && out_mem_kind != B200R_DEVICE))
         return fail(B200R_E_INVALID, "b200r_search: bad mem_kind");
     if (k > kMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_search: k = %d exceeds the supported maximum %d", k, kMaxK);
+    if (xchg && (nq > kScanMaxNQ || k > kScanMaxK || out_mem_kind != B200R_DEVICE))
+        return fail(B200R_E_UNSUPPORTED, "fused exchange serves nq <= %d, k <= %d with device results", kScanMaxNQ, kScanMaxK);
 
     std::lock_guard<std::mutex> lk(ix->mu);
     DeviceGuard g(ix->device);
+    const Knobs& kn = knobs();
     const bool any_dev = q_mem_kind == B200R_DEVICE || out_mem_kind == B200R_DEVICE;
     cudaStream_t st = (any_dev || stream) ? (cudaStream_t)stream : ix->stream;
-    // Two-way dispatch like faiss (scan for small batches, GEMM for large ones).  faiss switches
-    // at nq = 20 (distance_compute_blas_threshold).  Here one GEMM pass streams the corpus at
-    // ~6.9 TB/s whatever nq <= 128 is, while the scan kernel is FMA-bound beyond one query
-    // (10M x 1024 fp32: 5.7 ms for nq = 1, 9.5-10.1 ms for nq = 2..4; GEMM 5.9-6.2 ms), so on a
-    // corpus large enough to hide the GEMM path's extra launches the GEMM
-    // takes over at nq = 2 -- and at nq = 1 when it can filter on the bf16 shadow (3.0 ms).
-    // Small corpora keep the scan up to nq = 4.  Both paths end in the same fp32 scoring code, so
-    // the choice never changes a result.
-    const char* env_thr = getenv("B200R_GEMM_MIN_NQ");
-    const char* env_bytes = getenv("B200R_GEMM_MIN_BYTES");
-    const int64_t corpus_bytes = (int64_t)ix->ntotal * ix->row_bytes;
-    int64_t gemm_min = 5;
-    if (corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmSmallBatchBytes)) gemm_min = 2;
-    if (ix->shadow && ix->shadow_on && corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmShadowSingleBytes)) gemm_min = 1;
-    if (ix->bf16) {
-        // bf16 rows: the scan unpacks every element (5.5 TB/s for one query, 1.5 TB/s for four),
-        // the tensor cores take bf16 as it is (6.8 TB/s)
-        if (corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmBf16SmallBatchBytes)) gemm_min = 2;
-        if (corpus_bytes >= (env_bytes ? atoll(env_bytes) : kGemmBf16SingleBytes)) gemm_min = 1;
-    }
-    if (env_thr) gemm_min = atoll(env_thr);
     fold_fallback_counts(ix, false);  // may raise the K' boost used below
-    const bool use_gemm = ix->ntotal > 0 && (ix->cfg.search_path == B200R_PATH_GEMM ||
-                                             (ix->cfg.search_path == B200R_PATH_AUTO && nq >= gemm_min));
+    const bool use_gemm = !xchg && ix->ntotal > 0 &&
+                          (route == B200R_PATH_GEMM || (route == B200R_PATH_AUTO && auto_uses_gemm(ix, nq)));
     const int64_t nq_slots = use_gemm ? round_up(nq, 128) : round_up(nq, kScanMaxNQ);
     const bool filtered = use_gemm;  // answers come from a filter + re-score + check
     int rc = ensure_search_ws(ix, nq_slots, nq, k);
     if (rc != B200R_OK) return rc;
+    // this search is ordered after the last writer of the rows and the last user of the workspace
+    // BEFORE anything of it is enqueued (the max-norm refresh below reads the norms and rewrites a
+    // word that an earlier asynchronous search may still be reading)
+    if (ix->data_ev_set && ix->data_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->data_ev, 0));
+    if (ix->ws_ev_set && ix->ws_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->ws_ev, 0));
     if (filtered) {
         rc = ensure_gemm_ws(ix, nq, k, st);
         if (rc != B200R_OK) return rc;
     }
 
-    if (ix->data_ev_set && ix->data_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->data_ev, 0));
-    if (ix->ws_ev_set && ix->ws_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->ws_ev, 0));
     if (ix->timing) CU(cudaEventRecord(ix->t0, st));
     const float* q_src = (const float*)q;
     // queries that need no padding, normalisation or zero-filled spare slots skip the prep kernel:
@@ -644,6 +577,10 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     const size_t ids_off = round_up((size_t)nq * k * sizeof(float), 16);
     float* od = out_mem_kind == B200R_DEVICE ? D : reinterpret_cast<float*>(ix->out_buf);
     int64_t* oi = out_mem_kind == B200R_DEVICE ? I : reinterpret_cast<int64_t*>(ix->out_buf + ids_off);
+    if (xchg) {  // results go to the exchange slots; out_d / out_i stay unused placeholders
+        od = ix->out_d;
+        oi = ix->out_i;
+    }
 
     const bool use_shadow = use_gemm && ix->shadow && ix->shadow_on;
     int* fail_count = filtered ? ix->fail_dev + ix->fail_cap : nullptr;
@@ -691,13 +628,21 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     p.row_bytes = ix->row_bytes;
     p.k = k;
     p.evict_first = ((size_t)ix->ntotal * ix->row_bytes > (size_t)96 << 20) ? 1 : 0;
-    if (const char* ev = getenv("B200R_EVICT_FIRST")) p.evict_first = atoi(ev);  // tuning knob
+    if (kn.evict_first >= 0) p.evict_first = kn.evict_first;  // tuning knob
     p.scratch = ix->scratch;
     p.counter = ix->counter;
     p.id_base = ix->cfg.id_base;
+    if (xchg) {
+        p.xchg_ntargets = xchg->n_targets;
+        p.xchg_rank = xchg->slot;
+        p.xchg_epoch = xchg->epoch;
+        for (int r = 0; r < xchg->n_targets; r++) p.xchg_peer[r] = xchg->target[r];
+    }
     // one query per launch for k > 128 (wide lists) and for rows so wide that four queries do not
     // fit in shared memory beside the stages
     const int scan_step = k > kScanMaxK ? 1 : scan_queries_per_launch(ix->d_pad, ix->row_bytes, ix->smem_optin);
+    if (xchg && nq > scan_step)
+        return fail(B200R_E_UNSUPPORTED, "fused exchange: rows of %d bytes leave room for one query per launch", ix->row_bytes);
     if (!filtered) {
         for (int64_t q0 = 0; q0 < nq; q0 += scan_step) {
             const int nqg = (int)std::min<int64_t>(scan_step, nq - q0);
@@ -732,7 +677,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
         ix->fb_pending[sl] = true;
         ix->fb_pass_bytes[sl] = (int64_t)ix->ntotal * ix->row_bytes;
         ix->fb_per_pass[sl] = scan_step;
-        if (getenv("B200R_DEBUG_FAILS")) {  // diagnosis: read the per-query flags back (synchronises)
+        if (kn.debug_fails) {  // diagnosis: read the per-query flags back (synchronises)
             CU(cudaMemcpyAsync(ix->fail_pin, ix->fail_dev, (size_t)(ix->fail_cap + 1) * sizeof(int), cudaMemcpyDeviceToHost,
                                st));
             CU(cudaStreamSynchronize(st));
@@ -763,7 +708,7 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
         memcpy(D, pd, (size_t)nq * k * sizeof(float));
         memcpy(I, pi, (size_t)nq * k * sizeof(int64_t));
     }
-    if (ix->timing) {
+    if (ix->timing && !xchg && !ix->timing_deferred) {
         CU(cudaEventSynchronize(ix->t1));
         float ms = 0.f;
         CU(cudaEventElapsedTime(&ms, ix->t0, ix->t1));
@@ -783,69 +728,22 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     return B200R_OK;
 }
 
-// ---------------------------------------------------------------------------
-// fused search + NVLink exchange (multi-GPU small batches)
-// ---------------------------------------------------------------------------
-extern "C" int64_t b200r_exchange_buffer_bytes(void) { return kXchgBytes; }
-
-extern "C" int b200r_search_exchange(b200r_index* ix, const float* q, int64_t nq, int k, void* const* peer_bufs,
-                                     int32_t world, int32_t rank, uint32_t epoch, float* D, int64_t* I, void* stream) {
-    if (!ix) return fail(B200R_E_INVALID, "b200r_search_exchange: null index");
-    if (!q || !D || !I || !peer_bufs) return fail(B200R_E_INVALID, "b200r_search_exchange: null buffer");
-    if (nq < 1 || nq > kScanMaxNQ)
-        return fail(B200R_E_UNSUPPORTED, "b200r_search_exchange: nq %lld outside 1..%d", (long long)nq, kScanMaxNQ);
-    if (k < 1 || k > kScanMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_search_exchange: k %d outside 1..%d", k, kScanMaxK);
-    if (world < 1 || world > kXchgMaxWorld || rank < 0 || rank >= world)
-        return fail(B200R_E_INVALID, "b200r_search_exchange: bad world/rank %d/%d", world, rank);
-    if (epoch == 0) return fail(B200R_E_INVALID, "b200r_search_exchange: epoch must start at 1");
-    for (int r = 0; r < world; r++)
-        if (!peer_bufs[r]) return fail(B200R_E_INVALID, "b200r_search_exchange: null peer buffer %d", r);
+// with timing on and results in flight (multi-GPU search): device time of the last search once it has finished
+int leaf_last_search_ms(b200r_index* ix, double* ms_out) {
     std::lock_guard<std::mutex> lk(ix->mu);
     DeviceGuard g(ix->device);
-    cudaStream_t st = (cudaStream_t)stream;
-    const int64_t nq_slots = round_up(nq, kScanMaxNQ);
-    int rc = ensure_search_ws(ix, nq_slots, nq, k);
-    if (rc != B200R_OK) return rc;
-    if (ix->data_ev_set && ix->data_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->data_ev, 0));
-    if (ix->ws_ev_set && ix->ws_ev_stream != st) CU(cudaStreamWaitEvent(st, ix->ws_ev, 0));
-    CU(launch_prep_queries(q, nq, ix->d, ix->d_pad, nq_slots, ix->cfg.normalize_queries != 0, ix->q_dev, st));
-    ScanParams p{};
-    p.corpus = ix->rows;
-    p.n_rows = ix->ntotal;
-    p.d = ix->d_pad;
-    p.row_bytes = ix->row_bytes;
-    p.k = k;
-    p.evict_first = ((size_t)ix->ntotal * ix->row_bytes > (size_t)96 << 20) ? 1 : 0;
-    p.scratch = ix->scratch;
-    p.counter = ix->counter;
-    p.id_base = ix->cfg.id_base;
-    p.q = ix->q_dev;
-    p.out_d = ix->out_d;  // unused in exchange mode
-    p.out_i = ix->out_i;
-    p.xchg_world = world;
-    p.xchg_rank = rank;
-    p.xchg_epoch = epoch;
-    for (int r = 0; r < world; r++) p.xchg_peer[r] = reinterpret_cast<uint8_t*>(peer_bufs[r]);
-    int grid = 0;
-    CU(launch_scan(p, (int)nq, ix->l2, ix->bf16, ix->num_sms, ix->smem_optin, st, &grid));
-    CU(launch_merge_wait(ix->l2, reinterpret_cast<uint8_t*>(peer_bufs[rank]), world, (int)nq, k, epoch, D, I, st));
-    CU(cudaEventRecord(ix->ws_ev, st));
-    ix->ws_ev_set = true;
-    ix->ws_ev_stream = st;
-    ix->st.n_kernel_launches += 3;
-    ix->st.last_grid = grid;
-    ix->st.last_path = B200R_PATH_SCAN;
-    ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
-    ix->st.n_search_calls++;
-    ix->st.n_queries += nq;
+    CU(cudaEventSynchronize(ix->t1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, ix->t0, ix->t1));
+    ix->st.last_search_ms = ms;
+    *ms_out = ms;
     return B200R_OK;
 }
 
 // ---------------------------------------------------------------------------
 // remove_ids / reconstruct
 // ---------------------------------------------------------------------------
-extern "C" int b200r_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, int64_t* n_removed) {
-    if (!ix) return fail(B200R_E_INVALID, "b200r_remove_ids: null index");
+int leaf_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, int64_t* n_removed) {
     if (n < 0 || (n > 0 && !ids)) return fail(B200R_E_INVALID, "b200r_remove_ids: bad ids");
     if (n_removed) *n_removed = 0;
     std::lock_guard<std::mutex> lk(ix->mu);
@@ -866,42 +764,49 @@ extern "C" int b200r_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, 
     cudaStream_t st = ix->stream;
     CU(cudaDeviceSynchronize());  // rows move in place: nothing may be reading or writing them
     ix->data_ev_set = false;
-    int64_t* adj_dev = nullptr;
-    uint8_t* bounce = nullptr;
-    const int64_t chunk_rows = std::max<int64_t>(1, (int64_t)((64u << 20) / ix->row_bytes));
-    CU(cudaMalloc(&adj_dev, (size_t)m * sizeof(int64_t)));
-    cudaError_t e = cudaMalloc(&bounce, (size_t)chunk_rows * ix->row_bytes);
-    if (e != cudaSuccess) {
-        cudaFree(adj_dev);
-        cudaGetLastError();
-        return fail(B200R_E_NOMEM, "b200r_remove_ids: bounce buffer: %s", cudaGetErrorString(e));
-    }
-    int rc = B200R_OK;
-    auto body = [&]() -> int {
-        CU(cudaMemcpyAsync(adj_dev, adj.data(), (size_t)m * sizeof(int64_t), cudaMemcpyHostToDevice, st));
-        for (int64_t o0 = first; o0 < new_total; o0 += chunk_rows) {
-            const int64_t o1 = std::min(new_total, o0 + chunk_rows);
-            // rows: gather the survivors of this output range, then put them in place.
-            // Sources of later ranges lie above o1, so they are still intact.
-            CU(launch_gather_rows(ix->rows, bounce, o0, o1, ix->row_bytes, adj_dev, m, st));
-            CU(cudaMemcpyAsync(ix->rows + (size_t)o0 * ix->row_bytes, bounce, (size_t)(o1 - o0) * ix->row_bytes,
-                               cudaMemcpyDeviceToDevice, st));
-            if (ix->shadow) {
-                CU(launch_gather_rows(ix->shadow, bounce, o0, o1, ix->d_pad * 2, adj_dev, m, st));
-                CU(cudaMemcpyAsync(ix->shadow + (size_t)o0 * ix->d_pad * 2, bounce, (size_t)(o1 - o0) * ix->d_pad * 2,
-                                   cudaMemcpyDeviceToDevice, st));
-            }
-            CU(launch_gather_rows(ix->norms, bounce, o0, o1, (int)sizeof(float), adj_dev, m, st));
-            CU(cudaMemcpyAsync(ix->norms + o0, bounce, (size_t)(o1 - o0) * sizeof(float), cudaMemcpyDeviceToDevice, st));
-            ix->st.n_kernel_launches += 2;
+    // the bounce buffer and the id list stay with the index (a chain server deletes document by document)
+    const int64_t chunk_rows = std::max<int64_t>(1, std::min<int64_t>((int64_t)((64u << 20) / ix->row_bytes),
+                                                                       std::max<int64_t>(1, new_total - first)));
+    const size_t need_bounce = (size_t)chunk_rows * ix->row_bytes;
+    if (need_bounce > ix->bounce_bytes) {
+        cudaFree(ix->bounce);
+        ix->bounce = nullptr;
+        ix->bounce_bytes = 0;
+        cudaError_t e = cudaMalloc(&ix->bounce, need_bounce);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return fail(B200R_E_NOMEM, "b200r_remove_ids: bounce buffer: %s", cudaGetErrorString(e));
         }
-        CU(cudaStreamSynchronize(st));
-        return B200R_OK;
-    };
-    rc = body();
-    cudaFree(adj_dev);
-    cudaFree(bounce);
-    if (rc != B200R_OK) return rc;
+        ix->bounce_bytes = need_bounce;
+    }
+    if (m > ix->adj_cap) {
+        cudaFree(ix->adj_dev);
+        ix->adj_dev = nullptr;
+        ix->adj_cap = 0;
+        const int64_t cap = std::max<int64_t>(m, 1024);
+        CU(cudaMalloc(&ix->adj_dev, (size_t)cap * sizeof(int64_t)));
+        ix->adj_cap = cap;
+    }
+    uint8_t* bounce = ix->bounce;
+    int64_t* adj_dev = ix->adj_dev;
+    CU(cudaMemcpyAsync(adj_dev, adj.data(), (size_t)m * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+    for (int64_t o0 = first; o0 < new_total; o0 += chunk_rows) {
+        const int64_t o1 = std::min(new_total, o0 + chunk_rows);
+        // rows: gather the survivors of this output range, then put them in place.
+        // Sources of later ranges lie above o1, so they are still intact.
+        CU(launch_gather_rows(ix->rows, bounce, o0, o1, ix->row_bytes, adj_dev, m, st));
+        CU(cudaMemcpyAsync(ix->rows + (size_t)o0 * ix->row_bytes, bounce, (size_t)(o1 - o0) * ix->row_bytes,
+                           cudaMemcpyDeviceToDevice, st));
+        if (ix->shadow) {
+            CU(launch_gather_rows(ix->shadow, bounce, o0, o1, ix->d_pad * 2, adj_dev, m, st));
+            CU(cudaMemcpyAsync(ix->shadow + (size_t)o0 * ix->d_pad * 2, bounce, (size_t)(o1 - o0) * ix->d_pad * 2,
+                               cudaMemcpyDeviceToDevice, st));
+        }
+        CU(launch_gather_rows(ix->norms, bounce, o0, o1, (int)sizeof(float), adj_dev, m, st));
+        CU(cudaMemcpyAsync(ix->norms + o0, bounce, (size_t)(o1 - o0) * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        ix->st.n_kernel_launches += 2;
+    }
+    CU(cudaStreamSynchronize(st));
     ix->ntotal = new_total;
     ix->max_norm_dirty = true;
     ix->st.n_rows_removed += m;
@@ -909,27 +814,26 @@ extern "C" int b200r_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, 
     return B200R_OK;
 }
 
-extern "C" int b200r_reconstruct(b200r_index* ix, int64_t key, float* out) {
-    if (!ix || !out) return fail(B200R_E_INVALID, "b200r_reconstruct: null argument");
+int leaf_reconstruct(b200r_index* ix, int64_t key, float* out) {
     std::lock_guard<std::mutex> lk(ix->mu);
     if (key < 0 || key >= ix->ntotal)
         return fail(B200R_E_INVALID, "b200r_reconstruct: key %lld out of range [0, %lld)", (long long)key,
                     (long long)ix->ntotal);
     DeviceGuard g(ix->device);
     if (ix->data_ev_set) CU(cudaStreamWaitEvent(ix->stream, ix->data_ev, 0));
-    float* tmp = nullptr;
-    CU(cudaMalloc(&tmp, (size_t)ix->d * sizeof(float)));
-    cudaError_t e = launch_row_to_f32(ix->rows + (size_t)key * ix->row_bytes, ix->d, ix->bf16, tmp, ix->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out, tmp, (size_t)ix->d * sizeof(float), cudaMemcpyDeviceToHost, ix->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ix->stream);
-    cudaFree(tmp);
+    if (!ix->recon_dev) {  // one row of device + pinned staging, kept with the index
+        CU(cudaMalloc(&ix->recon_dev, (size_t)ix->d * sizeof(float)));
+        CU(cudaMallocHost(&ix->recon_pin, (size_t)ix->d * sizeof(float)));
+    }
+    CU(launch_row_to_f32(ix->rows + (size_t)key * ix->row_bytes, ix->d, ix->bf16, ix->recon_dev, ix->stream));
     ix->st.n_kernel_launches++;
-    if (e != cudaSuccess) return fail(B200R_E_CUDA, "b200r_reconstruct: %s", cudaGetErrorString(e));
+    CU(cudaMemcpyAsync(ix->recon_pin, ix->recon_dev, (size_t)ix->d * sizeof(float), cudaMemcpyDeviceToHost, ix->stream));
+    CU(cudaStreamSynchronize(ix->stream));
+    memcpy(out, ix->recon_pin, (size_t)ix->d * sizeof(float));
     return B200R_OK;
 }
 
-extern "C" int b200r_reconstruct_batch(b200r_index* ix, const int64_t* keys, int64_t n, float* out) {
-    if (!ix) return fail(B200R_E_INVALID, "b200r_reconstruct_batch: null index");
+int leaf_reconstruct_batch(b200r_index* ix, const int64_t* keys, int64_t n, float* out) {
     if (n < 0 || (n > 0 && (!keys || !out))) return fail(B200R_E_INVALID, "b200r_reconstruct_batch: bad arguments");
     if (n == 0) return B200R_OK;
     std::lock_guard<std::mutex> lk(ix->mu);
@@ -959,12 +863,58 @@ extern "C" int b200r_reconstruct_batch(b200r_index* ix, const int64_t* keys, int
     return B200R_OK;
 }
 
+// rows [r0, r0+n) as fp32 [n][d] into a device buffer on this GPU; synchronised on return
+int leaf_rows_to_device_f32(b200r_index* ix, int64_t r0, int64_t n, float* dev_out) {
+    std::lock_guard<std::mutex> lk(ix->mu);
+    if (r0 < 0 || n < 0 || r0 + n > ix->ntotal) return fail(B200R_E_INVALID, "row range out of bounds");
+    if (n == 0) return B200R_OK;
+    DeviceGuard g(ix->device);
+    if (ix->data_ev_set) CU(cudaStreamWaitEvent(ix->stream, ix->data_ev, 0));
+    CU(launch_rows_to_f32(ix->rows + (size_t)r0 * ix->row_bytes, ix->row_bytes, ix->d, ix->bf16, nullptr, n, dev_out,
+                          ix->stream));
+    ix->st.n_kernel_launches++;
+    CU(cudaStreamSynchronize(ix->stream));
+    return B200R_OK;
+}
+
+// rows [r0, r0+n) as fp32 without the padding columns into a host buffer, in bounded chunks
+int leaf_read_rows(b200r_index* ix, int64_t r0, int64_t n, float* out) {
+    std::lock_guard<std::mutex> lk(ix->mu);
+    if (r0 < 0 || n < 0 || r0 + n > ix->ntotal) return fail(B200R_E_INVALID, "row range out of bounds");
+    if (n == 0) return B200R_OK;
+    DeviceGuard g(ix->device);
+    if (ix->data_ev_set) CU(cudaStreamWaitEvent(ix->stream, ix->data_ev, 0));
+    const int d = ix->d;
+    const bool direct = !ix->bf16 && ix->d_pad == ix->d;  // stored rows are already packed fp32
+    const int64_t chunk = std::max<int64_t>(1, (int64_t)((32u << 20) / ((size_t)d * 4)));
+    float* dev = nullptr;
+    cudaError_t e = direct ? cudaSuccess : cudaMalloc(&dev, (size_t)std::min(chunk, n) * d * 4);
+    for (int64_t c0 = 0; e == cudaSuccess && c0 < n; c0 += chunk) {
+        const int64_t m = std::min(chunk, n - c0);
+        const uint8_t* src = ix->rows + (size_t)(r0 + c0) * ix->row_bytes;
+        if (direct) {
+            e = cudaMemcpyAsync(out + (size_t)c0 * d, src, (size_t)m * d * 4, cudaMemcpyDeviceToHost, ix->stream);
+        } else {
+            e = launch_rows_to_f32(src, ix->row_bytes, d, ix->bf16, nullptr, m, dev, ix->stream);
+            ix->st.n_kernel_launches++;
+            if (e == cudaSuccess)
+                e = cudaMemcpyAsync(out + (size_t)c0 * d, dev, (size_t)m * d * 4, cudaMemcpyDeviceToHost, ix->stream);
+        }
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ix->stream);
+    }
+    cudaFree(dev);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(e == cudaErrorMemoryAllocation ? B200R_E_NOMEM : B200R_E_CUDA, "reading rows back: %s",
+                    cudaGetErrorString(e));
+    }
+    return B200R_OK;
+}
+
 // ---------------------------------------------------------------------------
 // merge_from: append another index's rows, empty the other index
 // ---------------------------------------------------------------------------
-extern "C" int b200r_merge_from(b200r_index* dst, b200r_index* src) {
-    if (!dst || !src) return fail(B200R_E_INVALID, "b200r_merge_from: null index");
-    if (dst == src) return fail(B200R_E_INVALID, "b200r_merge_from: an index cannot be merged into itself");
+int leaf_merge_from(b200r_index* dst, b200r_index* src) {
     // faiss check_compatible_for_merge: same d, metric and index type (here also the storage and the GPU)
     if (dst->d != src->d || dst->l2 != src->l2 || dst->bf16 != src->bf16)
         return fail(B200R_E_INVALID, "b200r_merge_from: indexes are not compatible (dim %d/%d, metric or storage differ)",
@@ -1017,171 +967,4 @@ extern "C" int b200r_merge_from(b200r_index* dst, b200r_index* src) {
     return B200R_OK;
 }
 
-// ---------------------------------------------------------------------------
-// stand-alone normalise and merge
-// ---------------------------------------------------------------------------
-extern "C" int b200r_normalize_l2(float* x, int64_t n, int32_t d, int mem_kind, int32_t device, void* stream) {
-    if (n < 0 || d <= 0) return fail(B200R_E_INVALID, "b200r_normalize_l2: bad shape");
-    if (n == 0) return B200R_OK;
-    if (!x) return fail(B200R_E_INVALID, "b200r_normalize_l2: null data");
-    DeviceGuard g(device);
-    if (!g.ok) return fail(B200R_E_CUDA, "cudaSetDevice(%d) failed", device);
-    cudaStream_t st = (cudaStream_t)stream;
-    if (mem_kind == B200R_DEVICE) {
-        CU(launch_normalize(x, n, d, st));
-        return B200R_OK;
-    }
-    if (mem_kind != B200R_HOST) return fail(B200R_E_INVALID, "b200r_normalize_l2: bad mem_kind");
-    const size_t row = (size_t)d * sizeof(float);
-    const int64_t chunk = std::max<int64_t>(1, (int64_t)((64u << 20) / row));
-    float* dev = nullptr;
-    CU(cudaMalloc(&dev, (size_t)std::min(chunk, n) * row));
-    cudaError_t e = cudaSuccess;
-    for (int64_t r0 = 0; r0 < n && e == cudaSuccess; r0 += chunk) {
-        const int64_t m = std::min(chunk, n - r0);
-        e = cudaMemcpyAsync(dev, x + r0 * d, (size_t)m * row, cudaMemcpyHostToDevice, st);
-        if (e == cudaSuccess) e = launch_normalize(dev, m, d, st);
-        if (e == cudaSuccess) e = cudaMemcpyAsync(x + r0 * d, dev, (size_t)m * row, cudaMemcpyDeviceToHost, st);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    }
-    cudaFree(dev);
-    if (e != cudaSuccess) return fail(B200R_E_CUDA, "b200r_normalize_l2: %s", cudaGetErrorString(e));
-    return B200R_OK;
-}
-
-extern "C" int b200r_merge_topk(int32_t metric, const float* cand_D, const int64_t* cand_I, int64_t nq, int32_t n_lists,
-                                int32_t k_in, int64_t stride_D, int64_t stride_I, int32_t k_out, float* D, int64_t* I,
-                                int32_t device, void* stream) {
-    if (metric != B200R_METRIC_INNER_PRODUCT && metric != B200R_METRIC_L2)
-        return fail(B200R_E_INVALID, "b200r_merge_topk: bad metric");
-    if (nq < 0 || n_lists < 1 || k_in < 1 || k_out < 1 || stride_D < 0 || stride_I < 0)
-        return fail(B200R_E_INVALID, "b200r_merge_topk: bad shape");
-    if (k_out > kMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_merge_topk: k_out %d > %d", k_out, kMaxK);
-    if (nq == 0) return B200R_OK;
-    if (!cand_D || !cand_I || !D || !I) return fail(B200R_E_INVALID, "b200r_merge_topk: null buffer");
-    DeviceGuard g(device);
-    if (!g.ok) return fail(B200R_E_CUDA, "cudaSetDevice(%d) failed", device);
-    CU(launch_merge(metric == B200R_METRIC_L2, cand_D, cand_I, nq, n_lists, k_in, stride_D, stride_I, k_out, D, I,
-                    (cudaStream_t)stream));
-    return B200R_OK;
-}
-
-// ---------------------------------------------------------------------------
-// save / load: faiss flat-index file ("IxF2" / "IxFI"), fp32 payload
-//   u32 fourcc | i32 d | i64 ntotal | i64 dummy(1<<20) x2 | u8 is_trained | i32 metric |
-//   u64 n_floats | fp32 data          (faiss/impl/index_write.cpp write_index_header +
-//   WRITEXBVECTOR(codes))
-// ---------------------------------------------------------------------------
-static uint32_t fourcc(const char* s) {
-    return (uint32_t)(uint8_t)s[0] | ((uint32_t)(uint8_t)s[1] << 8) | ((uint32_t)(uint8_t)s[2] << 16) |
-           ((uint32_t)(uint8_t)s[3] << 24);
-}
-
-extern "C" int b200r_save(b200r_index* ix, const char* path) {
-    if (!ix || !path) return fail(B200R_E_INVALID, "b200r_save: null argument");
-    std::lock_guard<std::mutex> lk(ix->mu);
-    DeviceGuard g(ix->device);
-    if (ix->data_ev_set) cudaStreamWaitEvent(ix->stream, ix->data_ev, 0);
-    FILE* f = fopen(path, "wb");
-    if (!f) return fail(B200R_E_IO, "b200r_save: cannot open %s", path);
-    const uint32_t h = fourcc(ix->l2 ? "IxF2" : "IxFI");
-    const int32_t d = ix->d;
-    const int64_t nt = ix->ntotal, dummy = 1 << 20;
-    const uint8_t trained = 1;
-    const int32_t metric = ix->cfg.metric;
-    const uint64_t nfloats = (uint64_t)nt * (uint64_t)d;
-    bool ok = fwrite(&h, 4, 1, f) == 1 && fwrite(&d, 4, 1, f) == 1 && fwrite(&nt, 8, 1, f) == 1 &&
-              fwrite(&dummy, 8, 1, f) == 1 && fwrite(&dummy, 8, 1, f) == 1 && fwrite(&trained, 1, 1, f) == 1 &&
-              fwrite(&metric, 4, 1, f) == 1 && fwrite(&nfloats, 8, 1, f) == 1;
-    // rows go out as fp32 without the padding columns, in bounded chunks
-    const int64_t chunk = std::max<int64_t>(1, (int64_t)((32u << 20) / ((size_t)d * 4)));
-    float* dev = nullptr;
-    float* host = nullptr;
-    cudaError_t e = cudaMalloc(&dev, (size_t)chunk * d * 4);
-    if (e == cudaSuccess) e = cudaMallocHost(&host, (size_t)chunk * d * 4);
-    for (int64_t r0 = 0; ok && e == cudaSuccess && r0 < nt; r0 += chunk) {
-        const int64_t m = std::min(chunk, nt - r0);
-        if (!ix->bf16 && ix->d_pad == ix->d) {
-            e = cudaMemcpyAsync(host, ix->rows + (size_t)r0 * ix->row_bytes, (size_t)m * d * 4, cudaMemcpyDeviceToHost,
-                                ix->stream);
-        } else {
-            for (int64_t r = 0; r < m && e == cudaSuccess; r++)
-                e = launch_row_to_f32(ix->rows + (size_t)(r0 + r) * ix->row_bytes, d, ix->bf16, dev + r * d, ix->stream);
-            if (e == cudaSuccess)
-                e = cudaMemcpyAsync(host, dev, (size_t)m * d * 4, cudaMemcpyDeviceToHost, ix->stream);
-        }
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ix->stream);
-        if (e == cudaSuccess) ok = fwrite(host, (size_t)d * 4, (size_t)m, f) == (size_t)m;
-    }
-    cudaFree(dev);
-    cudaFreeHost(host);
-    ok = (fclose(f) == 0) && ok;
-    if (e != cudaSuccess) return fail(B200R_E_CUDA, "b200r_save: %s", cudaGetErrorString(e));
-    if (!ok) return fail(B200R_E_IO, "b200r_save: write to %s failed", path);
-    return B200R_OK;
-}
-
-extern "C" int b200r_load(const char* path, const b200r_config* cfg, b200r_index** out) {
-    if (!path || !cfg || !out) return fail(B200R_E_INVALID, "b200r_load: null argument");
-    *out = nullptr;
-    FILE* f = fopen(path, "rb");
-    if (!f) return fail(B200R_E_IO, "b200r_load: cannot open %s", path);
-    uint32_t h = 0;
-    int32_t d = 0, metric = 0;
-    int64_t nt = 0, dummy = 0;
-    uint8_t trained = 0;
-    uint64_t nfloats = 0;
-    bool ok = fread(&h, 4, 1, f) == 1 && fread(&d, 4, 1, f) == 1 && fread(&nt, 8, 1, f) == 1 &&
-              fread(&dummy, 8, 1, f) == 1 && fread(&dummy, 8, 1, f) == 1 && fread(&trained, 1, 1, f) == 1 &&
-              fread(&metric, 4, 1, f) == 1;
-    if (ok && metric > 1) {
-        float metric_arg;
-        ok = fread(&metric_arg, 4, 1, f) == 1;
-    }
-    ok = ok && fread(&nfloats, 8, 1, f) == 1;
-    if (!ok || (h != fourcc("IxF2") && h != fourcc("IxFI") && h != fourcc("IxFl"))) {
-        fclose(f);
-        return fail(B200R_E_IO, "b200r_load: %s is not a faiss flat index file", path);
-    }
-    if (metric != B200R_METRIC_INNER_PRODUCT && metric != B200R_METRIC_L2) {
-        fclose(f);
-        return fail(B200R_E_UNSUPPORTED, "b200r_load: metric type %d is not supported", metric);
-    }
-    if (d <= 0 || nt < 0 || nfloats != (uint64_t)nt * (uint64_t)d) {
-        fclose(f);
-        return fail(B200R_E_IO, "b200r_load: inconsistent header in %s", path);
-    }
-    b200r_config c = *cfg;
-    c.dim = d;
-    c.metric = metric;
-    c.reserve_rows = std::max<int64_t>(c.reserve_rows, nt);
-    const int norm_on_add = c.normalize_on_add;
-    c.normalize_on_add = 0;  // stored rows are loaded verbatim
-    b200r_index* ix = nullptr;
-    int rc = b200r_create(&c, &ix);
-    if (rc != B200R_OK) {
-        fclose(f);
-        return rc;
-    }
-    const int64_t chunk = std::max<int64_t>(1, (int64_t)((32u << 20) / ((size_t)d * 4)));
-    std::vector<float> buf((size_t)std::min<int64_t>(chunk, std::max<int64_t>(nt, 1)) * d);
-    for (int64_t r0 = 0; r0 < nt; r0 += chunk) {
-        const int64_t m = std::min(chunk, nt - r0);
-        if (fread(buf.data(), (size_t)d * 4, (size_t)m, f) != (size_t)m) {
-            fclose(f);
-            free_index(ix);
-            return fail(B200R_E_IO, "b200r_load: %s is truncated", path);
-        }
-        rc = b200r_add(ix, buf.data(), m, B200R_F32, B200R_HOST, nullptr);
-        if (rc != B200R_OK) {
-            fclose(f);
-            free_index(ix);
-            return rc;
-        }
-    }
-    fclose(f);
-    ix->cfg.normalize_on_add = norm_on_add;
-    ix->st.n_rows_added = 0;
-    *out = ix;
-    return B200R_OK;
-}
+}  // namespace b200r

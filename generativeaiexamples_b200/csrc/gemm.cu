@@ -28,8 +28,7 @@
 //   warp 2 = TMEM allocator, warps 4.. = epilogue: tcgen05.ld 32 columns at a time, each
 //   THREAD owns one query (TMEM lane), keeps its running K'-th best in a register and its
 //   sorted survivor list in local memory (touched only on the rare insert).
-#include "common.cuh"
-#include "kernels.h"
+#include "index.h"
 
 #include <cuda.h>
 #include <cstdlib>
@@ -1227,8 +1226,8 @@ void gemm_aux_layout(void* aux, unsigned** hist, float** qscale, int** gthr, int
 // per doubling of K' (more chunks take the append path), one scan-path fallback costs about as
 // much as the whole block, so K' is the smallest value that gave no fallback plus a margin.
 int gemm_kp_cap(int k, int filter, int boost_pct) {
-    if (const char* ev = getenv("B200R_GEMM_KPCAP")) {  // tuning knob
-        if (atoi(ev) == 256 || k + kGemmSlack > 32) return 256;
+    if (knobs().gemm_kpcap > 0) {  // tuning knob
+        if (knobs().gemm_kpcap == 256 || k + kGemmSlack > 32) return 256;
         return 32;
     }
     if (filter != kFilterTf32 || boost_pct > 100) return 256;
@@ -1242,7 +1241,7 @@ int gemm_kprime(int k, int filter, int boost_pct) {
     if (k + kGemmSlack <= 32) kp = 32;
     if (filter == kFilterBf16) kp = 3 * k + 34;
     if (filter == kFilterShadow) kp = 4 * k + 72;
-    if (const char* ev = getenv("B200R_GEMM_KPRIME")) kp = atoi(ev) > k ? atoi(ev) : k + 1;  // tuning knob
+    if (knobs().gemm_kprime > 0) kp = knobs().gemm_kprime > k ? knobs().gemm_kprime : k + 1;  // tuning knob
     if (boost_pct > 100) kp = (int)((int64_t)kp * boost_pct / 100);
     const int cap = k + 512;
     return kp < cap ? kp : cap;
@@ -1325,7 +1324,7 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     const int kprime = gemm_kprime(a.k, filter, boost);
     const int64_t n_tiles_all = (a.n_rows + kGemmTileN - 1) / kGemmTileN;
     int cs = 2;  // query-operand multicast over CTA pairs
-    if (const char* ev = getenv("B200R_GEMM_CLUSTER")) cs = atoi(ev) == 1 ? 1 : 2;
+    if (knobs().gemm_cluster > 0) cs = knobs().gemm_cluster == 1 ? 1 : 2;
     if (n_tiles_all < 2 || a.num_sms < 2) cs = 1;
     if (cs == 2) {
         // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load
@@ -1342,7 +1341,7 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     }
     // more than 128 queries: 2-CTA MMA over CTA pairs (double-buffered accumulators) unless turned off
     bool pair = MT == 2 && cs == 2;
-    if (const char* ev = getenv("B200R_GEMM_PAIR")) pair = pair && atoi(ev) != 0;
+    if (knobs().gemm_pair >= 0) pair = pair && knobs().gemm_pair != 0;
     if (pair) cs = 3;
     // what the filter pass streams: the corpus itself, or its bf16 shadow
     const bool fbf16 = a.bf16 || a.shadow != nullptr;
@@ -1363,12 +1362,8 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     p.cand = a.cand;
     p.gthr = a.gthr;
     p.corpus = fcorpus;
-    {
-        const char* ev = getenv("B200R_GEMM_PREFETCH");  // tuning knob
-        p.prefetch_tiles = ev ? atoi(ev) : 0;
-        const char* dv = getenv("B200R_GEMM_DEBUG_NOSELECT");
-        p.debug_no_select = dv ? atoi(dv) : 0;  // measured: the extra L2 fill stream hurts (r01 notes)
-    }
+    p.prefetch_tiles = knobs().gemm_prefetch;    // tuning knob; measured: the extra L2 fill stream hurts (r01 notes)
+    p.debug_no_select = knobs().gemm_noselect;
     p.hist = a.hist;
     p.list_counts = a.list_counts;
     p.overflow = a.overflow;
@@ -1385,9 +1380,8 @@ cudaError_t launch_gemm_search(const GemmSearchArgs& a, cudaStream_t st) {
     {
         // warm-up pays one extra tile per CTA; worth it when the lists are large (memory heaps)
         // and every CTA has several tiles
-        const char* wv = getenv("B200R_GEMM_WARMUP");
         p.warmup = kp_cap > 32 ? 1 : 0;  // the append-only lists of the large-K' variant rely on it
-        if (wv && kp_cap == 32) p.warmup = atoi(wv);
+        if (knobs().gemm_warmup >= 0 && kp_cap == 32) p.warmup = knobs().gemm_warmup;
     }
     cudaError_t e;
     if (fbf16) {

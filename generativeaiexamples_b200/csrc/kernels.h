@@ -28,9 +28,10 @@ struct ScanParams {
     float* out_d;         // [nq][k]
     int64_t* out_i;       // [nq][k]
     int64_t id_base;      // added to every returned id (row-sharded multi-GPU)
-    // fused exchange (xchg_world > 0): the final writer stores this shard's result straight into every
-    // peer's exchange buffer over NVLink and raises a flag there, instead of writing out_d / out_i
-    int xchg_world, xchg_rank;
+    // fused exchange (xchg_ntargets > 0): the final writer stores this shard's result straight into slot
+    // [xchg_rank] of every target exchange buffer (over NVLink when it is a peer's) and raises a flag
+    // there, instead of writing out_d / out_i.  Targets = every rank (allgather) or the primary GPU alone.
+    int xchg_ntargets, xchg_rank;
     uint32_t xchg_epoch;
     uint8_t* xchg_peer[8];  // peer-mapped base of each rank's exchange buffer (layout below)
     // flagged re-run (launch_scan_flagged): the queries to serve are q[flag_list[0..*flag_count)], their
@@ -82,6 +83,13 @@ cudaError_t launch_gather_rows(const void* src, void* out, int64_t o0, int64_t o
 cudaError_t launch_merge(bool l2, const float* cand_d, const int64_t* cand_i, int64_t nq, int n_lists, int k_in,
                          int64_t stride_d, int64_t stride_i, int k_out, float* out_d, int64_t* out_i,
                          cudaStream_t st);
+
+// final select of the single-process multi-GPU index: n_lists sorted per-shard lists in the slots of a
+// gather buffer, local row numbers translated to global positions through per-shard segment tables
+cudaError_t launch_merge_shards(bool l2, const uint8_t* base, int64_t slot_stride, int64_t ids_off, int n_lists, int nq,
+                                int k_in, int k_out, const int* seg_off, const int64_t* seg_lstart,
+                                const int64_t* seg_gbase, int64_t id_base, float* out_d, int64_t* out_i, uint8_t* xbuf,
+                                uint32_t wait_epoch, int* status_out, cudaStream_t st);
 
 // K3 (gemm.cu): tcgen05 GEMM filter + exact re-score for one block of <= 256 queries
 constexpr int kGemmSlack = 22;       // survivors kept beyond k when k + slack <= 32

@@ -18,8 +18,7 @@
 //  * epilogue: lists -> shared memory -> per-CTA merge -> global scratch; the last
 //    CTA to finish (atomic ticket) merges all CTA lists and writes D/I.  The score
 //    vector is never written to HBM.
-#include "common.cuh"
-#include "kernels.h"
+#include "index.h"
 
 #include <cooperative_groups.h>
 
@@ -279,7 +278,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
         WarpTopK<KPL, L2> m;
         m.init(p.k);
         m.template merge_from<false>(sm_lists + (size_t)warp * NW * KCAP, 0, NW, 1, KCAP);
-        if (FLAGGED || p.xchg_world == 0) {
+        if (FLAGGED || p.xchg_ntargets == 0) {
             // result row: the query's own position (flagged re-run) or its slot in this launch
             const size_t orow = FLAGGED ? (size_t)p.flag_list[grp * NQ + warp] : (size_t)warp;
 #pragma unroll
@@ -294,7 +293,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
             // fused exchange: this shard's top-k goes straight into slot [my rank] of EVERY rank's
             // exchange buffer (plain stores to peer-mapped addresses = NVLink writes)
             const size_t slot = (size_t)(p.xchg_epoch & 1u) * kXchgParityBytes + (size_t)p.xchg_rank * kXchgSlotBytes;
-            for (int r = 0; r < p.xchg_world; r++) {
+            for (int r = 0; r < p.xchg_ntargets; r++) {
                 float* pd = reinterpret_cast<float*>(p.xchg_peer[r] + slot);
                 int64_t* pi = reinterpret_cast<int64_t*>(p.xchg_peer[r] + slot + kXchgIdOffset);
 #pragma unroll
@@ -309,9 +308,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
             __threadfence_system();
         }
     }
-    if (!FLAGGED && p.xchg_world > 0) {
+    if (!FLAGGED && p.xchg_ntargets > 0) {
         __syncthreads();  // every result store of this CTA is fenced; now raise the flags
-        if (threadIdx.x < p.xchg_world) {
+        if (threadIdx.x < p.xchg_ntargets) {
             uint32_t* flag = reinterpret_cast<uint32_t*>(p.xchg_peer[threadIdx.x] + kXchgFlagOffset +
                                                         ((p.xchg_epoch & 1u) * kXchgMaxWorld + p.xchg_rank) * 128);
             asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(p.xchg_epoch) : "memory");
@@ -386,8 +385,8 @@ static cudaError_t launch_scan_impl(ScanParams p, int nq, bool l2, bool bf16, in
     // 48 KB x 4 = 5.69, 32 KB x 6 = 5.74, 16 KB x 12 = 6.39, 8 KB x 16 = 8.00.
     int stage_bytes = 64 * 1024;
     int max_stages = 3;
-    if (const char* ev = getenv("B200R_SCAN_STAGE_KB")) stage_bytes = atoi(ev) * 1024;  // tuning knobs
-    if (const char* ev = getenv("B200R_SCAN_STAGES")) max_stages = atoi(ev);
+    if (knobs().scan_stage_kb > 0) stage_bytes = knobs().scan_stage_kb * 1024;  // tuning knobs
+    if (knobs().scan_stages > 0) max_stages = knobs().scan_stages;
     if (p.row_bytes > stage_bytes) stage_bytes = (p.row_bytes + 127) / 128 * 128;
     int R = stage_bytes / p.row_bytes;
     if (smem_limit < q_bytes + bar_bytes + 2 * (size_t)stage_bytes) return cudaErrorInvalidValue;
@@ -454,7 +453,7 @@ cudaError_t launch_scan_flagged(ScanParams p, const int* fail_flags, int64_t nq_
     if (e != cudaSuccess) return e;
     p.flag_list = flag_list;
     p.flag_count = flag_count;
-    p.xchg_world = 0;
+    p.xchg_ntargets = 0;
     // four flagged queries per corpus pass where the four-query variants exist and fit
     const int per_pass = p.k > kScanMaxK ? 1 : scan_queries_per_launch(p.d, p.row_bytes, smem_limit);
     return launch_scan_impl(p, per_pass, l2, bf16, num_sms, smem_limit, st, nullptr, true);

@@ -9,8 +9,10 @@ convention (``RAG/src/chain_server/configuration_wizard.py:38``,
 so an existing FAISS deployment switches over by installing this package.
 
 Engine options (no reference counterpart) use the ``B200R_`` prefix:
-``B200R_DEVICE`` (CUDA ordinal, default 0), ``B200R_STORAGE`` (``f32`` | ``bf16``),
-``B200R_RESERVE_ROWS`` (rows of HBM reserved up front).
+``B200R_DEVICE`` (CUDA ordinal, default 0), ``B200R_DEVICES`` (comma-separated ordinals, e.g.
+``0,1,2,3,4,5,6,7``: ONE store whose rows are spread over those GPUs of this process -- the chain
+server is a single process, ``RAG/src/chain_server/server.py:203-238``), ``B200R_STORAGE``
+(``f32`` | ``bf16``), ``B200R_RESERVE_ROWS`` (rows of HBM reserved up front).
 """
 from __future__ import annotations
 
@@ -37,7 +39,8 @@ def create_vectorstore_langchain(document_embedder, collection_name: str = "", *
         raise ValueError(f"{name} vector database is not supported")
     d = int(dimensions if dimensions is not None else os.getenv("APP_EMBEDDINGS_DIMENSIONS", "1024"))
     storage = os.getenv("B200R_STORAGE", "f32")
-    index = B200IndexFlatL2(d, device=int(os.getenv("B200R_DEVICE", "0")), storage=storage,
+    devices = [int(t) for t in os.getenv("B200R_DEVICES", "").replace(" ", "").split(",") if t != ""]
+    index = B200IndexFlatL2(d, device=int(os.getenv("B200R_DEVICE", "0")), devices=devices or None, storage=storage,
                             reserve_rows=int(os.getenv("B200R_RESERVE_ROWS", "0")),
                             # opt-in bf16 copy of the fp32 rows for the filter pass (+50 % HBM, same answers)
                             shadow_bf16=storage == "f32" and os.getenv("B200R_SHADOW_BF16", "0") == "1")
@@ -54,21 +57,32 @@ def get_vectorstore(vectorstore: Optional[B200FlatVectorStore], document_embedde
 
 
 def get_docs_vectorstore_langchain(vectorstore: B200FlatVectorStore):
-    """utils.py:492-529, FAISS branch (:506-510): file names of the ingested documents."""
-    in_memory_docstore = vectorstore.docstore._dict
-    filenames = [os.path.basename(doc.metadata["source"]) for doc in in_memory_docstore.values()]
-    return list(dict.fromkeys(filenames))  # the reference returns list(set(...)): same members
+    """utils.py:492-529, FAISS branch (:506-510): file names of the ingested documents.  As in the
+    reference any failure (a document without ``metadata['source']``, a store without a docstore)
+    is logged and yields ``[]``."""
+    try:
+        in_memory_docstore = vectorstore.docstore._dict
+        filenames = [os.path.basename(doc.metadata["source"]) for doc in in_memory_docstore.values()]
+        return list(dict.fromkeys(filenames))  # the reference returns list(set(...)): same members
+    except Exception as e:
+        logger.error(f"Error occurred while retrieving documents: {e}")
+    return []
 
 
 def del_docs_vectorstore_langchain(vectorstore: B200FlatVectorStore, filenames) -> bool:
-    """utils.py:532-603, FAISS branch (:546-560): delete every chunk of the named files."""
-    in_memory_docstore = vectorstore.docstore._dict
-    for filename in filenames:
-        ids_list = [doc_id for doc_id, doc_data in in_memory_docstore.items()
-                    if os.path.basename(doc_data.metadata["source"]) == filename]
-        if not ids_list:
-            logger.info("File does not exist in the vectorstore")
-            return False
-        vectorstore.delete(ids_list)
-        logger.info(f"Deleted documents with filenames {filename}")
+    """utils.py:532-603, FAISS branch (:546-560): delete every chunk of the named files; ``False`` when
+    a file is unknown or, as in the reference, when anything raises on the way."""
+    try:
+        in_memory_docstore = vectorstore.docstore._dict
+        for filename in filenames:
+            ids_list = [doc_id for doc_id, doc_data in in_memory_docstore.items()
+                        if os.path.basename(doc_data.metadata["source"]) == filename]
+            if not ids_list:
+                logger.info("File does not exist in the vectorstore")
+                return False
+            vectorstore.delete(ids_list)
+            logger.info(f"Deleted documents with filenames {filename}")
+    except Exception as e:
+        logger.error(f"Error occurred while deleting documents: {e}")
+        return False
     return True

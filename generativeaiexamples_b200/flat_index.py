@@ -42,7 +42,8 @@ class B200IndexFlat:
 
     def __init__(self, d: int, metric: int = METRIC_L2, *, storage: str = "f32", device: int = 0,
                  normalize_on_add: bool = False, normalize_queries: bool = False, reserve_rows: int = 0,
-                 id_base: int = 0, search_path: int = _lib.PATH_AUTO, shadow_bf16: bool = False):
+                 id_base: int = 0, search_path: int = _lib.PATH_AUTO, shadow_bf16: bool = False,
+                 devices=None):
         if storage not in ("f32", "bf16"):
             raise ValueError("storage must be 'f32' or 'bf16'")
         if shadow_bf16 and storage != "f32":
@@ -53,11 +54,16 @@ class B200IndexFlat:
         self.metric_type = int(metric)
         self.is_trained = True
         self.storage = storage
-        self.device = int(device)
-        cfg = _lib.Config(dim=self.d, metric=self.metric_type, storage=_lib.BF16 if storage == "bf16" else _lib.F32,
-                          normalize_on_add=int(normalize_on_add), normalize_queries=int(normalize_queries),
-                          device=self.device, search_path=int(search_path), shadow_bf16=int(bool(shadow_bf16)),
-                          reserve_rows=int(reserve_rows), id_base=int(id_base))
+        # devices=[0, 1, ...]: one index spread over several GPUs of this process (rows keep faiss's
+        # "id == position" contract; see csrc/multi.cu).  self.device is then the primary GPU, the one
+        # that CUDA tensors handed to add()/search() are expected on.
+        self.devices = [int(x) for x in devices] if devices else [int(device)]
+        self.device = self.devices[0]
+        cfg = _lib.make_config(dim=self.d, metric=self.metric_type,
+                               storage=_lib.BF16 if storage == "bf16" else _lib.F32,
+                               normalize_on_add=normalize_on_add, normalize_queries=normalize_queries,
+                               device=self.device, search_path=search_path, shadow_bf16=shadow_bf16,
+                               reserve_rows=reserve_rows, id_base=id_base, devices=self.devices)
         h = ctypes.c_void_p()
         _lib.check(self._L.b200r_create(ctypes.byref(cfg), ctypes.byref(h)))
         self._h = h
@@ -86,13 +92,14 @@ class B200IndexFlat:
         if _is_torch(x) and x.is_cuda:
             n, d = x.shape
             assert d == self.d
-            assert x.device.index == self.device, "tensor and index live on different GPUs"
+            assert x.device.index in self.devices, "tensor and index live on different GPUs"
             x = x.contiguous().to(torch.float32)
-            _lib.check(self._L.b200r_add(self._h, ctypes.c_void_p(x.data_ptr()), n, _lib.F32, _lib.DEVICE,
-                                         _torch_stream(self.device)))
-            # the ingest kernel reads x asynchronously on the caller's stream: keep it
-            # alive until that stream has passed this point
-            x.record_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.device(x.device):  # the stream handed over belongs to the tensor's GPU
+                _lib.check(self._L.b200r_add(self._h, ctypes.c_void_p(x.data_ptr()), n, _lib.F32, _lib.DEVICE,
+                                             _torch_stream(x.device.index)))
+                # the ingest kernel reads x asynchronously on the caller's stream: keep it
+                # alive until that stream has passed this point
+                x.record_stream(torch.cuda.current_stream(x.device.index))
             return
         if _is_torch(x):
             x = x.numpy()
@@ -111,17 +118,18 @@ class B200IndexFlat:
             n, d = x.shape
             assert d == self.d
             assert k > 0
-            assert x.device.index == self.device, "tensor and index live on different GPUs"
+            assert x.device.index in self.devices, "tensor and index live on different GPUs"
             x = x.contiguous().to(torch.float32)
             if D is None:
                 D = torch.empty((n, k), dtype=torch.float32, device=x.device)
             if I is None:
                 I = torch.empty((n, k), dtype=torch.int64, device=x.device)
             assert D.shape == (n, k) and I.shape == (n, k) and D.is_contiguous() and I.is_contiguous()
-            _lib.check(self._L.b200r_search(self._h, ctypes.c_void_p(x.data_ptr()), n, k, _lib.DEVICE,
-                                            ctypes.c_void_p(D.data_ptr()), ctypes.c_void_p(I.data_ptr()), _lib.DEVICE,
-                                            _torch_stream(self.device)))
-            x.record_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.device(x.device):
+                _lib.check(self._L.b200r_search(self._h, ctypes.c_void_p(x.data_ptr()), n, k, _lib.DEVICE,
+                                                ctypes.c_void_p(D.data_ptr()), ctypes.c_void_p(I.data_ptr()),
+                                                _lib.DEVICE, _torch_stream(x.device.index)))
+                x.record_stream(torch.cuda.current_stream(x.device.index))
             return D, I
         if _is_torch(x):
             x = x.numpy()
@@ -176,21 +184,22 @@ class B200IndexFlat:
         _lib.check(self._L.b200r_save(self._h, str(path).encode()))
 
     @classmethod
-    def read(cls, path: str, *, storage: str = "f32", device: int = 0, **kw) -> "B200IndexFlat":
+    def read(cls, path: str, *, storage: str = "f32", device: int = 0, devices=None, **kw) -> "B200IndexFlat":
         L = _lib.load()
         self = cls.__new__(cls)
         self._L = L
         self._h = None
-        cfg = _lib.Config(dim=1, metric=METRIC_L2, storage=_lib.BF16 if storage == "bf16" else _lib.F32,
-                          normalize_on_add=int(kw.get("normalize_on_add", False)),
-                          normalize_queries=int(kw.get("normalize_queries", False)), device=int(device),
-                          search_path=int(kw.get("search_path", _lib.PATH_AUTO)),
-                          shadow_bf16=int(bool(kw.get("shadow_bf16", False))), reserve_rows=0,
-                          id_base=int(kw.get("id_base", 0)))
+        self.devices = [int(x) for x in devices] if devices else [int(device)]
+        cfg = _lib.make_config(dim=1, metric=METRIC_L2, storage=_lib.BF16 if storage == "bf16" else _lib.F32,
+                               normalize_on_add=kw.get("normalize_on_add", False),
+                               normalize_queries=kw.get("normalize_queries", False), device=self.devices[0],
+                               search_path=kw.get("search_path", _lib.PATH_AUTO),
+                               shadow_bf16=kw.get("shadow_bf16", False), reserve_rows=0,
+                               id_base=kw.get("id_base", 0), devices=self.devices)
         h = ctypes.c_void_p()
         _lib.check(L.b200r_load(str(path).encode(), ctypes.byref(cfg), ctypes.byref(h)))
         self._h = h
-        self.storage, self.device, self.is_trained = storage, int(device), True
+        self.storage, self.device, self.is_trained = storage, self.devices[0], True
         # d and metric come from the file: recover them through a zero-row probe
         st = self.stats()
         self.d, self.metric_type = _read_header(path)

@@ -206,7 +206,15 @@ class ShardedFlatIndex:
                                                        torch.cuda.current_stream(self.device).cuda_stream)))
                 if as_numpy:
                     ws["out_pin"].copy_(out, non_blocking=True)
-                    torch.cuda.current_stream(self.device).synchronize()
+                    # the select kernel gives a peer 2 s to deliver; a miss sets a status word in this
+                    # rank's buffer (b200r_exchange_status reads and clears it after synchronising)
+                    status = ctypes.c_int32(0)
+                    _lib.check(L.b200r_exchange_status(ctypes.c_void_p(xchg["buf"].data_ptr()), self.device,
+                                                       ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream),
+                                                       ctypes.byref(status)))
+                    if status.value != 0:
+                        raise RuntimeError(f"fused exchange: rank {status.value - 1} did not deliver its candidates "
+                                           "within 2 s (set B200R_FUSED_EXCHANGE=0 to use the NCCL allgather)")
                     host = ws["out_pin"].numpy()
                     return (host[: nq * k * 4].view(np.float32).reshape(nq, k).copy(),
                             host[d_bytes:].view(np.int64).reshape(nq, k).copy())

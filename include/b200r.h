@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define B200R_VERSION 100
+#define B200R_VERSION 200
 
 /* status codes */
 #define B200R_OK 0
@@ -57,6 +57,8 @@ extern "C" {
 #define B200R_PATH_SCAN 1
 #define B200R_PATH_GEMM 2
 
+#define B200R_MAX_DEVICES 8
+
 typedef struct b200r_index b200r_index; /* opaque */
 
 typedef struct b200r_config {
@@ -75,7 +77,13 @@ typedef struct b200r_config {
                                   faiss counterpart.  0 = off (default). */
     int64_t reserve_rows;      /* HBM reserved up front (0 = grow on demand) */
     int64_t id_base;           /* added to every returned id: global position of local row 0
-                                  when the corpus is row-sharded over several GPUs */
+                                  when the corpus is row-sharded over several processes */
+    int32_t n_devices;         /* 0 or 1: the index lives on `device`.  2..8: ONE index whose rows are spread
+                                  over the GPUs device_ids[0..n_devices) of this process (SURVEY.md section 8e:
+                                  the reference's chain server is a single process,
+                                  RAG/src/chain_server/server.py:203-238).  Rows keep faiss's "id == position"
+                                  contract; every entry point below works on such an index. */
+    int32_t device_ids[B200R_MAX_DEVICES];
 } b200r_config;
 
 typedef struct b200r_stats {
@@ -94,6 +102,12 @@ typedef struct b200r_stats {
     double last_search_ms;       /* device time of the last search (events), 0 if timing is off */
     int64_t n_gemm_fallbacks;    /* queries of the GEMM path whose containment check failed and
                                     were re-run on the scan path (results are exact either way) */
+    double last_kernel_us;       /* with timing on: device time of the scoring kernels of the last search
+                                    (multi-GPU: the slowest shard) */
+    double last_exchange_us;     /* multi-GPU, timing on: what the last search took beyond that -- the
+                                    candidate exchange over NVLink plus the final select (0 on one GPU) */
+    int32_t n_devices;           /* GPUs this index is spread over */
+    int32_t n_segments;          /* multi-GPU: contiguous runs of rows in the position -> (GPU, slot) map */
 } b200r_stats;
 
 /* faiss.IndexFlatL2(d) / IndexFlatIP(d)   [utils.py:306; rag_service.py:88] */
@@ -197,6 +211,10 @@ int b200r_search_noalloc(const void* corpus, int64_t n_rows, int32_t dim, int32_
 int64_t b200r_exchange_buffer_bytes(void);
 int b200r_search_exchange(b200r_index* idx, const float* q, int64_t nq, int k, void* const* peer_bufs, int32_t world,
                           int32_t rank, uint32_t epoch, float* D, int64_t* I, void* stream);
+/* After a b200r_search_exchange: synchronises `stream` and reports whether the select kernel gave up
+ * waiting for a peer (*status = 0: all arrived; r + 1: rank r's candidates did not arrive within ~2 s
+ * and the results of that call are padding).  A non-zero word is cleared.  my_buf = this rank's buffer. */
+int b200r_exchange_status(void* my_buf, int32_t device, void* stream, int32_t* status);
 
 /* index.merge_from(other)   [faiss 1.7.4 IndexFlatCodes::merge_from, reached through LangChain's
  * FAISS.merge_from: community/oran-chatbot-multimodal/vectorstore/vectorstore_updater.py:217]
@@ -214,6 +232,10 @@ int b200r_set_shadow_filter(b200r_index* idx, int32_t enabled);
 /* observability (no faiss counterpart) */
 int b200r_stats_get(b200r_index* idx, b200r_stats* out);
 int b200r_set_timing(b200r_index* idx, int32_t enabled);
+
+/* The B200R_* environment switches (README.md) are read once per process; this reads them again
+ * (tests and tuning tools change them between searches).  No faiss counterpart. */
+int b200r_reload_env(void);
 
 const char* b200r_last_error(void);
 int b200r_version(void);

@@ -40,3 +40,14 @@ def built_lib():
 
         __graft_entry__.build()
     return _lib.load()
+
+
+@pytest.fixture(autouse=True)
+def _fresh_engine_switches():
+    """libb200r reads its B200R_* environment switches once per process: tests that change them call
+    ``_lib.reload_env()``; this puts the library back in step with the restored environment."""
+    yield
+    from generativeaiexamples_b200 import _lib
+
+    if _lib._lib is not None:
+        _lib.reload_env()

@@ -27,13 +27,14 @@ def test_header_symbols_exported(built_lib):
 
 
 def test_struct_layout_matches_header():
-    # b200r_config: 8 x int32 + 2 x int64; b200r_stats: 8 x int64 + 4 x int32 + double + int64
-    assert ctypes.sizeof(_lib.Config) == 8 * 4 + 2 * 8
-    assert ctypes.sizeof(_lib.Stats) == 8 * 8 + 4 * 4 + 8 + 8
+    # b200r_config: 8 x int32 + 2 x int64 + (1 + 8) x int32 (+ tail padding to 8);
+    # b200r_stats: 8 x int64 + 4 x int32 + double + int64 + 2 x double + 2 x int32
+    assert ctypes.sizeof(_lib.Config) == 8 * 4 + 2 * 8 + 9 * 4 + 4
+    assert ctypes.sizeof(_lib.Stats) == 8 * 8 + 4 * 4 + 8 + 8 + 2 * 8 + 2 * 4
 
 
 def test_version(built_lib):
-    assert built_lib.b200r_version() == 100
+    assert built_lib.b200r_version() == 200
 
 
 def test_argument_errors_without_gpu(built_lib):

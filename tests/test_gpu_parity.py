@@ -10,7 +10,27 @@ import os
 import numpy as np
 import pytest
 
+from generativeaiexamples_b200 import _lib
+
 pytestmark = pytest.mark.gpu
+
+
+def _device_sets():
+    """Index placements every mutable-corpus test runs on: one GPU, two shards on one GPU (the
+    multi-GPU code path -- segment map, per-shard workers, gather + final select -- on a 1-GPU box)
+    and, when the box has them, two real GPUs."""
+    sets = [None, [0, 0]]
+    try:
+        import torch
+
+        if torch.cuda.device_count() >= 2:
+            sets.append([0, 1])
+    except Exception:
+        pass
+    return sets
+
+
+DEVICE_SETS = _device_sets()
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 FLT_MAX = np.finfo(np.float32).max
@@ -272,12 +292,19 @@ def test_concurrent_searches(built_lib):
     ix.close()
 
 
-def test_vectorstore_end_to_end(built_lib):
+@pytest.mark.parametrize("devices", DEVICE_SETS, ids=lambda v: "dev" + "".join(map(str, v or [0])))
+def test_vectorstore_end_to_end(built_lib, devices, monkeypatch):
     """basic_rag call sequence on the real engine against the LangChain restatement."""
     import warnings
     import zlib
 
-    from generativeaiexamples_b200 import B200FlatVectorStore, create_vectorstore_langchain
+    from generativeaiexamples_b200 import (B200FlatVectorStore, create_vectorstore_langchain,
+                                           del_docs_vectorstore_langchain, get_docs_vectorstore_langchain,
+                                           get_vectorstore)
+
+    if devices:
+        monkeypatch.setenv("B200R_DEVICES", ",".join(map(str, devices)))
+        monkeypatch.setenv("B200R_MULTI_MIN_PIECE", "16")
     from oracle.flat_ref import IndexFlatRef
     from oracle.lc_faiss_shim import RefDocstore, RefFAISS
 
@@ -297,8 +324,13 @@ def test_vectorstore_end_to_end(built_lib):
         def embed_query(self, t):
             return self._v(t)
 
-    vs = create_vectorstore_langchain(Emb(), name="b200flat", dimensions=d)
-    assert isinstance(vs, B200FlatVectorStore)
+    monkeypatch.setenv("APP_EMBEDDINGS_DIMENSIONS", str(d))
+    vs = get_vectorstore(None, Emb())  # utils.py:335-347: created lazily on first use ...
+    assert isinstance(vs, B200FlatVectorStore) and vs.index.d == d
+    assert get_vectorstore(vs, Emb()) is vs  # ... and handed back afterwards
+    assert vs.index.stats()["n_devices"] == (len(devices) if devices else 1)
+    other = create_vectorstore_langchain(Emb(), name="b200flat", dimensions=d)
+    assert isinstance(other, B200FlatVectorStore) and other is not vs
     ref = RefFAISS(Emb(), IndexFlatRef(d, 1), RefDocstore(), {})
     texts = [f"chunk {i}" for i in range(300)]
     metas = [{"source": f"/tmp-data/uploaded_files/f{i % 6}.pdf"} for i in range(300)]
@@ -323,6 +355,20 @@ def test_vectorstore_end_to_end(built_lib):
     a = vs.similarity_search("about chunk 18", k=3)
     b = ref.similarity_search("about chunk 18", k=3)
     assert [x.page_content for x in a] == [x.page_content for x in b]
+    # the chain server's document listing / deletion helpers (utils.py:492-603, FAISS branches)
+    assert sorted(get_docs_vectorstore_langchain(vs)) == [f"f{i}.pdf" for i in range(6)]
+    assert del_docs_vectorstore_langchain(vs, ["f3.pdf"]) is True
+    ref.delete([i_ for i_, m_ in zip(ids, metas) if m_["source"].endswith("f3.pdf") and i_ not in (ids[17], ids[5])])
+    assert vs.index.ntotal == ref.index.ntotal == 248 and vs.index_to_docstore_id == ref.index_to_docstore_id
+    assert sorted(get_docs_vectorstore_langchain(vs)) == [f"f{i}.pdf" for i in (0, 1, 2, 4, 5)]
+    assert del_docs_vectorstore_langchain(vs, ["never-uploaded.pdf"]) is False
+    a = vs.similarity_search_with_score("about chunk 21", k=6)
+    b = ref.similarity_search_with_score("about chunk 21", k=6)
+    assert [x.page_content for x, _ in a] == [x.page_content for x, _ in b]
+    # a chunk without metadata['source'] makes the reference log an error and answer [] / False
+    vs.add_texts(["orphan"], [{}])
+    assert get_docs_vectorstore_langchain(vs) == []
+    assert del_docs_vectorstore_langchain(vs, ["f0.pdf"]) is False
 
 
 def test_merge_kernel(built_lib):
@@ -668,8 +714,10 @@ def test_shadow_small_batches(built_lib, metric, monkeypatch):
         for big in (False, True):
             if big:
                 monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")  # treat this corpus as a large one
+                _lib.reload_env()
             else:
                 monkeypatch.delenv("B200R_GEMM_MIN_BYTES", raising=False)
+                _lib.reload_env()
             for nq, k in ((1, 10), (4, 10), (3, 1), (2, 14), (1, 100), (2, 200)):
                 b0 = ix.stats()["bytes_scanned"]
                 D, I = ix.search(q[:nq], k)
@@ -702,6 +750,7 @@ def test_small_batch_dispatch_by_corpus_size(built_lib, monkeypatch):
     D0, I0 = ix.search(q, 10)
     assert ix.stats()["last_path"] == _lib.PATH_SCAN
     monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
+    _lib.reload_env()
     for nq in (2, 3, 4):
         D1, I1 = ix.search(q[:nq], 10)
         assert ix.stats()["last_path"] == _lib.PATH_GEMM
@@ -718,6 +767,7 @@ def test_shadow_single_query_fallback(built_lib, monkeypatch):
     from generativeaiexamples_b200 import B200IndexFlatIP, _lib
 
     monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
+    _lib.reload_env()
     rng = np.random.default_rng(78)
     n, d = 20000, 1024
     x = rng.standard_normal((n, d), dtype=np.float32)
@@ -769,6 +819,7 @@ def test_shadow_survives_load_and_reset(built_lib, tmp_path, monkeypatch):
     from generativeaiexamples_b200 import B200IndexFlat, B200IndexFlatIP, _lib
 
     monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
+    _lib.reload_env()
     rng = np.random.default_rng(93)
     n, d = 9000, 200
     x = rng.standard_normal((n, d), dtype=np.float32)
@@ -815,6 +866,7 @@ def test_randomised_differential(built_lib, seed, monkeypatch):
     norm_q = bool(rng.random() < 0.3)
     if rng.random() < 0.5:
         monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
+        _lib.reload_env()
     x = rng.standard_normal((n, d), dtype=np.float32) * rng.uniform(0.3, 3.0, (n, 1)).astype(np.float32)
     q = rng.standard_normal((nq, d), dtype=np.float32)
     src = rng.integers(0, n, nq)
@@ -853,8 +905,9 @@ def test_randomised_differential(built_lib, seed, monkeypatch):
     ix.close()
 
 
+@pytest.mark.parametrize("devices", DEVICE_SETS, ids=lambda v: "dev" + "".join(map(str, v or [0])))
 @pytest.mark.parametrize("seed", range(8))
-def test_randomised_mutation_sequences(built_lib, seed, monkeypatch):
+def test_randomised_mutation_sequences(built_lib, seed, devices, monkeypatch):
     """add / remove_ids / reset / search in random order against a numpy model of faiss's semantics
     (positions are ids; remove_ids compacts and shifts later ids down)."""
     from generativeaiexamples_b200 import B200IndexFlat
@@ -866,7 +919,9 @@ def test_randomised_mutation_sequences(built_lib, seed, monkeypatch):
     shadow = bool(seed % 3 == 0)
     if seed % 4 < 2:
         monkeypatch.setenv("B200R_GEMM_MIN_BYTES", "1")
-    ix = B200IndexFlat(d, 1 if metric == "l2" else 0, shadow_bf16=shadow)
+        _lib.reload_env()
+    monkeypatch.setenv("B200R_MULTI_MIN_PIECE", "64")  # several segments per shard even at these sizes
+    ix = B200IndexFlat(d, 1 if metric == "l2" else 0, shadow_bf16=shadow, devices=devices)
     model = np.zeros((0, d), dtype=np.float32)
     for step in range(14):
         op = rng.choice(["add", "add", "remove", "search", "search", "reset"], p=[0.3, 0.2, 0.2, 0.15, 0.1, 0.05])

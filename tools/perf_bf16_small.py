@@ -3,6 +3,7 @@ import os, sys, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from generativeaiexamples_b200 import B200IndexFlat, synth
+from generativeaiexamples_b200 import _lib as _b200r_lib
 dev = torch.device("cuda", 0)
 d = 1024
 def timed(fn, reps=20, warm=3):
@@ -21,9 +22,9 @@ for n in (50_000, 100_000, 250_000, 500_000, 4_000_000):
         q = torch.randn(nq, d, device=dev); q /= q.norm(dim=1, keepdim=True)
         rec = {"n": n, "nq": nq}
         for name, m in (("scan", 99), ("gemm", 1)):
-            os.environ["B200R_GEMM_MIN_NQ"] = str(m)
+            os.environ["B200R_GEMM_MIN_NQ"] = str(m); _b200r_lib.reload_env()
             rec[name] = round(timed(lambda: ix.search(q, 10)), 3)
-        os.environ.pop("B200R_GEMM_MIN_NQ")
+        os.environ.pop("B200R_GEMM_MIN_NQ"); _b200r_lib.reload_env()
         rec["auto"] = round(timed(lambda: ix.search(q, 10)), 3)
         print(json.dumps(rec), flush=True)
     ix.close(); del ix; torch.cuda.empty_cache()

@@ -3,6 +3,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, os, sys
 from generativeaiexamples_b200 import B200IndexFlat, synth
+from generativeaiexamples_b200 import _lib as _b200r_lib
 dev = torch.device("cuda",0)
 n, d = 4_000_000, 1024
 def build(storage):
@@ -24,11 +25,11 @@ def perf(ix, nq, k, storage, tag):
 for storage in ("f32","bf16"):
     ix = build(storage)
     for dbg in ("0","1","2"):
-        os.environ["B200R_GEMM_DEBUG_NOSELECT"]=dbg
+        os.environ["B200R_GEMM_DEBUG_NOSELECT"]=dbg; _b200r_lib.reload_env()
         for nq,k in ((32,10),(128,10),(256,10)):
             perf(ix, nq, k, storage, f"noselect={dbg}")
     ix.close()
-os.environ["B200R_GEMM_DEBUG_NOSELECT"]="0"
+os.environ["B200R_GEMM_DEBUG_NOSELECT"]="0"; _b200r_lib.reload_env()
 for storage in ("f32","bf16"):
     ix = build(storage)
     for nq,k in ((64,100),(256,100),(1024,100),(1024,10)):

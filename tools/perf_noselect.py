@@ -6,6 +6,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 os.environ["B200R_GEMM_NOBOOST"] = "1"
 import torch
 from generativeaiexamples_b200 import B200IndexFlat, synth
+from generativeaiexamples_b200 import _lib as _b200r_lib
 dev = torch.device("cuda", 0)
 d, n, chunk = 1024, 4_000_000, 500_000
 def timed(fn, reps=8, warm=3):
@@ -21,8 +22,8 @@ for storage in ("bf16", "f32"):
     for c in range(n // chunk): ix.add(synth.corpus_chunk_device(c, chunk, d, dev))
     q = torch.randn(256, d, device=dev); q /= q.norm(dim=1, keepdim=True)
     for mode in ("0", "1", "2", "0"):
-        os.environ["B200R_GEMM_DEBUG_NOSELECT"] = mode
+        os.environ["B200R_GEMM_DEBUG_NOSELECT"] = mode; _b200r_lib.reload_env()
         ms = timed(lambda: ix.search(q, 10))
         print(json.dumps({"storage": storage, "noselect": mode, "ms": round(ms, 3), "tflops": round(2 * n * d * 256 / ms / 1e9, 1)}), flush=True)
-    os.environ["B200R_GEMM_DEBUG_NOSELECT"] = "0"
+    os.environ["B200R_GEMM_DEBUG_NOSELECT"] = "0"; _b200r_lib.reload_env()
     ix.close(); del ix; torch.cuda.empty_cache()

@@ -4,6 +4,7 @@ import os, sys, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from generativeaiexamples_b200 import B200IndexFlat, synth
+from generativeaiexamples_b200 import _lib as _b200r_lib
 
 dev = torch.device("cuda", 0)
 d = 1024
@@ -34,6 +35,6 @@ for nq in (1, 2, 3, 4, 5, 8):
     for name, shadow, min_nq in (("scan_f32", False, 99), ("gemm_tf32", False, 1), ("scan_shadow", True, 99),
                                  ("gemm_shadow", True, 1)):
         ix.set_shadow_filter(shadow)
-        os.environ["B200R_GEMM_MIN_NQ"] = str(min_nq)
+        os.environ["B200R_GEMM_MIN_NQ"] = str(min_nq); _b200r_lib.reload_env()
         rec[name] = round(timed(lambda: ix.search(q, 10)), 3)
     print(json.dumps(rec), flush=True)

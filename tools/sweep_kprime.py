@@ -4,11 +4,12 @@ import os, sys, json
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from generativeaiexamples_b200 import B200IndexFlat, synth
+from generativeaiexamples_b200 import _lib as _b200r_lib
 
 dev = torch.device("cuda", 0)
 d, n, chunk = 1024, 4_000_000, 500_000
 mode = sys.argv[1]  # bf16 | shadow | f32
-os.environ["B200R_GEMM_NOBOOST"] = "1"
+os.environ["B200R_GEMM_NOBOOST"] = "1"; _b200r_lib.reload_env()
 
 
 def timed(fn, reps=6, warm=2):
@@ -34,11 +35,11 @@ q /= q.norm(dim=1, keepdim=True)
 for k, kps in ((10, (0, 32, 48, 64, 96, 128, 192)), (100, (224, 280, 324, 400, 488, 600))):
     for kp in kps:
         if kp == 0:
-            os.environ["B200R_GEMM_KPCAP"] = "32"
-            os.environ.pop("B200R_GEMM_KPRIME", None)
+            os.environ["B200R_GEMM_KPCAP"] = "32"; _b200r_lib.reload_env()
+            os.environ.pop("B200R_GEMM_KPRIME", None); _b200r_lib.reload_env()
         else:
-            os.environ["B200R_GEMM_KPCAP"] = "256"
-            os.environ["B200R_GEMM_KPRIME"] = str(kp)
+            os.environ["B200R_GEMM_KPCAP"] = "256"; _b200r_lib.reload_env()
+            os.environ["B200R_GEMM_KPRIME"] = str(kp); _b200r_lib.reload_env()
         f0 = ix.stats()["n_gemm_fallbacks"]
         ms = timed(lambda: ix.search(q, k))
         fb = (ix.stats()["n_gemm_fallbacks"] - f0) / 8

@@ -3,6 +3,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from generativeaiexamples_b200 import B200IndexFlat
+from generativeaiexamples_b200 import _lib as _b200r_lib
 dev = torch.device("cuda", 0)
 d = 1024
 def run(ix, n, k, tag):
@@ -22,8 +23,8 @@ for n in (1_250_000, 10_000_000):
     ix = B200IndexFlat(d, 0, reserve_rows=n)
     for lo in range(0, n, 1_000_000): ix.add(torch.randn(min(1_000_000, n - lo), d, device=dev))
     for kb, st in ((32, 6), (16, 12), (64, 3), (32, 4), (24, 8), (48, 4), (8, 16)):
-        os.environ["B200R_SCAN_STAGE_KB"] = str(kb); os.environ["B200R_SCAN_STAGES"] = str(st)
+        os.environ["B200R_SCAN_STAGE_KB"] = str(kb); _b200r_lib.reload_env(); os.environ["B200R_SCAN_STAGES"] = str(st); _b200r_lib.reload_env()
         for ev in ("1", "0"):
-            os.environ["B200R_EVICT_FIRST"] = ev
+            os.environ["B200R_EVICT_FIRST"] = ev; _b200r_lib.reload_env()
             run(ix, n, 10, f"stage={kb}KB x{st} evict_first={ev}")
     ix.close()
