@@ -208,7 +208,7 @@ static int upload_segments(MultiIndex* m) {
         gpos += s.len;
     }
     DeviceGuard dg(m->primary);
-    if (n > m->seg_tab_cap) {
+    if (n > m->seg_tab_cap || !m->seg_tab_dev) {
         cudaFree(m->seg_tab_dev);
         m->seg_tab_dev = nullptr;
         m->seg_tab_cap = 0;
@@ -297,6 +297,12 @@ void multi_free(b200r_index* ix) {
 
 static int enable_peer(int from, int to) {
     if (from == to) return B200R_OK;
+    // remembered per process: asking the driver again costs far more than a search step
+    static std::mutex mu;
+    static bool enabled[64][64] = {};
+    if (from < 0 || to < 0 || from >= 64 || to >= 64) return fail(B200R_E_INVALID, "device ordinal out of range");
+    std::lock_guard<std::mutex> lk(mu);
+    if (enabled[from][to]) return B200R_OK;
     int can = 0;
     CU(cudaDeviceCanAccessPeer(&can, from, to));
     if (!can) return fail(B200R_E_UNSUPPORTED, "GPU %d cannot address GPU %d's memory (no peer access)", from, to);
@@ -304,9 +310,10 @@ static int enable_peer(int from, int to) {
     cudaError_t e = cudaDeviceEnablePeerAccess(to, 0);
     if (e == cudaErrorPeerAccessAlreadyEnabled) {
         cudaGetLastError();
-        return B200R_OK;
+        e = cudaSuccess;
     }
     CU(e);
+    enabled[from][to] = true;
     return B200R_OK;
 }
 

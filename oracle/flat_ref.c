@@ -67,6 +67,17 @@ int oracle_max_threads(void) {
 #endif
 }
 
+/* Size of the OpenMP team used from now on.  A launcher may export
+ * OMP_NUM_THREADS=1 (torch.distributed.run does), which would silently turn
+ * the "all cores" baseline into one core; bench.py states the team instead. */
+void oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n >= 1) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* ------------------------------------------------------------------ */
 /* elementary distances: faiss fvec_inner_product / fvec_L2sqr /       */
 /* fvec_norm_L2sqr.  8 partial sums, as the 8-lane SIMD versions keep. */

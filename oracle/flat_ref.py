@@ -68,6 +68,8 @@ def load_flat_ref(rebuild: bool = False):
     lib.oracle_set_sgemm.argtypes = [ctypes.c_void_p]
     lib.oracle_has_blas.restype = ctypes.c_int
     lib.oracle_max_threads.restype = ctypes.c_int
+    lib.oracle_set_threads.argtypes = [ctypes.c_int]
+    lib.oracle_set_threads.restype = None
     for name in ("oracle_fvec_inner_product", "oracle_fvec_L2sqr"):
         f = getattr(lib, name)
         f.argtypes = [_f32p, _f32p, ctypes.c_int64]
