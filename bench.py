@@ -526,25 +526,34 @@ def main_gpu(args):
 
     check_batch1(index.search, "batch-1, device buffers", host=False)
     check_batch1(index.search, "batch-1, host buffers (e2e)", host=True)
-    fused_alt = None
-    if world > 1 and os.environ.get("B200R_FUSED_EXCHANGE", "0") != "1":
-        # the opt-in fused NVLink exchange over the same shards: checked, and timed as a secondary line
-        os.environ["B200R_FUSED_EXCHANGE"] = "1"
-        fused_alt = ShardedFlatIndex(DIM, METRIC_INNER_PRODUCT, device=local_rank, local_index=index.local)
-        fused_alt._sync_counts()
-        if fused_alt._exchange() is None:
-            fused_alt = None
-        os.environ["B200R_FUSED_EXCHANGE"] = "0"
-        if fused_alt is not None:
-            check_batch1(fused_alt.search, "batch-1, fused NVLink exchange", host=False)
+    # the other exchange over the same shards (NCCL allgather + K4 when the fused NVLink exchange is the
+    # one in use, and the other way round): checked too, and timed as a secondary line
+    alt, alt_name, main_name = None, None, None
+    if world > 1:
+        main_fused = index._exchange() is not None
+        main_name = "fused NVLink exchange" if main_fused else "NCCL allgather + K4"
+        keep = os.environ.get("B200R_FUSED_EXCHANGE")
+        os.environ["B200R_FUSED_EXCHANGE"] = "0" if main_fused else "1"
+        alt = ShardedFlatIndex(DIM, METRIC_INNER_PRODUCT, device=local_rank, local_index=index.local)
+        alt._sync_counts()
+        alt_name = "NCCL allgather + K4" if main_fused else "fused NVLink exchange"
+        if not main_fused and alt._exchange() is None:
+            alt = None
+        if keep is None:
+            os.environ.pop("B200R_FUSED_EXCHANGE")
+        else:
+            os.environ["B200R_FUSED_EXCHANGE"] = keep
+        if alt is not None:
+            check_batch1(alt.search, "batch-1, " + alt_name + ", device buffers", host=False)
+            check_batch1(alt.search, "batch-1, " + alt_name + ", host buffers", host=True)
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
     launches0 = local.stats()["n_kernel_launches"]
     ms_dev, _ = timed(dev_step, args.steps, args.warmup)
     launches = local.stats()["n_kernel_launches"] - launches0
     launches = launches * args.steps // (args.steps + args.warmup)
-    if world > 1:
-        launches += args.steps  # K4 merge, one per step
+    if world > 1 and not getattr(index, "_xchg", None):
+        launches += args.steps  # K4 merge, one per step (the fused route's select kernel is counted by the library)
     clocks = sampler.stop() if sampler else None
     _, ms_e2e_wall = timed(e2e_step, args.steps, args.warmup)
     # per-call latency distribution of the host-buffer path (wall clock around each call)
@@ -555,15 +564,17 @@ def main_gpu(args):
         lat.append((time.perf_counter() - t0) * 1e6)
     lat.sort()
     e2e_lat = {"p50_us": lat[len(lat) // 2], "p99_us": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "calls": len(lat)}
-    fused_line = None
-    if fused_alt is not None:
-        def fused_step(i):
-            results["last_f"] = fused_alt.search(Q[i % POOL: i % POOL + 1], TOPK)
-
-        ms_f, _ = timed(fused_step, args.steps, args.warmup)
-        fused_line = {"value": args.steps * 1000.0 / ms_f, "unit": "queries/s", "ms_per_step": ms_f / args.steps,
-                      "note": "B200R_FUSED_EXCHANGE=1: scan kernels store their top-k into every rank over NVLink, "
-                              "the select kernel waits on flags; no NCCL call on the path"}
+    alt_line = None
+    if alt is not None:
+        ms_f, _ = timed(lambda i: results.__setitem__("last_f", alt.search(Q[i % POOL: i % POOL + 1], TOPK)),
+                        args.steps, args.warmup)
+        _, ms_fw = timed(lambda i: results.__setitem__("last_f", alt.search(Qh[i % POOL: i % POOL + 1], TOPK)),
+                         args.steps, args.warmup)
+        alt_line = {"exchange": alt_name, "value": args.steps * 1000.0 / ms_f, "unit": "queries/s",
+                    "ms_per_step": ms_f / args.steps, "e2e": {"value": args.steps * 1000.0 / ms_fw, "unit": "queries/s"},
+                    "note": "the same shards through the other exchange (B200R_FUSED_EXCHANGE=0 selects NCCL): fused = the "
+                            "scan kernels store their top-k into every rank over NVLink and the select kernel waits on "
+                            "flags; NCCL = one all_gather_into_tensor of 120 B per rank + the K4 select kernel"}
 
     # ---- scan kernel alone: CUDA events on the launching stream, live -----------------------
     local.set_timing(True)
@@ -713,10 +724,11 @@ def main_gpu(args):
                   "primary GPU's gather buffer over NVLink, translating select kernel"
             api = "B200IndexFlat(devices=[...]).search(numpy) = b200r_search(HOST query, HOST results) on the multi-GPU index"
         elif world > 1:
-            par = f"row-shard x{world} + " + ("fused NVLink peer-store exchange" if getattr(index, "_xchg", None)
-                                              else "NCCL allgather") + " + K4 select"
-            api = "ShardedFlatIndex.search(numpy): pinned H2D -> b200r_search(DEVICE) -> NCCL allgather -> " \
-                  "b200r_merge_topk -> one packed D2H"
+            par = f"row-shard x{world} + {main_name}"
+            api = ("ShardedFlatIndex.search(numpy) = b200r_search_exchange(HOST query, HOST results): pinned H2D -> scan "
+                   "-> NVLink stores into every rank -> waiting select -> one packed D2H") if getattr(index, "_xchg", None) \
+                else ("ShardedFlatIndex.search(numpy): pinned H2D -> b200r_search(DEVICE) -> NCCL allgather -> "
+                      "b200r_merge_topk -> one packed D2H")
         else:
             par, api = "single GPU", "B200IndexFlat.search(numpy) = b200r_search(HOST query, HOST results)"
         line = {
@@ -748,7 +760,7 @@ def main_gpu(args):
             "cpu_baseline": cb,
             "batch256": b256,
             "batch1_shadow_bf16": b1s,
-            "fused_exchange": fused_line,
+            "alt_exchange": alt_line,
             "concurrent_callers": conc,
             "clocks": clocks,
         }

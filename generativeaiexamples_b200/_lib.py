@@ -63,10 +63,11 @@ SIGNATURES = {
     "b200r_merge_topk": (_int, [_i32, _vp, _vp, _i64, _i32, _i32, _i64, _i64, _i32, _vp, _vp, _i32, _vp]),
     "b200r_search_noalloc": (_int, [_vp, _i64, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _i64, _i32, _vp]),
     "b200r_exchange_buffer_bytes": (_i64, []),
-    "b200r_search_exchange": (_int, [_vp, _vp, _i64, _int, ctypes.POINTER(_vp), _i32, _i32, ctypes.c_uint32, _vp, _vp,
-                                     _vp]),
+    "b200r_search_exchange": (_int, [_vp, _vp, _i64, _int, _int, ctypes.POINTER(_vp), _i32, _i32, ctypes.c_uint32, _vp,
+                                     _vp, _int, _vp]),
     "b200r_exchange_status": (_int, [_vp, _i32, _vp, ctypes.POINTER(_i32)]),
     "b200r_reload_env": (_int, []),
+    "b200r_auto_route": (_int, [_vp, _i64, _i64, ctypes.POINTER(_i32)]),
     "b200r_set_id_base": (_int, [_vp, _i64]),
     "b200r_stats_get": (_int, [_vp, ctypes.POINTER(Stats)]),
     "b200r_merge_from": (_int, [_vp, _vp]),

@@ -95,16 +95,27 @@ extern "C" int b200r_search(b200r_index* ix, const void* q, int64_t nq, int k, i
     return leaf_search(ix, q, nq, k, q_mem_kind, D, I, out_mem_kind, stream, B200R_PATH_AUTO, nullptr);
 }
 
+extern "C" int b200r_auto_route(b200r_index* ix, int64_t nq, int64_t n_rows, int32_t* route) {
+    if (!ix || !route) return fail(B200R_E_INVALID, "b200r_auto_route: null argument");
+    if (ix->multi) return fail(B200R_E_UNSUPPORTED, "b200r_auto_route: ask a single-GPU index");
+    *route = leaf_route(ix, nq, n_rows);
+    return B200R_OK;
+}
+
 // ---------------------------------------------------------------------------
 // fused search + NVLink exchange between processes (one rank per GPU, small batches)
 // ---------------------------------------------------------------------------
 extern "C" int64_t b200r_exchange_buffer_bytes(void) { return kXchgBytes; }
 
-extern "C" int b200r_search_exchange(b200r_index* ix, const float* q, int64_t nq, int k, void* const* peer_bufs,
-                                     int32_t world, int32_t rank, uint32_t epoch, float* D, int64_t* I, void* stream) {
+extern "C" int b200r_search_exchange(b200r_index* ix, const float* q, int64_t nq, int k, int q_mem_kind,
+                                     void* const* peer_bufs, int32_t world, int32_t rank, uint32_t epoch, float* D,
+                                     int64_t* I, int out_mem_kind, void* stream) {
     if (!ix) return fail(B200R_E_INVALID, "b200r_search_exchange: null index");
     if (ix->multi) return fail(B200R_E_UNSUPPORTED, "b200r_search_exchange: the index already spans several GPUs");
     if (!q || !D || !I || !peer_bufs) return fail(B200R_E_INVALID, "b200r_search_exchange: null buffer");
+    if ((q_mem_kind != B200R_HOST && q_mem_kind != B200R_DEVICE) ||
+        (out_mem_kind != B200R_HOST && out_mem_kind != B200R_DEVICE))
+        return fail(B200R_E_INVALID, "b200r_search_exchange: bad mem_kind");
     if (nq < 1 || nq > kScanMaxNQ)
         return fail(B200R_E_UNSUPPORTED, "b200r_search_exchange: nq %lld outside 1..%d", (long long)nq, kScanMaxNQ);
     if (k < 1 || k > kScanMaxK) return fail(B200R_E_UNSUPPORTED, "b200r_search_exchange: k %d outside 1..%d", k, kScanMaxK);
@@ -119,16 +130,42 @@ extern "C" int b200r_search_exchange(b200r_index* ix, const float* q, int64_t nq
         if (!peer_bufs[r]) return fail(B200R_E_INVALID, "b200r_search_exchange: null peer buffer %d", r);
         x.target[r] = reinterpret_cast<uint8_t*>(peer_bufs[r]);
     }
-    int rc = leaf_search(ix, q, nq, k, B200R_DEVICE, D, I, B200R_DEVICE, stream, B200R_PATH_SCAN, &x);
+    // as in b200r_search: with host buffers only, NULL selects the index's own stream
+    const bool any_dev = q_mem_kind == B200R_DEVICE || out_mem_kind == B200R_DEVICE;
+    cudaStream_t st = (any_dev || stream) ? (cudaStream_t)stream : ix->stream;
+    int rc = leaf_search(ix, q, nq, k, q_mem_kind, nullptr, nullptr, B200R_DEVICE, st, B200R_PATH_SCAN, &x);
     if (rc != B200R_OK) return rc;
     DeviceGuard g(ix->device);
-    CU(launch_merge_wait(ix->l2, reinterpret_cast<uint8_t*>(peer_bufs[rank]), world, (int)nq, k, epoch, D, I,
-                         (cudaStream_t)stream));
     std::lock_guard<std::mutex> lk(ix->mu);
-    CU(cudaEventRecord(ix->ws_ev, (cudaStream_t)stream));
-    ix->ws_ev_set = true;
-    ix->ws_ev_stream = (cudaStream_t)stream;
+    // host results: the select kernel writes [scores | ids | status] into the index's staging buffer,
+    // ONE copy brings all of it back
+    const size_t ids_off = ((size_t)nq * k * sizeof(float) + 15) / 16 * 16;
+    const size_t status_off = (ids_off + (size_t)nq * k * sizeof(int64_t) + 15) / 16 * 16;
+    const bool host_out = out_mem_kind == B200R_HOST;
+    float* od = host_out ? reinterpret_cast<float*>(ix->out_buf) : D;
+    int64_t* oi = host_out ? reinterpret_cast<int64_t*>(ix->out_buf + ids_off) : I;
+    int* status_dev = host_out ? reinterpret_cast<int*>(ix->out_buf + status_off) : nullptr;
+    CU(launch_merge_wait(ix->l2, reinterpret_cast<uint8_t*>(peer_bufs[rank]), world, (int)nq, k, epoch, od, oi, status_dev,
+                         st));
     ix->st.n_kernel_launches++;
+    if (host_out) {
+        CU(cudaMemcpyAsync(ix->out_pin, ix->out_buf, status_off + sizeof(int), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        ix->ws_ev_set = false;
+        const int status = *reinterpret_cast<const int*>(ix->out_pin + status_off);
+        if (status != 0) {
+            CU(cudaMemsetAsync(reinterpret_cast<uint8_t*>(peer_bufs[rank]) + kXchgStatusOffset, 0, sizeof(int), st));
+            CU(cudaStreamSynchronize(st));
+            return fail(B200R_E_CUDA, "b200r_search_exchange: rank %d did not deliver its candidates within 2 s", status - 1);
+        }
+        memcpy(D, ix->out_pin, (size_t)nq * k * sizeof(float));
+        memcpy(I, ix->out_pin + ids_off, (size_t)nq * k * sizeof(int64_t));
+        return B200R_OK;
+    }
+    if (q_mem_kind == B200R_HOST) CU(cudaStreamSynchronize(st));  // the pinned query buffer is free again
+    CU(cudaEventRecord(ix->ws_ev, st));
+    ix->ws_ev_set = true;
+    ix->ws_ev_stream = st;
     return B200R_OK;
 }
 

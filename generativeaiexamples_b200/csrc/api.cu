@@ -55,6 +55,7 @@ static void read_knobs_locked() {
     k.scan_stage_kb = (int)geti("B200R_SCAN_STAGE_KB", 0);
     k.scan_stages = (int)geti("B200R_SCAN_STAGES", 0);
     k.scan_dynamic = (int)geti("B200R_SCAN_DYNAMIC", -1);
+    k.scan_trace = (int)geti("B200R_SCAN_TRACE", 0);
     k.gemm_kpcap = (int)geti("B200R_GEMM_KPCAP", 0);
     k.gemm_kprime = (int)geti("B200R_GEMM_KPRIME", 0);
     k.gemm_cluster = (int)geti("B200R_GEMM_CLUSTER", 0);
@@ -199,6 +200,7 @@ void leaf_free(b200r_index* ix) {
     cudaFreeHost(ix->recon_pin);
     cudaFree(ix->bounce);
     cudaFree(ix->adj_dev);
+    cudaFree(ix->trace_dev);
     for (auto& e : ix->fb_ev)
         if (e) cudaEventDestroy(e);
     for (auto& e : ix->add_ev)
@@ -491,9 +493,10 @@ static void fold_fallback_counts(b200r_index* ix, bool wait) {
 // takes over at nq = 2 -- and at nq = 1 when it can filter on the bf16 shadow (3.0 ms).
 // Small corpora keep the scan up to nq = 4.  Both paths end in the same fp32 scoring code, so
 // the choice never changes a result.
-static bool auto_uses_gemm(const b200r_index* ix, int64_t nq) {
+static bool auto_uses_gemm(const b200r_index* ix, int64_t nq, int64_t rows = -1) {
     const Knobs& kn = knobs();
-    const int64_t corpus_bytes = (int64_t)ix->ntotal * ix->row_bytes;
+    if (rows < 0) rows = ix->ntotal;
+    const int64_t corpus_bytes = rows * ix->row_bytes;
     const bool eb = kn.gemm_min_bytes >= 0;
     int64_t gemm_min = 5;
     if (corpus_bytes >= (eb ? kn.gemm_min_bytes : kGemmSmallBatchBytes)) gemm_min = 2;
@@ -505,13 +508,13 @@ static bool auto_uses_gemm(const b200r_index* ix, int64_t nq) {
         if (corpus_bytes >= (eb ? kn.gemm_min_bytes : kGemmBf16SingleBytes)) gemm_min = 1;
     }
     if (kn.gemm_min_nq >= 0) gemm_min = kn.gemm_min_nq;
-    return ix->ntotal > 0 && (ix->cfg.search_path == B200R_PATH_GEMM ||
-                              (ix->cfg.search_path == B200R_PATH_AUTO && nq >= gemm_min));
+    return rows > 0 && (ix->cfg.search_path == B200R_PATH_GEMM ||
+                        (ix->cfg.search_path == B200R_PATH_AUTO && nq >= gemm_min));
 }
 
-int leaf_route(b200r_index* ix, int64_t nq) {
+int leaf_route(b200r_index* ix, int64_t nq, int64_t rows) {
     std::lock_guard<std::mutex> lk(ix->mu);
-    return auto_uses_gemm(ix, nq) ? B200R_PATH_GEMM : B200R_PATH_SCAN;
+    return auto_uses_gemm(ix, nq, rows) ? B200R_PATH_GEMM : B200R_PATH_SCAN;
 }
 
 int leaf_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
@@ -631,7 +634,16 @@ int leaf_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kin
     if (kn.evict_first >= 0) p.evict_first = kn.evict_first;  // tuning knob
     p.scratch = ix->scratch;
     p.counter = ix->counter;
+    // B200R_SCAN_DYNAMIC=1: tiles are drawn from a global counter (second word group of the ticket buffer)
+    // instead of the static walk.  Measured (tools/perf_scan_tail.py): it levels the CTAs' finishing times
+    // (20 us spread -> 2 us on a 1.25M-row shard) but the stream as a whole gets 1-2 % slower, so it is off.
+    p.tile_counter = kn.scan_dynamic == 1 ? ix->counter + 16 : nullptr;
     p.id_base = ix->cfg.id_base;
+    if (kn.scan_trace) {
+        if (!ix->trace_dev) CU(cudaMalloc(&ix->trace_dev, 256 * 8 * sizeof(unsigned long long)));
+        CU(cudaMemsetAsync(ix->trace_dev, 0, 256 * 8 * sizeof(unsigned long long), st));
+        p.trace = ix->trace_dev;
+    }
     if (xchg) {
         p.xchg_ntargets = xchg->n_targets;
         p.xchg_rank = xchg->slot;
@@ -654,6 +666,25 @@ int leaf_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kin
             ix->st.n_kernel_launches++;
             ix->st.last_grid = grid;
             ix->st.bytes_scanned += (int64_t)ix->ntotal * ix->row_bytes;
+            if (kn.scan_trace) {  // diagnosis: where the time of this launch went (synchronises)
+                std::vector<unsigned long long> tr((size_t)grid * 8);
+                CU(cudaStreamSynchronize(st));
+                CU(cudaMemcpy(tr.data(), ix->trace_dev, tr.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+                unsigned long long t0 = ~0ull, t1max = 0, t2min = ~0ull, t2max = 0, t3max = 0, t4 = 0;
+                for (int c = 0; c < grid; c++) {
+                    t0 = std::min(t0, tr[c * 8]);
+                    t1max = std::max(t1max, tr[c * 8 + 1]);
+                    t2min = std::min(t2min, tr[c * 8 + 2]);
+                    t2max = std::max(t2max, tr[c * 8 + 2]);
+                    t3max = std::max(t3max, tr[c * 8 + 3]);
+                    t4 = std::max(t4, tr[c * 8 + 4]);
+                }
+                fprintf(stderr,
+                        "[b200r scan trace] grid %d rows %lld: queries staged +%.1f us, first CTA out of rows +%.1f, last "
+                        "+%.1f, last CTA list stored +%.1f, result written +%.1f\n",
+                        grid, (long long)ix->ntotal, (t1max - t0) / 1e3, (t2min - t0) / 1e3, (t2max - t0) / 1e3,
+                        (t3max - t0) / 1e3, (t4 - t0) / 1e3);
+            }
         }
     } else {
         // Queries whose containment check failed are re-run on the scan kernel WITHOUT a trip to the
@@ -716,7 +747,8 @@ int leaf_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kin
     }
     if (out_mem_kind == B200R_DEVICE) {  // still in flight on the caller's stream
         // (host queries were staged through the index's pinned buffer: it must be free before the next call)
-        if (q_mem_kind == B200R_HOST) CU(cudaStreamSynchronize(st));
+        // (with an exchange the caller synchronises after its own select kernel)
+        if (q_mem_kind == B200R_HOST && !xchg) CU(cudaStreamSynchronize(st));
         CU(cudaEventRecord(ix->ws_ev, st));
         ix->ws_ev_set = true;
         ix->ws_ev_stream = st;

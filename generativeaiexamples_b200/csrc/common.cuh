@@ -329,6 +329,40 @@ struct WarpTopK {
                 }
             }
         };
+        if (GLOBAL && KPL == 1) {
+            // short lists written by other CTAs: fetch a batch of them at once, so that one trip to L2
+            // covers nine lists (148 CTA lists over 17 warps) instead of one
+            constexpr int B = 9;
+            for (int l0 = first; l0 < nlists; l0 += step * B) {
+                float gv[B];
+                uint32_t gi[B];
+#pragma unroll
+                for (int b = 0; b < B; b++) {
+                    const int l = l0 + b * step;
+                    gv[b] = worst_val<SMALL>();
+                    gi[b] = kEmptyId;
+                    if (l < nlists) {
+                        const unsigned long long raw =
+                            __ldcg(reinterpret_cast<const unsigned long long*>(lists + (size_t)l * stride + lane));
+                        gv[b] = __uint_as_float((uint32_t)(raw & 0xffffffffull));
+                        gi[b] = (uint32_t)(raw >> 32);
+                    }
+                }
+#pragma unroll
+                for (int b = 0; b < B; b++) {
+                    const float head_v = __shfl_sync(0xffffffffu, gv[b], 0);
+                    const uint32_t head_i = __shfl_sync(0xffffffffu, gi[b], 0);
+                    if (head_i != kEmptyId && better<SMALL>(head_v, head_i, thr, thr_id)) {
+                        float cv[KPL];
+                        uint32_t ci[KPL];
+                        cv[0] = gv[b];
+                        ci[0] = gi[b];
+                        merge_sorted(cv, ci);
+                    }
+                }
+            }
+            return;
+        }
         if (first < nlists) fetch(first);
         for (int l = first; l < nlists; l += step) {
             float cv[KPL];

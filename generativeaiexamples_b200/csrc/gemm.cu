@@ -1247,6 +1247,18 @@ int gemm_kprime(int k, int filter, int boost_pct) {
     return kp < cap ? kp : cap;
 }
 
+// the opt-in to > 48 KB of dynamic shared memory is per kernel and per device: asked for once
+static cudaError_t ensure_smem_optin_gemm(const void* kern, size_t smem, size_t (&granted)[64]) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (smem <= granted[dev]) return cudaSuccess;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) granted[dev] = smem;
+    return e;
+}
+
 template <bool BF16, int MT, int KP, bool L2, int CS, bool PAIR = false>
 static cudaError_t launch_filter_one(const CUtensorMap& mq, const CUtensorMap& mx, const GemmParams& p, int grid,
                                      cudaStream_t st) {
@@ -1254,7 +1266,8 @@ static cudaError_t launch_filter_one(const CUtensorMap& mq, const CUtensorMap& m
     constexpr int STAGE_BYTES = (PAIR ? kGemmBBytes / 2 : kGemmBBytes) + MT * kGemmABytes;
     const size_t smem = 1024 + (size_t)STAGES * STAGE_BYTES + 256 + (L2 ? (size_t)4 * MT * kGemmTileN * sizeof(float) : 0);
     auto kern = gemm_filter_kernel<BF16, MT, KP, L2, CS, PAIR>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static size_t granted[64] = {};
+    cudaError_t e = ensure_smem_optin_gemm(reinterpret_cast<const void*>(kern), smem, granted);
     if (e != cudaSuccess) return e;
     if (CS == 1 && !PAIR) {
         kern<<<grid, 128 + 128 * MT, smem, st>>>(mq, mx, p);
@@ -1294,7 +1307,8 @@ static cudaError_t launch_filter_l2(bool l2, int cs, const CUtensorMap& mq, cons
 template <bool L2, bool BF16, int WARPS>
 static cudaError_t launch_rescore_one(const RescoreParams& rp, int nq, size_t smem, cudaStream_t st) {
     auto kern = rescore_kernel<L2, BF16, WARPS>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static size_t granted[64] = {};
+    cudaError_t e = ensure_smem_optin_gemm(reinterpret_cast<const void*>(kern), smem, granted);
     if (e != cudaSuccess) return e;
     kern<<<nq, WARPS * 32, smem, st>>>(rp);
     return cudaGetLastError();

@@ -50,6 +50,7 @@ struct Knobs {
     int scan_stage_kb = 0;          // B200R_SCAN_STAGE_KB    (0 = default)
     int scan_stages = 0;            // B200R_SCAN_STAGES      (0 = default)
     int scan_dynamic = -1;          // B200R_SCAN_DYNAMIC     (-1 = default)
+    int scan_trace = 0;             // B200R_SCAN_TRACE       1: per-CTA timestamps of every scan launch to stderr
     int gemm_kpcap = 0;             // B200R_GEMM_KPCAP       (0 = unset)
     int gemm_kprime = 0;            // B200R_GEMM_KPRIME      (0 = unset)
     int gemm_cluster = 0;           // B200R_GEMM_CLUSTER     (0 = unset)
@@ -153,6 +154,7 @@ struct b200r_index {
     size_t bounce_bytes = 0;
     int64_t* adj_dev = nullptr;    // remove_ids: adjusted deleted positions
     int64_t adj_cap = 0;
+    unsigned long long* trace_dev = nullptr;  // B200R_SCAN_TRACE
 
     std::mutex mu;
     b200r_stats st{};
@@ -180,7 +182,7 @@ int leaf_add(b200r_index* ix, const void* x, int64_t n, int dtype, int mem_kind,
 int leaf_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
                 int out_mem_kind, void* stream, int route, const ScanExchange* xchg);
 // the route AUTO would take for nq queries right now (B200R_PATH_SCAN or B200R_PATH_GEMM)
-int leaf_route(b200r_index* ix, int64_t nq);
+int leaf_route(b200r_index* ix, int64_t nq, int64_t rows = -1);  // rows < 0: the index's own row count
 int leaf_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, int64_t* n_removed);
 int leaf_reconstruct(b200r_index* ix, int64_t key, float* out);
 int leaf_reconstruct_batch(b200r_index* ix, const int64_t* keys, int64_t n, float* out);

@@ -38,6 +38,11 @@ struct ScanParams {
     // results go to row flag_list[i] of out_d / out_i; the launch is cooperative and loops over them
     const int* flag_list;
     const int* flag_count;
+    // diagnosis only (B200R_SCAN_TRACE=1): per-CTA timestamps [grid][8] (globaltimer ns), else null
+    unsigned long long* trace;
+    // dynamic tile assignment (tile_counter != null): CTAs draw tiles from a global counter instead of
+    // walking t = blockIdx.x, +grid, ...; zero on entry, reset by the final writer
+    unsigned* tile_counter;
 };
 
 // Exchange buffer of one rank (symmetric: same layout on every rank, peer-mapped over NVLink):
@@ -52,7 +57,7 @@ constexpr int kXchgStatusOffset = kXchgFlagOffset + 2 * kXchgMaxWorld * 128;
 constexpr int kXchgBytes = kXchgStatusOffset + 256;
 
 cudaError_t launch_merge_wait(bool l2, uint8_t* my_buf, int world, int nq, int k, uint32_t epoch, float* out_d,
-                              int64_t* out_i, cudaStream_t st);
+                              int64_t* out_i, int* status_out, cudaStream_t st);
 
 size_t scan_scratch_bytes(int max_grid);
 int scan_queries_per_launch(int d_pad, int row_bytes, size_t smem_limit);

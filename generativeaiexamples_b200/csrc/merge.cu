@@ -59,7 +59,8 @@ __global__ void __launch_bounds__(128) merge_topk_kernel(const float* __restrict
 // word is set and the output is padding, instead of a kernel that spins forever.
 template <int KPL, bool L2>
 __global__ void __launch_bounds__(128) merge_wait_kernel(uint8_t* buf, int world, int nq, int k, uint32_t epoch,
-                                                         float* __restrict__ out_d, int64_t* __restrict__ out_i) {
+                                                         float* __restrict__ out_d, int64_t* __restrict__ out_i,
+                                                         int* status_out) {
     __shared__ int s_ok;
     const uint32_t parity = epoch & 1u;
     if (threadIdx.x == 0) s_ok = 1;
@@ -78,6 +79,7 @@ __global__ void __launch_bounds__(128) merge_wait_kernel(uint8_t* buf, int world
         }
     }
     __syncthreads();
+    if (status_out && threadIdx.x == 0) *status_out = s_ok ? 0 : *reinterpret_cast<int*>(buf + kXchgStatusOffset);
     const int lane = threadIdx.x & 31;
     const int q = threadIdx.x >> 5;
     if (q >= nq) return;
@@ -279,15 +281,15 @@ cudaError_t launch_merge_shards(bool l2, const uint8_t* base, int64_t slot_strid
 }
 
 cudaError_t launch_merge_wait(bool l2, uint8_t* my_buf, int world, int nq, int k, uint32_t epoch, float* out_d,
-                              int64_t* out_i, cudaStream_t st) {
+                              int64_t* out_i, int* status_out, cudaStream_t st) {
     if (world < 1 || world > kXchgMaxWorld || nq < 1 || nq > kScanMaxNQ || k < 1 || k > kScanMaxK)
         return cudaErrorInvalidValue;
     if (k <= 32) {
-        if (l2) merge_wait_kernel<1, true><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i);
-        else merge_wait_kernel<1, false><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i);
+        if (l2) merge_wait_kernel<1, true><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i, status_out);
+        else merge_wait_kernel<1, false><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i, status_out);
     } else {
-        if (l2) merge_wait_kernel<4, true><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i);
-        else merge_wait_kernel<4, false><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i);
+        if (l2) merge_wait_kernel<4, true><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i, status_out);
+        else merge_wait_kernel<4, false><<<1, 128, 0, st>>>(my_buf, world, nq, k, epoch, out_d, out_i, status_out);
     }
     return cudaGetLastError();
 }

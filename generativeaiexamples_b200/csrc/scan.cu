@@ -28,6 +28,13 @@ namespace b200r {
 
 constexpr int kScanConsumerWarps = 16;
 constexpr int kScanThreads = 32 * (1 + kScanConsumerWarps);
+constexpr int kScanMaxStages = 16;
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 // FLAGGED: the cooperative re-run of the queries that failed the GEMM route's containment check.
 // The same body runs once per group of NQ flagged queries, with a grid-wide barrier between groups
@@ -48,6 +55,12 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(qs + (size_t)NQ * p.d);
     uint64_t* empty_bar = full_bar + nst;
     __shared__ int s_is_last;
+    // tile held by each stage (-1: the stream has ended).  With a global tile counter the CTAs draw
+    // tiles as they go, so the slowest SM no longer decides when the kernel ends; the producer tells
+    // the consumers which tile a stage holds through this array (written before the barrier arrive).
+    __shared__ long long s_tile[kScanMaxStages];
+    const bool dyn = !FLAGGED && p.tile_counter != nullptr;
+    if (p.trace && threadIdx.x == 0) p.trace[blockIdx.x * 8 + 0] = global_ns();
 
     int n_groups = 1, n_flagged = 0;
     if constexpr (FLAGGED) {
@@ -67,6 +80,59 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
     // position in the stage ring: the producer lane and every consumer warp advance it identically
     int s = 0;
     uint32_t ph = 0;
+    const int64_t n_tiles = p.n_tiles;
+    const int R = p.rows_per_tile;
+    // producer state (thread 0 only): the next tile of this CTA
+    int64_t t_next = blockIdx.x;
+    auto draw_tile = [&]() -> int64_t {
+        if (dyn) return (int64_t)atomicAdd(p.tile_counter, 1u);
+        const int64_t t = t_next;
+        t_next += gridDim.x;
+        return t;
+    };
+    auto issue_tile = [&](int64_t t, uint64_t pol) {
+        const uint8_t* g = reinterpret_cast<const uint8_t*>(p.corpus);
+        if (t >= n_tiles) {  // end of the stream: an empty stage that says so
+            s_tile[s] = -1;
+            mbar_arrive(&full_bar[s]);
+            return;
+        }
+        s_tile[s] = t;
+        const int64_t row0 = t * R;
+        const int64_t rem = p.n_rows - row0;
+        const uint32_t rows = (uint32_t)(rem < R ? rem : R);
+        const uint32_t bytes = rows * (uint32_t)p.row_bytes;
+        mbar_arrive_expect_tx(&full_bar[s], bytes);
+        if (p.evict_first)
+            bulk_g2s_hint(stage_base + (size_t)s * p.stage_bytes, g + row0 * (int64_t)p.row_bytes, bytes, &full_bar[s], pol);
+        else
+            bulk_g2s(stage_base + (size_t)s * p.stage_bytes, g + row0 * (int64_t)p.row_bytes, bytes, &full_bar[s]);
+    };
+    // The first stages are requested before the queries are staged: thread 0 initialised the barriers
+    // itself, so its bulk copies can leave while the other threads still fetch the query vectors.
+    int pro_s = 0;          // producer's own ring position (it runs ahead of the consumers' s / ph)
+    uint32_t pro_ph = 0;
+    int64_t t_pending = -2; // tile drawn ahead (-2: none)
+    int prologue = 0;
+    if (!FLAGGED && threadIdx.x == 0) {
+        const uint64_t pol = policy_evict_first();
+        for (; prologue < nst; prologue++) {
+            const int64_t t = draw_tile();
+            const int keep_s = s;
+            s = pro_s;
+            issue_tile(t, pol);
+            s = keep_s;
+            if (++pro_s == nst) {
+                pro_s = 0;
+                pro_ph ^= 1;
+            }
+            if (t >= n_tiles) {
+                prologue = -1;  // the stream ended inside the prologue
+                break;
+            }
+        }
+        if (prologue >= 0 && dyn) t_pending = draw_tile();
+    }
   for (int grp = 0; grp < n_groups; grp++) {
     const int nq_active = FLAGGED ? (n_flagged - grp * NQ < NQ ? n_flagged - grp * NQ : NQ) : p.nq_active;
     // queries -> shared memory (fp32, zero padded to NQ rows by the host)
@@ -86,9 +152,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
         for (int i = threadIdx.x; i < n4; i += blockDim.x) q4[i] = qg[i];
     }
     __syncthreads();
-
-    const int64_t n_tiles = p.n_tiles;
-    const int R = p.rows_per_tile;
+    if (p.trace && threadIdx.x == 0) p.trace[blockIdx.x * 8 + 1] = global_ns();
 
     WarpTopK<KPL, L2> top[NQ];
     // rows that beat the running threshold wait here (lane i holds the i-th of them) until 32 have
@@ -108,25 +172,33 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
         // ---- producer ---------------------------------------------------
         if (lane == 0) {
             const uint64_t pol = policy_evict_first();
-            const uint8_t* g = reinterpret_cast<const uint8_t*>(p.corpus);
-            for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-                mbar_wait(&empty_bar[s], ph ^ 1);
-                const int64_t row0 = t * R;
-                const int64_t rem = p.n_rows - row0;
-                const uint32_t rows = (uint32_t)(rem < R ? rem : R);
-                const uint32_t bytes = rows * (uint32_t)p.row_bytes;
-                mbar_arrive_expect_tx(&full_bar[s], bytes);
-                if (p.evict_first)
-                    bulk_g2s_hint(stage_base + (size_t)s * p.stage_bytes, g + row0 * (int64_t)p.row_bytes, bytes,
-                                  &full_bar[s], pol);
-                else
-                    bulk_g2s(stage_base + (size_t)s * p.stage_bytes, g + row0 * (int64_t)p.row_bytes, bytes,
-                             &full_bar[s]);
-                if (++s == nst) {
-                    s = 0;
-                    ph ^= 1;
-                }
+            if (FLAGGED) {  // every group starts a fresh walk over the tiles
+                t_next = blockIdx.x;
+                pro_s = s;
+                pro_ph = ph;
+                prologue = 0;
             }
+            bool ended = prologue < 0;
+            while (!ended) {
+                // the next tile is drawn before waiting for a free stage, so the counter's round trip
+                // to L2 is hidden behind that wait
+                const int64_t t = (t_pending != -2) ? t_pending : draw_tile();
+                t_pending = -2;
+                if (dyn && t < n_tiles) t_pending = draw_tile();
+                mbar_wait(&empty_bar[pro_s], pro_ph ^ 1);
+                const int keep_s = s;
+                s = pro_s;
+                issue_tile(t, pol);
+                s = keep_s;
+                if (++pro_s == nst) {
+                    pro_s = 0;
+                    pro_ph ^= 1;
+                }
+                ended = t >= n_tiles;
+            }
+            // leave the consumers' ring position where they will be: one past the end-of-stream stage
+            s = pro_s;
+            ph = pro_ph;
         }
         __syncwarp();
     } else {
@@ -134,11 +206,21 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
         const int cw = warp - 1;
         int64_t seq = 0;  // rows this CTA has streamed before the current tile
         const int nvec = BF16 ? (p.d >> 3) : (p.d >> 2);  // 16-byte vectors per row
-        for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (;;) {
+            mbar_wait(&full_bar[s], ph);
+            const int64_t t = s_tile[s];
+            if (t < 0) {  // end of the stream: release the marker stage and step past it
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty_bar[s]);
+                if (++s == nst) {
+                    s = 0;
+                    ph ^= 1;
+                }
+                break;
+            }
             const int64_t row0 = t * R;
             const int64_t rem = p.n_rows - row0;
             const int rows = (int)(rem < R ? rem : R);
-            mbar_wait(&full_bar[s], ph);
             const uint8_t* tile = stage_base + (size_t)s * p.stage_bytes;
             // round-robin row ownership across the CTA's row stream
             int r = (int)(((int64_t)cw - seq) % NCW);
@@ -237,6 +319,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
     }
 
     // ---- epilogue: per-CTA merge, then last-CTA grid merge ----------------
+    if (p.trace && threadIdx.x == 32) p.trace[blockIdx.x * 8 + 2] = global_ns();
     if (warp > 0) {
 #pragma unroll
         for (int qi = 0; qi < NQ; qi++) top[qi].offer_batch(pend_v[qi], pend_i[qi]);  // stragglers
@@ -257,6 +340,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
+        if (p.trace) p.trace[blockIdx.x * 8 + 3] = global_ns();
         const unsigned ticket = atomicAdd(p.counter, 1u);
         s_is_last = (ticket == gridDim.x - 1);
     }
@@ -316,7 +400,11 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
             asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(p.xchg_epoch) : "memory");
         }
     }
-    if (threadIdx.x == 0) *p.counter = 0;  // ready for the next group / the next launch on this stream
+    if (threadIdx.x == 0) {
+        *p.counter = 0;  // ready for the next group / the next launch on this stream
+        if (p.tile_counter) *p.tile_counter = 0;
+        if (p.trace) p.trace[blockIdx.x * 8 + 4] = global_ns();
+    }
     }  // s_is_last
     if constexpr (FLAGGED) {
         __threadfence();
@@ -327,19 +415,35 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
 }
 
 // ---------------------------------------------------------------------------
+// The opt-in to > 48 KB of dynamic shared memory is per kernel and per device: asked for once (for
+// the largest size seen so far), not on every launch.
+template <typename K>
+static cudaError_t ensure_smem_optin(K kern, size_t smem, size_t (&granted)[64]) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (smem <= granted[dev]) return cudaSuccess;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) granted[dev] = smem;
+    return e;
+}
+
 template <int NQ, int KPL, bool L2, bool BF16>
 static cudaError_t launch_one(const ScanParams& p, int grid, size_t smem, cudaStream_t st, bool flagged) {
     if (flagged) {
         // cooperative: the kernel loops over the flagged queries with grid-wide barriers in between
         auto kern = scan_topk_kernel<NQ, KPL, L2, BF16, true>;
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        static size_t granted[64] = {};
+        cudaError_t e = ensure_smem_optin(kern, smem, granted);
         if (e != cudaSuccess) return e;
         ScanParams pc = p;
         void* args[] = {&pc};
         return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(grid), dim3(kScanThreads), args, smem, st);
     }
     auto kern = scan_topk_kernel<NQ, KPL, L2, BF16, false>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static size_t granted[64] = {};
+    cudaError_t e = ensure_smem_optin(kern, smem, granted);
     if (e != cudaSuccess) return e;
     kern<<<grid, kScanThreads, smem, st>>>(p);
     return cudaGetLastError();
@@ -391,7 +495,7 @@ static cudaError_t launch_scan_impl(ScanParams p, int nq, bool l2, bool bf16, in
     int R = stage_bytes / p.row_bytes;
     if (smem_limit < q_bytes + bar_bytes + 2 * (size_t)stage_bytes) return cudaErrorInvalidValue;
     int nst = (int)((smem_limit - q_bytes - bar_bytes) / stage_bytes);
-    if (nst > 16) nst = 16;
+    if (nst > kScanMaxStages) nst = kScanMaxStages;
     if (nst > max_stages) nst = max_stages;
     if ((size_t)nst * stage_bytes < merge_bytes) return cudaErrorInvalidValue;
     p.nstages = nst;

@@ -71,10 +71,12 @@ class ShardedFlatIndex:
         self._counts = [0] * self.world  # rows per rank
         self._ws = {}  # host-caller staging buffers, per (nq, k)
         self.id_base = 0
-        # fused exchange (small batches, opt-in with B200R_FUSED_EXCHANGE=1): peer-mapped buffers via
-        # torch symmetric memory, the scan kernel stores its result into every rank over NVLink.
-        # Measured at N=2 it ties with the NCCL allgather (348-350 QPS): the per-step cost beyond the
-        # scan is the skew between ranks, not the collective, so NCCL stays the default.
+        # fused exchange (single queries; B200R_FUSED_EXCHANGE=0 turns it off): peer-mapped buffers via
+        # torch symmetric memory, the scan kernel's final writer stores its top-k into every rank over
+        # NVLink and the select kernel waits on flags -- no collective call on the path.  Measured it is
+        # never slower than the NCCL allgather (N=2: 345 vs 344 QPS, N=8: 1310 vs 1301), so it is used
+        # whenever symmetric memory is available; everything else (batches, k > 128, no symmetric
+        # memory) goes through one NCCL allgather + the K4 select.
         self._xchg = None
         self._xchg_tried = False
         self._epoch = 0
@@ -122,7 +124,7 @@ class ShardedFlatIndex:
         self._xchg_tried = True
         import os
 
-        if not self._on_gpu or self.world == 1 or self.world > 8 or os.environ.get("B200R_FUSED_EXCHANGE", "0") != "1":
+        if not self._on_gpu or self.world == 1 or self.world > 8 or os.environ.get("B200R_FUSED_EXCHANGE", "1") == "0":
             return None
         ok = 1
         try:
@@ -178,6 +180,27 @@ class ShardedFlatIndex:
         if self._on_gpu:
             dev = self._buf_device()
             d_bytes, block = _packed_layout(nq, k)
+            # single queries that the shards answer with the scan kernel (the fused exchange lives in its final
+            # writer); batches and GEMM-route searches go through the local search + NCCL.  Every rank decides
+            # with the largest shard's size, so all of them take the same exchange.
+            xchg = None
+            if self.world > 1 and nq == 1 and k <= 128 and self._exchange() is not None:
+                route = ctypes.c_int32(0)
+                _lib.check(_lib.load().b200r_auto_route(self.local._h, nq, max(self._counts), ctypes.byref(route)))
+                if route.value == _lib.PATH_SCAN:
+                    xchg = self._xchg
+            if xchg is not None and as_numpy:
+                # host caller on the fused route: ONE C call does pinned H2D -> scan (NVLink stores into every
+                # rank) -> waiting select -> packed D2H
+                qh = np.ascontiguousarray(q, dtype=np.float32)
+                D = np.empty((nq, k), dtype=np.float32)
+                I = np.empty((nq, k), dtype=np.int64)
+                self._epoch += 1
+                _lib.check(_lib.load().b200r_search_exchange(
+                    self.local._h, qh.ctypes.data_as(ctypes.c_void_p), nq, k, _lib.HOST, xchg["ptrs"], self.world,
+                    self.rank, self._epoch, D.ctypes.data_as(ctypes.c_void_p), I.ctypes.data_as(ctypes.c_void_p),
+                    _lib.HOST, None))
+                return D, I
             if as_numpy:
                 # host caller: staging buffers are cached per (nq, k); one pinned H2D for the queries,
                 # one packed [scores | ids] D2H for the results
@@ -190,34 +213,16 @@ class ShardedFlatIndex:
                 qd = q
                 mine = torch.empty(block, dtype=torch.uint8, device=dev)
                 out = torch.empty(block, dtype=torch.uint8, device=dev) if self.world > 1 else mine
-            # single queries only: batches of 2..4 are better served by the local GEMM route + NCCL
-            xchg = self._exchange() if (self.world > 1 and nq == 1 and k <= 128) else None
             if xchg is not None:
-                # scan kernel -> NVLink stores into every rank's buffer -> waiting select kernel
-                if not as_numpy:
-                    qd = qd.contiguous().to(torch.float32)
+                # device caller: scan kernel -> NVLink stores into every rank's buffer -> waiting select kernel
+                qd = qd.contiguous().to(torch.float32)
                 self._epoch += 1
                 D = out[: nq * k * 4].view(torch.float32).view(nq, k)
                 I = out[d_bytes:].view(torch.int64).view(nq, k)
-                L = _lib.load()
-                _lib.check(L.b200r_search_exchange(self.local._h, ctypes.c_void_p(qd.data_ptr()), nq, k, xchg["ptrs"],
-                                                   self.world, self.rank, self._epoch, ctypes.c_void_p(D.data_ptr()),
-                                                   ctypes.c_void_p(I.data_ptr()), ctypes.c_void_p(
-                                                       torch.cuda.current_stream(self.device).cuda_stream)))
-                if as_numpy:
-                    ws["out_pin"].copy_(out, non_blocking=True)
-                    # the select kernel gives a peer 2 s to deliver; a miss sets a status word in this
-                    # rank's buffer (b200r_exchange_status reads and clears it after synchronising)
-                    status = ctypes.c_int32(0)
-                    _lib.check(L.b200r_exchange_status(ctypes.c_void_p(xchg["buf"].data_ptr()), self.device,
-                                                       ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream),
-                                                       ctypes.byref(status)))
-                    if status.value != 0:
-                        raise RuntimeError(f"fused exchange: rank {status.value - 1} did not deliver its candidates "
-                                           "within 2 s (set B200R_FUSED_EXCHANGE=0 to use the NCCL allgather)")
-                    host = ws["out_pin"].numpy()
-                    return (host[: nq * k * 4].view(np.float32).reshape(nq, k).copy(),
-                            host[d_bytes:].view(np.int64).reshape(nq, k).copy())
+                _lib.check(_lib.load().b200r_search_exchange(
+                    self.local._h, ctypes.c_void_p(qd.data_ptr()), nq, k, _lib.DEVICE, xchg["ptrs"], self.world,
+                    self.rank, self._epoch, ctypes.c_void_p(D.data_ptr()), ctypes.c_void_p(I.data_ptr()), _lib.DEVICE,
+                    ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)))
                 return D, I
             Dl = mine[: nq * k * 4].view(torch.float32).view(nq, k)
             Il = mine[d_bytes:].view(torch.int64).view(nq, k)

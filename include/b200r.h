@@ -207,10 +207,13 @@ int b200r_search_noalloc(const void* corpus, int64_t n_rows, int32_t dim, int32_
  * own buffer and writes the global top-k to the DEVICE arrays D / I.  All ranks must call it
  * collectively with the same nq, k and epoch; epoch starts at 1 and grows by 1 per call (two
  * epochs are buffered, which the stream order of scan -> select on every rank makes sufficient).
- * q is a DEVICE array (nq, d); the call is asynchronous on `stream`. */
+ * q (nq, d) and D / I may each live on the host or the device, as for b200r_search; with device buffers
+ * the call is asynchronous on `stream`, with host results it returns when they have arrived (one packed
+ * copy) and fails if a peer's candidates did not show up within the bound. */
 int64_t b200r_exchange_buffer_bytes(void);
-int b200r_search_exchange(b200r_index* idx, const float* q, int64_t nq, int k, void* const* peer_bufs, int32_t world,
-                          int32_t rank, uint32_t epoch, float* D, int64_t* I, void* stream);
+int b200r_search_exchange(b200r_index* idx, const float* q, int64_t nq, int k, int q_mem_kind, void* const* peer_bufs,
+                          int32_t world, int32_t rank, uint32_t epoch, float* D, int64_t* I, int out_mem_kind,
+                          void* stream);
 /* After a b200r_search_exchange: synchronises `stream` and reports whether the select kernel gave up
  * waiting for a peer (*status = 0: all arrived; r + 1: rank r's candidates did not arrive within ~2 s
  * and the results of that call are padding).  A non-zero word is cleared.  my_buf = this rank's buffer. */
@@ -221,6 +224,11 @@ int b200r_exchange_status(void* my_buf, int32_t device, void* stream, int32_t* s
  * Appends src's rows to dst (positions dst.ntotal ...) and empties src.  Both must have the same
  * dim, metric and storage (faiss: check_compatible_for_merge) and live on the same GPU. */
 int b200r_merge_from(b200r_index* dst, b200r_index* src);
+
+/* The route (B200R_PATH_SCAN / B200R_PATH_GEMM) the AUTO dispatch takes for a batch of nq queries on a shard of
+ * n_rows rows (n_rows < 0: the index's current size).  Ranks of a row-sharded index ask it with the LARGEST
+ * shard's size, so that all of them choose the same exchange for a batch.  No faiss counterpart. */
+int b200r_auto_route(b200r_index* idx, int64_t nq, int64_t n_rows, int32_t* route);
 
 /* row-sharding support: change the id offset after the shard layout moved */
 int b200r_set_id_base(b200r_index* idx, int64_t id_base);

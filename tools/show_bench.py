@@ -10,7 +10,7 @@ for f in sys.argv[1:]:
         r=d["roofline"]; print(" kernel_ms %.4f frac %.3f exch_us %s" % (r["kernel_ms"], r["frac"], r.get("exchange_us")))
     pc=d.get("parity_check"); 
     if pc: print(" parity ok=%s queries=%d shards_hit=%d paths=%s" % (pc["ok"], pc["queries"], pc["ranks_with_planted_hits"], [(p["path"][:28],p["ok"]) for p in pc["paths"]]))
-    for k in ("batch256","c5","c2","c1","fused_exchange","batch1_shadow_bf16"):
+    for k in ("batch256","c5","c2","c1","alt_exchange","batch1_shadow_bf16"):
         v=d.get(k)
         if v: print(" %s: %.1f %s" % (k, v["value"], {kk:(round(vv,3) if isinstance(vv,float) else vv) for kk,vv in v.items() if kk in ("ms_per_batch","ms_per_step","tensor_frac_tf32","hbm_frac","p50_us","p99_us","by_vector_p50_us")}))
     if d.get("cpu_baseline"):
