@@ -52,6 +52,8 @@ SIGNATURES = {
     "b200r_destroy": (_int, [_vp]),
     "b200r_add": (_int, [_vp, _vp, _i64, _int, _int, _vp]),
     "b200r_search": (_int, [_vp, _vp, _i64, _int, _int, _vp, _vp, _int, _vp]),
+    "b200r_search_threshold": (_int, [_vp, _vp, _i64, _int, _i32, ctypes.c_double, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "b200r_mmr": (_int, [_vp, _vp, _vp, _i64, _int, ctypes.c_double, _vp, ctypes.POINTER(_i32)]),
     "b200r_remove_ids": (_int, [_vp, _vp, _i64, ctypes.POINTER(_i64)]),
     "b200r_ntotal": (_int, [_vp, ctypes.POINTER(_i64)]),
     "b200r_reconstruct": (_int, [_vp, _i64, _vp]),

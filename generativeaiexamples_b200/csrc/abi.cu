@@ -217,6 +217,137 @@ extern "C" int b200r_merge_from(b200r_index* dst, b200r_index* src) {
 }
 
 // ---------------------------------------------------------------------------
+// relevance threshold and MMR on the device (rerank.cu)
+// ---------------------------------------------------------------------------
+namespace b200r {
+void free_rerank_ws(b200r_index* ix) {
+    if (ix->rr_stream) cudaStreamSynchronize(ix->rr_stream);
+    cudaFree(ix->rr_dev);
+    cudaFreeHost(ix->rr_pin);
+    if (ix->rr_stream) cudaStreamDestroy(ix->rr_stream);
+    ix->rr_dev = ix->rr_pin = nullptr;
+    ix->rr_stream = nullptr;
+    ix->rr_cap = 0;
+}
+}  // namespace b200r
+
+static int ensure_rerank_ws(b200r_index* ix, size_t bytes) {
+    if (!ix->rr_stream) CU(cudaStreamCreateWithFlags(&ix->rr_stream, cudaStreamNonBlocking));
+    if (bytes <= ix->rr_cap) return B200R_OK;
+    CU(cudaStreamSynchronize(ix->rr_stream));
+    cudaFree(ix->rr_dev);
+    cudaFreeHost(ix->rr_pin);
+    ix->rr_dev = ix->rr_pin = nullptr;
+    ix->rr_cap = 0;
+    const size_t cap = std::max<size_t>(bytes, 1u << 20);
+    CU(cudaMalloc(&ix->rr_dev, cap));
+    CU(cudaMallocHost(&ix->rr_pin, cap));
+    ix->rr_cap = cap;
+    return B200R_OK;
+}
+
+static size_t align16(size_t v) { return (v + 15) / 16 * 16; }
+
+extern "C" int b200r_search_threshold(b200r_index* ix, const float* q, int64_t nq, int k, int32_t relevance_kind,
+                                      double threshold, int32_t apply_threshold, double* R, float* D, int64_t* I,
+                                      int32_t* counts, int32_t* out_of_range) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_search_threshold: null index");
+    if (nq < 0) return fail(B200R_E_INVALID, "b200r_search_threshold: nq = %lld", (long long)nq);
+    if (k <= 0) return fail(B200R_E_INVALID, "b200r_search_threshold: k must be > 0, got %d", k);
+    if (nq == 0) return B200R_OK;
+    if (!q || !R || !D || !I || !counts) return fail(B200R_E_INVALID, "b200r_search_threshold: null buffer");
+    if (relevance_kind < 0 || relevance_kind > 2)
+        return fail(B200R_E_INVALID, "b200r_search_threshold: relevance_kind must be 0 (euclidean), 1 (cosine) or 2 "
+                                     "(max inner product)");
+    std::lock_guard<std::mutex> lk(ix->rr_mu);
+    DeviceGuard g(ix->device);
+    const int d = ix->cfg.dim;
+    const size_t nk = (size_t)nq * k;
+    // device: [queries | raw D | raw I] then the block that travels back: [R | D | I | counts | out-of-range]
+    const size_t o_q = 0, o_rd = align16(o_q + (size_t)nq * d * 4), o_ri = align16(o_rd + nk * 4);
+    const size_t o_back = align16(o_ri + nk * 8);
+    const size_t b_r = 0, b_d = align16(b_r + nk * 8), b_i = align16(b_d + nk * 4), b_c = align16(b_i + nk * 8),
+                 b_o = align16(b_c + (size_t)nq * 4), back_bytes = align16(b_o + (size_t)nq * 4);
+    int rc = ensure_rerank_ws(ix, o_back + back_bytes);
+    if (rc != B200R_OK) return rc;
+    cudaStream_t st = ix->rr_stream;
+    uint8_t* dv = ix->rr_dev;
+    memcpy(ix->rr_pin, q, (size_t)nq * d * 4);
+    CU(cudaMemcpyAsync(dv + o_q, ix->rr_pin, (size_t)nq * d * 4, cudaMemcpyHostToDevice, st));
+    float* raw_d = reinterpret_cast<float*>(dv + o_rd);
+    int64_t* raw_i = reinterpret_cast<int64_t*>(dv + o_ri);
+    rc = ix->multi ? multi_search(ix, dv + o_q, nq, k, B200R_DEVICE, raw_d, raw_i, B200R_DEVICE, st)
+                   : leaf_search(ix, dv + o_q, nq, k, B200R_DEVICE, raw_d, raw_i, B200R_DEVICE, st, B200R_PATH_AUTO, nullptr);
+    if (rc != B200R_OK) return rc;
+    uint8_t* back = dv + o_back;
+    CU(launch_relevance_filter(raw_d, raw_i, (int)nq, k, relevance_kind, threshold, apply_threshold != 0,
+                               reinterpret_cast<double*>(back + b_r), reinterpret_cast<float*>(back + b_d),
+                               reinterpret_cast<int64_t*>(back + b_i), reinterpret_cast<int32_t*>(back + b_c),
+                               reinterpret_cast<int32_t*>(back + b_o), st));
+    CU(cudaMemcpyAsync(ix->rr_pin, back, back_bytes, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const uint8_t* hb = ix->rr_pin;
+    const int32_t* hc = reinterpret_cast<const int32_t*>(hb + b_c);
+    memcpy(counts, hc, (size_t)nq * 4);
+    if (out_of_range) memcpy(out_of_range, hb + b_o, (size_t)nq * 4);
+    // only the passing hits are meaningful: rows are copied whole (k is small), the tail is left as it is
+    memcpy(R, hb + b_r, nk * 8);
+    memcpy(D, hb + b_d, nk * 4);
+    memcpy(I, hb + b_i, nk * 8);
+    return B200R_OK;
+}
+
+extern "C" int b200r_mmr(b200r_index* ix, const float* query, const int64_t* keys, int64_t m, int k, double lambda_mult,
+                         int32_t* selected, int32_t* n_selected) {
+    if (!ix) return fail(B200R_E_INVALID, "b200r_mmr: null index");
+    if (m < 0 || k <= 0) return fail(B200R_E_INVALID, "b200r_mmr: bad sizes");
+    if (!query || !selected || !n_selected || (m > 0 && !keys)) return fail(B200R_E_INVALID, "b200r_mmr: null buffer");
+    if (m > kMmrMaxCandidates)
+        return fail(B200R_E_UNSUPPORTED, "b200r_mmr: %lld candidates, at most %d are supported", (long long)m, kMmrMaxCandidates);
+    *n_selected = 0;
+    if (m == 0) return B200R_OK;
+    std::lock_guard<std::mutex> lk(ix->rr_mu);
+    DeviceGuard g(ix->device);
+    const int d = ix->cfg.dim;
+    const size_t o_q = 0, o_k = align16((size_t)d * 4), o_e = align16(o_k + (size_t)m * 8),
+                 o_s = align16(o_e + (size_t)m * d * 4), total = align16(o_s + ((size_t)k + 1) * 4);
+    int rc = ensure_rerank_ws(ix, total);
+    if (rc != B200R_OK) return rc;
+    cudaStream_t st = ix->rr_stream;
+    uint8_t* dv = ix->rr_dev;
+    float* emb = reinterpret_cast<float*>(dv + o_e);
+    if (ix->multi) {
+        // the candidates live on several GPUs: fetch them through the segment map, then select on the primary GPU
+        rc = multi_reconstruct_batch(ix, keys, m, reinterpret_cast<float*>(ix->rr_pin + o_e));
+        if (rc != B200R_OK) return rc;
+        memcpy(ix->rr_pin + o_q, query, (size_t)d * 4);
+        CU(cudaMemcpyAsync(dv + o_q, ix->rr_pin + o_q, (size_t)d * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(emb, ix->rr_pin + o_e, (size_t)m * d * 4, cudaMemcpyHostToDevice, st));
+    } else {
+        std::lock_guard<std::mutex> li(ix->mu);
+        for (int64_t i = 0; i < m; i++)
+            if (keys[i] < 0 || keys[i] >= ix->ntotal)
+                return fail(B200R_E_INVALID, "b200r_mmr: key %lld out of range [0, %lld)", (long long)keys[i],
+                            (long long)ix->ntotal);
+        memcpy(ix->rr_pin + o_q, query, (size_t)d * 4);
+        memcpy(ix->rr_pin + o_k, keys, (size_t)m * 8);
+        CU(cudaMemcpyAsync(dv + o_q, ix->rr_pin + o_q, o_k + (size_t)m * 8, cudaMemcpyHostToDevice, st));
+        if (ix->data_ev_set) CU(cudaStreamWaitEvent(st, ix->data_ev, 0));
+        // the candidates' rows never leave the GPU: gathered as fp32 next to the query
+        CU(launch_rows_to_f32(ix->rows, ix->row_bytes, d, ix->bf16, reinterpret_cast<const int64_t*>(dv + o_k), m, emb, st));
+        ix->st.n_kernel_launches++;
+    }
+    int32_t* sel_dev = reinterpret_cast<int32_t*>(dv + o_s);
+    CU(launch_mmr(emb, reinterpret_cast<const float*>(dv + o_q), (int)m, d, k, lambda_mult, sel_dev + 1, sel_dev, st));
+    CU(cudaMemcpyAsync(ix->rr_pin + o_s, sel_dev, ((size_t)std::min<int64_t>(k, m) + 1) * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const int32_t* hs = reinterpret_cast<const int32_t*>(ix->rr_pin + o_s);
+    *n_selected = hs[0];
+    memcpy(selected, hs + 1, (size_t)hs[0] * 4);
+    return B200R_OK;
+}
+
+// ---------------------------------------------------------------------------
 // stand-alone normalise and merge
 // ---------------------------------------------------------------------------
 extern "C" int b200r_normalize_l2(float* x, int64_t n, int32_t d, int mem_kind, int32_t device, void* stream) {

@@ -65,7 +65,7 @@ static void read_knobs_locked() {
     k.gemm_warmup = (int)geti("B200R_GEMM_WARMUP", -1);
     k.small_gemm = (int)geti("B200R_SMALL_GEMM", -1);
     k.multi_workers = (int)geti("B200R_MULTI_WORKERS", -1);
-    k.multi_spin_us = (int)geti("B200R_MULTI_SPIN_US", 200);
+    k.multi_spin_us = (int)geti("B200R_MULTI_SPIN_US", 2000);
     k.multi_fused = (int)geti("B200R_MULTI_FUSED", -1);
     g_knobs = k;
 }
@@ -201,6 +201,7 @@ void leaf_free(b200r_index* ix) {
     cudaFree(ix->bounce);
     cudaFree(ix->adj_dev);
     cudaFree(ix->trace_dev);
+    free_rerank_ws(ix);
     for (auto& e : ix->fb_ev)
         if (e) cudaEventDestroy(e);
     for (auto& e : ix->add_ev)

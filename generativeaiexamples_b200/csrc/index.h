@@ -60,7 +60,7 @@ struct Knobs {
     int gemm_warmup = -1;           // B200R_GEMM_WARMUP      (-1 = unset)
     int small_gemm = -1;            // B200R_SMALL_GEMM       (-1 = default)
     int multi_workers = -1;         // B200R_MULTI_WORKERS    (-1 = default: on for >= 2 shards)
-    int multi_spin_us = 200;        // B200R_MULTI_SPIN_US    how long an idle shard worker polls before it sleeps
+    int multi_spin_us = 2000;       // B200R_MULTI_SPIN_US    how long an idle shard worker polls before it sleeps
     int multi_fused = -1;           // B200R_MULTI_FUSED      (-1 = default)
 };
 const Knobs& knobs();
@@ -155,6 +155,12 @@ struct b200r_index {
     int64_t* adj_dev = nullptr;    // remove_ids: adjusted deleted positions
     int64_t adj_cap = 0;
     unsigned long long* trace_dev = nullptr;  // B200R_SCAN_TRACE
+    // threshold / MMR entry points (abi.cu): staging on this index's (primary) GPU
+    std::mutex rr_mu;
+    uint8_t* rr_dev = nullptr;
+    uint8_t* rr_pin = nullptr;
+    size_t rr_cap = 0;
+    cudaStream_t rr_stream = nullptr;
 
     std::mutex mu;
     b200r_stats st{};
@@ -194,6 +200,15 @@ int leaf_reset(b200r_index* ix);
 int leaf_merge_from(b200r_index* dst, b200r_index* src);
 int leaf_stats(b200r_index* ix, b200r_stats* out);
 int leaf_last_search_ms(b200r_index* ix, double* ms_out);
+
+// re-ranking kernels (rerank.cu)
+constexpr int kMmrMaxCandidates = 2048;
+cudaError_t launch_relevance_filter(const float* d_in, const int64_t* i_in, int nq, int k, int kind, double threshold,
+                                    bool apply_threshold, double* r_out, float* d_out, int64_t* i_out, int32_t* counts,
+                                    int32_t* out_of_range, cudaStream_t st);
+cudaError_t launch_mmr(const float* emb, const float* q, int m, int d, int k, double lambda_mult, int32_t* selected,
+                       int32_t* n_selected, cudaStream_t st);
+void free_rerank_ws(b200r_index* ix);
 
 // multi-GPU index (multi.cu)
 int multi_create(const b200r_config* cfg, b200r_index** out);

@@ -293,6 +293,10 @@ void multi_free(b200r_index* ix) {
         cudaGetLastError();
         delete m;
     }
+    {
+        DeviceGuard dg(ix->device);
+        free_rerank_ws(ix);
+    }
     delete ix;
 }
 

@@ -150,6 +150,44 @@ class B200IndexFlat:
                                         _lib.HOST, None))
         return D, I
 
+    # -- search + relevance threshold / MMR selection on the device (no faiss counterpart) -----------
+    RELEVANCE_KINDS = {"EUCLIDEAN_DISTANCE": 0, "COSINE": 1, "MAX_INNER_PRODUCT": 2}
+
+    def search_threshold(self, x, k: int, relevance: str, score_threshold: Optional[float]):
+        """``search`` followed on the GPU by LangChain's relevance function and ``score >= score_threshold``
+        (``VectorStore.similarity_search_with_relevance_scores``).  Returns ``(R, D, I, counts, out_of_range)``:
+        for query ``i`` the first ``counts[i]`` entries are the kept hits (relevance float64, raw score float32,
+        id), the dropped hits follow, then padding with id -1."""
+        x = np.ascontiguousarray(x, dtype="float32")
+        n, d = x.shape
+        assert d == self.d
+        assert k > 0
+        R = np.empty((n, k), dtype=np.float64)
+        D = np.empty((n, k), dtype=np.float32)
+        I = np.empty((n, k), dtype=np.int64)
+        counts = np.empty(n, dtype=np.int32)
+        oor = np.empty(n, dtype=np.int32)
+        _lib.check(self._L.b200r_search_threshold(
+            self._h, x.ctypes.data_as(ctypes.c_void_p), n, k, self.RELEVANCE_KINDS[relevance],
+            0.0 if score_threshold is None else float(score_threshold), int(score_threshold is not None),
+            R.ctypes.data_as(ctypes.c_void_p), D.ctypes.data_as(ctypes.c_void_p), I.ctypes.data_as(ctypes.c_void_p),
+            counts.ctypes.data_as(ctypes.c_void_p), oor.ctypes.data_as(ctypes.c_void_p)))
+        return R, D, I, counts, oor
+
+    def mmr_select(self, query, keys, k: int, lambda_mult: float = 0.5) -> np.ndarray:
+        """LangChain's ``maximal_marginal_relevance`` over the stored rows ``keys``: positions into ``keys`` of the
+        ``min(k, len(keys))`` picks, in picking order.  The rows are gathered and compared on the GPU."""
+        query = np.ascontiguousarray(query, dtype="float32").reshape(-1)
+        assert query.size == self.d
+        keys = np.ascontiguousarray(keys, dtype="int64")
+        assert keys.ndim == 1 and k > 0
+        sel = np.empty(k, dtype=np.int32)
+        n_sel = ctypes.c_int32(0)
+        _lib.check(self._L.b200r_mmr(self._h, query.ctypes.data_as(ctypes.c_void_p), keys.ctypes.data_as(ctypes.c_void_p),
+                                     keys.size, k, float(lambda_mult), sel.ctypes.data_as(ctypes.c_void_p),
+                                     ctypes.byref(n_sel)))
+        return sel[: n_sel.value].copy()
+
     # -- remove / reconstruct / reset ----------------------------------------
     def remove_ids(self, x) -> int:
         """faiss ``replacement_remove_ids`` with an id array (IDSelectorBatch)."""

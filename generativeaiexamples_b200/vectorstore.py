@@ -218,7 +218,7 @@ class B200FlatVectorStore(_VSBase):
                  index_to_docstore_id: Optional[Dict[int, str]] = None,
                  relevance_score_fn: Optional[Callable[[float], float]] = None, normalize_L2: bool = False,
                  distance_strategy: DistanceStrategy = DistanceStrategy.EUCLIDEAN_DISTANCE, *, storage: str = "f32",
-                 device: int = 0, reserve_rows: int = 0, coalesce: bool = False):
+                 device: int = 0, reserve_rows: int = 0, coalesce: bool = False, devices=None):
         """``index`` is a ``B200IndexFlat`` or, for lazy construction, the embedding
         dimension (int) / None (sized from the first vectors added, like ``FAISS.__from``)."""
         if not (hasattr(embedding_function, "embed_documents") and hasattr(embedding_function, "embed_query")):
@@ -230,7 +230,8 @@ class B200FlatVectorStore(_VSBase):
         self.distance_strategy = DistanceStrategy(distance_strategy)
         self.override_relevance_score_fn = relevance_score_fn
         self._normalize_L2 = bool(normalize_L2)
-        self._opts = dict(storage=storage, device=device, reserve_rows=reserve_rows)
+        # devices=[0, 1, ...]: a lazily created index spans those GPUs of this process (csrc/multi.cu)
+        self._opts = dict(storage=storage, device=device, reserve_rows=reserve_rows, devices=devices)
         # coalesce=True: concurrent single-query searches (e.g. asyncio.gather of
         # asimilarity_search_by_vector, faiss_vdb_service.py:169-174) share one batched launch
         self._coalesce = bool(coalesce)
@@ -413,9 +414,46 @@ class B200FlatVectorStore(_VSBase):
         hits = self.similarity_search_with_score(query, k=k, filter=filter, fetch_k=fetch_k, **kwargs)
         return [(doc, fn(score)) for doc, score in hits]
 
+    def _device_relevance(self, query: str, k: int, score_threshold: Optional[float]):
+        """Relevance scores and the threshold computed by the engine (``b200r_search_threshold``): the host
+        only walks the docstore for hits that passed.  ``None`` when this store's configuration needs
+        LangChain's host path (custom relevance function, coalesced searches, a foreign index object)."""
+        if (self.override_relevance_score_fn is not None or self._coalesce or self.index is None
+                or not hasattr(self.index, "search_threshold")):
+            return None
+        kinds = {DistanceStrategy.EUCLIDEAN_DISTANCE: "EUCLIDEAN_DISTANCE", DistanceStrategy.COSINE: "COSINE",
+                 DistanceStrategy.MAX_INNER_PRODUCT: "MAX_INNER_PRODUCT"}
+        if self.distance_strategy not in kinds:
+            return None
+        R, _, I, counts, oor = self.index.search_threshold(_to_matrix(self._embed_query(query)), k,
+                                                           kinds[self.distance_strategy], score_threshold)
+
+        def docs(lo, hi):
+            out = []
+            for j in range(lo, hi):
+                _id = self.index_to_docstore_id[int(I[0, j])]
+                doc = self.docstore.search(_id)
+                if not isinstance(doc, Document):
+                    raise ValueError(f"Could not find document for id {_id}, got {doc}")
+                out.append((doc, float(R[0, j])))
+            return out
+
+        kept = docs(0, int(counts[0]))
+        if oor[0] > 0:  # LangChain's warning lists every hit, also the ones the threshold drops
+            n_valid = int((I[0] >= 0).sum())
+            warnings.warn(f"Relevance scores must be between 0 and 1, got {kept + docs(int(counts[0]), n_valid)}")
+        return kept
+
     def similarity_search_with_relevance_scores(self, query: str, k: int = 4,
                                                 **kwargs: Any) -> List[Tuple[Document, float]]:
         score_threshold = kwargs.pop("score_threshold", None)
+        if not kwargs:
+            scored = self._device_relevance(query, k, score_threshold)
+            if scored is not None:
+                if score_threshold is not None and len(scored) == 0:
+                    warnings.warn("No relevant docs were retrieved using the relevance score threshold "
+                                  f"{score_threshold}")
+                return scored
         scored = self._similarity_search_with_relevance_scores(query, k=k, **kwargs)
         if any(s < 0.0 or s > 1.0 for _, s in scored):
             warnings.warn(f"Relevance scores must be between 0 and 1, got {scored}")
@@ -452,12 +490,18 @@ class B200FlatVectorStore(_VSBase):
             scores = np.array([scores[order[p_]] for p_ in keep], dtype=np.float32)
             indices = np.array(keep, dtype=np.int64)
         valid = [int(i) for i in indices if i != -1]  # -1 happens when not enough docs are returned
-        if hasattr(self.index, "reconstruct_batch"):
-            embeddings = self.index.reconstruct_batch(np.array(valid, dtype=np.int64))
+        if hasattr(self.index, "mmr_select") and len(valid) <= 2048:
+            # the candidates' rows are gathered and compared on the GPU; only the picks come back
+            selected = [int(j) for j in self.index.mmr_select(np.asarray(embedding, dtype=np.float32),
+                                                              np.array(valid, dtype=np.int64), k, lambda_mult)]
         else:
-            embeddings = np.stack([self.index.reconstruct(i) for i in valid]) if valid else np.zeros((0, 1), np.float32)
-        selected = maximal_marginal_relevance(np.array([embedding], dtype=np.float32), embeddings, k=k,
-                                              lambda_mult=lambda_mult)
+            if hasattr(self.index, "reconstruct_batch"):
+                embeddings = self.index.reconstruct_batch(np.array(valid, dtype=np.int64))
+            else:
+                embeddings = (np.stack([self.index.reconstruct(i) for i in valid]) if valid
+                              else np.zeros((0, 1), np.float32))
+            selected = maximal_marginal_relevance(np.array([embedding], dtype=np.float32), embeddings, k=k,
+                                                  lambda_mult=lambda_mult)
         out = []
         for i in selected:
             if indices[i] == -1:

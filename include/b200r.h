@@ -139,6 +139,28 @@ int b200r_add(b200r_index* idx, const void* x, int64_t n, int dtype, int mem_kin
 int b200r_search(b200r_index* idx, const void* q, int64_t nq, int k, int q_mem_kind, float* D, int64_t* I,
                  int out_mem_kind, void* stream);
 
+/* index.search followed, ON THE DEVICE, by what LangChain's VectorStore.similarity_search_with_relevance_scores
+ * does on the host: every hit's distance d becomes a relevance score (relevance_kind 0 EUCLIDEAN: 1 - d/sqrt(2);
+ * 1 COSINE: 1 - d; 2 MAX_INNER_PRODUCT: d > 0 ? 1 - d : -d -- evaluated in double like the Python functions) and,
+ * with apply_threshold != 0, only hits with relevance >= threshold are kept, moved to the front in their order.
+ * [as_retriever(search_type="similarity_score_threshold") -> chains.py:156-163; multi_turn_rag/chains.py:157-170]
+ * q is a HOST array (nq, d); R (nq, k) double, D (nq, k) fp32, I (nq, k) int64, counts (nq) and out_of_range
+ * (nq, may be NULL) are HOST arrays: the first counts[i] entries of row i are the kept hits; the hits that the
+ * threshold dropped follow them (so that a caller can still word LangChain's warning), then padding with id -1;
+ * out_of_range[i] = how many of the query's hits (kept or not) had a relevance outside [0, 1] (LangChain warns
+ * about those). */
+int b200r_search_threshold(b200r_index* idx, const float* q, int64_t nq, int k, int32_t relevance_kind, double threshold,
+                           int32_t apply_threshold, double* R, float* D, int64_t* I, int32_t* counts,
+                           int32_t* out_of_range);
+
+/* The greedy selection of LangChain's maximal_marginal_relevance(query, embeddings, lambda_mult, k)
+ * [search_type="mmr": FAISS.max_marginal_relevance_search_with_score_by_vector] over the rows keys[0..m) of
+ * the index: the rows are gathered and compared on the device (cosine similarities, the score
+ * lambda*sim(q, x) - (1 - lambda)*max sim(x, picked) in double), only the min(k, m) selected POSITIONS INTO
+ * keys come back.  query, keys, selected (k entries) and n_selected are HOST arrays; m <= 2048. */
+int b200r_mmr(b200r_index* idx, const float* query, const int64_t* keys, int64_t m, int k, double lambda_mult,
+              int32_t* selected, int32_t* n_selected);
+
 /* IndexFlat.remove_ids(ids) -- IDSelectorBatch semantics: positions in ids are
  * removed, later rows shift down (stable), duplicates / out-of-range ignored.
  * [langchain FAISS.delete -> utils.py:559].  ids is a host array. */

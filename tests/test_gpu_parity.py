@@ -1119,3 +1119,45 @@ def test_many_queries_and_many_flagged(built_lib):
     np.testing.assert_array_equal(I2.cpu().numpy(), I[:1500])
     np.testing.assert_array_equal(D1.cpu().numpy(), D)
     ix.close()
+
+
+@pytest.mark.parametrize("metric", ["ip", "l2"])
+@pytest.mark.parametrize("d", [4096, 8192, 16384])
+def test_gemm_parity_wide_rows(built_lib, metric, d):
+    """The tensor-core route on the widest rows the index accepts (a row may be up to 64 KB): the containment
+    bound's accumulation slack grows with the K depth, so the filter + exact re-score is checked against the
+    float64 truth at d = 4096, 8192 and 16384, for fp32 rows, bf16 rows and the bf16 shadow of fp32 rows."""
+    rng = np.random.default_rng(d + (1 if metric == "l2" else 0))
+    n, nq, k = 5000, 40, 10
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    q = rng.standard_normal((nq, d), dtype=np.float32)
+    q[::2] = x[rng.integers(0, n, nq // 2)] + 0.3 * q[::2] / np.sqrt(d)
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    for kw in (dict(), dict(shadow_bf16=True), dict(storage="bf16")):
+        if kw.get("storage") == "bf16" and d * 2 > 64 * 1024:
+            continue
+        ix = _mk(metric, d, search_path=_lib.PATH_GEMM, **kw)
+        ix.add(x)
+        D, I = ix.search(q, k)
+        st = ix.stats()
+        assert st["last_path"] == _lib.PATH_GEMM
+        if kw.get("storage") == "bf16":
+            import torch
+
+            xr = torch.from_numpy(x).to(torch.bfloat16).to(torch.float32).numpy()  # exact vs the rounded corpus
+            _check(metric, D, I, q, xr, k, f"wide rows d={d} bf16 storage")
+        else:
+            _check(metric, D, I, q, x, k, f"wide rows d={d} {kw}")
+            D1, I1 = _mk_scan_result(metric, d, x, q[:3], k)
+            np.testing.assert_array_equal(I[:3], I1)
+            np.testing.assert_array_equal(D[:3], D1)  # both routes end in the same fp32 scoring code
+        ix.close()
+
+
+def _mk_scan_result(metric, d, x, q, k):
+    ix = _mk(metric, d, search_path=_lib.PATH_SCAN)
+    ix.add(x)
+    out = ix.search(q, k)
+    ix.close()
+    return out

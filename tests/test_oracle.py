@@ -217,3 +217,48 @@ def test_merge_from_restatement():
     assert s1.index.ntotal == 5 and sorted(s1.index_to_docstore_id) == [0, 1, 2, 3, 4]
     assert s1.similarity_search("e", k=1)[0].page_content == "e"
     assert s1.similarity_search("a", k=1)[0].page_content == "a"
+
+
+def test_restatement_against_a_real_faiss_when_one_is_installed():
+    """The pin this oracle is waiting for: faiss-cpu is the reference's engine, but there is
+    no wheel for it in this image, so this test skips here.  On a machine that has faiss (any 1.7.x / 1.8.x), the
+    restatement must return faiss's own ids and scores on both code paths (nq < 20 sequential, nq >= 20 BLAS),
+    both metrics, k > ntotal padding, normalize_L2 and remove_ids."""
+    import os
+    import sys
+
+    ref_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref")
+    if os.path.isdir(ref_dir) and ref_dir not in sys.path:
+        sys.path.append(ref_dir)
+    faiss = pytest.importorskip("faiss")
+    from oracle import FlatRef, IndexFlatRef, assert_topk_parity
+
+    rng = np.random.default_rng(2024)
+    d, n = 96, 3000
+    x = rng.standard_normal((n, d), dtype=np.float32)
+    for metric, ctor in ((1, faiss.IndexFlatL2), (0, faiss.IndexFlatIP)):
+        fx = ctor(d)
+        fx.add(x)
+        for nq in (1, 7, 19, 20, 64):
+            q = rng.standard_normal((nq, d), dtype=np.float32)
+            q[::2] = x[rng.integers(0, n, (nq + 1) // 2)] + 0.05 * q[::2]
+            for k in (1, 10, 100):
+                Df, If = fx.search(q, k)
+                Dr, Ir = FlatRef.knn(metric, q, x, k)
+                scale = float((q ** 2).sum(1).max() + (x ** 2).sum(1).max()) if (metric == 1 and nq >= 20) else 1.0
+                assert_topk_parity(Dr, Ir, Df, If, what=f"faiss m={metric} nq={nq} k={k}", scale=scale)
+        Df, If = fx.search(x[:2], n + 5)  # k > ntotal: -1 padding, +-FLT_MAX
+        Dr, Ir = FlatRef.knn(metric, x[:2], x, n + 5)
+        assert (If[:, n:] == -1).all() and (Ir[:, n:] == -1).all()
+        np.testing.assert_array_equal(Df[:, n:], Dr[:, n:])
+        ours = IndexFlatRef(d, metric)
+        ours.add(x)
+        ids = np.array([5, 17, 17, 2999, 4000], dtype=np.int64)
+        assert fx.remove_ids(ids) == ours.remove_ids(ids)
+        np.testing.assert_array_equal(fx.reconstruct(16), ours.reconstruct(16))
+    y = x[:50].copy()
+    y[3] = 0
+    z = y.copy()
+    faiss.normalize_L2(y)
+    FlatRef.normalize_L2(z)
+    np.testing.assert_allclose(y, z, rtol=1e-6, atol=0)

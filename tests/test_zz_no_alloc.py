@@ -61,6 +61,14 @@ def test_noalloc_matches_regular_search_twice(built_lib, metric):
 
     assert_topk_parity(got1[0], got1[1], want1[0], want1[1], what="no-alloc call 1")
     assert_topk_parity(got2[0], got2[1], want2[0], want2[1], what="no-alloc call 2")
+    # ... and against the float64 brute force, so that a fault shared with b200r_search (both run the scan
+    # kernel) cannot hide behind the comparison above
+    from oracle import truth_topk
+
+    name = "l2" if metric == 1 else "ip"
+    Xh, qh = X.cpu().numpy(), q.cpu().numpy()
+    assert_topk_parity(got1[0], got1[1], *truth_topk(name, qh, Xh, 18), what="no-alloc call 1 vs f64 truth")
+    assert_topk_parity(got2[0], got2[1], *truth_topk(name, qh[1:2], Xh, 41), what="no-alloc call 2 vs f64 truth")
     assert got1[1][:, 0].tolist() == [11, 30_000, 59_999]
     assert free_after == free_before, "the no-alloc entry point changed the amount of free device memory"
     index.close()
