@@ -23,11 +23,13 @@ import numpy as np
 
 
 class _Request:
-    __slots__ = ("vec", "k", "done", "D", "I", "err")
+    __slots__ = ("vec", "k", "event", "finished", "lead", "D", "I", "err")
 
     def __init__(self, vec, k):
         self.vec, self.k = vec, k
-        self.done = threading.Event()
+        self.event = threading.Event()  # set when the request is served OR when its caller is made the leader
+        self.finished = False
+        self.lead = False
         self.D = self.I = self.err = None
 
 
@@ -42,6 +44,7 @@ class SearchCoalescer:
         self._busy = False
         self.n_requests = 0
         self.n_launches = 0
+        self.n_handoffs = 0
 
     def search(self, vec: np.ndarray, k: int) -> Tuple[np.ndarray, np.ndarray]:
         """vec: (1, d) float32.  Blocks until this request has been served; thread-safe."""
@@ -52,19 +55,35 @@ class SearchCoalescer:
             lead = not self._busy
             if lead:
                 self._busy = True
-        if lead:
-            self._drain()
-        req.done.wait()
+        while True:
+            if lead:
+                self._drain(req)
+            if req.finished:
+                break
+            req.event.wait()
+            with self._lock:
+                lead, req.lead = req.lead, False
+                if not req.finished:
+                    req.event.clear()
         if req.err is not None:
             raise req.err
         return req.D, req.I
 
-    def _drain(self) -> None:
-        """Run by whichever caller found the coalescer idle: serve batches until nothing is queued."""
+    def _drain(self, own: _Request) -> None:
+        """Run by the leader -- the caller that found the coalescer idle, or one that an earlier leader handed
+        over to: serve batches until the leader's OWN request is done, then pass the role to a caller that is
+        still waiting (so no caller keeps serving strangers under sustained load) or, with nothing queued,
+        mark the coalescer idle."""
         while True:
             with self._lock:
                 if not self._pending:
                     self._busy = False
+                    return
+                if own.finished:
+                    nxt = self._pending[0]
+                    nxt.lead = True
+                    nxt.event.set()
+                    self.n_handoffs += 1
                     return
                 k = self._pending[0].k
                 batch = [r for r in self._pending if r.k == k][: self.max_batch]
@@ -81,7 +100,9 @@ class SearchCoalescer:
                 for r in batch:
                     r.err = e
             finally:
-                for r in batch:
-                    r.done.set()
+                with self._lock:
+                    for r in batch:
+                        r.finished = True
+                        r.event.set()
             if len(batch) > 1 and self.linger_frac > 0:
                 time.sleep(min(self.max_linger_s, self.linger_frac * (time.perf_counter() - t0)))

@@ -279,14 +279,17 @@ extern "C" int b200r_search_threshold(b200r_index* ix, const float* q, int64_t n
     rc = ix->multi ? multi_search(ix, dv + o_q, nq, k, B200R_DEVICE, raw_d, raw_i, B200R_DEVICE, st)
                    : leaf_search(ix, dv + o_q, nq, k, B200R_DEVICE, raw_d, raw_i, B200R_DEVICE, st, B200R_PATH_AUTO, nullptr);
     if (rc != B200R_OK) return rc;
-    uint8_t* back = dv + o_back;
+    // small results: the filter kernel writes straight into the pinned host block (mapped memory); larger
+    // ones go through device memory and one copy
+    const bool zc = back_bytes <= ((size_t)32 << 10) && knobs().zero_copy_out != 0;
+    uint8_t* back = zc ? ix->rr_pin + o_back : dv + o_back;
     CU(launch_relevance_filter(raw_d, raw_i, (int)nq, k, relevance_kind, threshold, apply_threshold != 0,
                                reinterpret_cast<double*>(back + b_r), reinterpret_cast<float*>(back + b_d),
                                reinterpret_cast<int64_t*>(back + b_i), reinterpret_cast<int32_t*>(back + b_c),
                                reinterpret_cast<int32_t*>(back + b_o), st));
-    CU(cudaMemcpyAsync(ix->rr_pin, back, back_bytes, cudaMemcpyDeviceToHost, st));
+    if (!zc) CU(cudaMemcpyAsync(ix->rr_pin + o_back, back, back_bytes, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
-    const uint8_t* hb = ix->rr_pin;
+    const uint8_t* hb = ix->rr_pin + o_back;
     const int32_t* hc = reinterpret_cast<const int32_t*>(hb + b_c);
     memcpy(counts, hc, (size_t)nq * 4);
     if (out_of_range) memcpy(out_of_range, hb + b_o, (size_t)nq * 4);

@@ -56,6 +56,7 @@ static void read_knobs_locked() {
     k.scan_stages = (int)geti("B200R_SCAN_STAGES", 0);
     k.scan_dynamic = (int)geti("B200R_SCAN_DYNAMIC", -1);
     k.scan_trace = (int)geti("B200R_SCAN_TRACE", 0);
+    k.zero_copy_out = (int)geti("B200R_ZERO_COPY_OUT", 1);
     k.gemm_kpcap = (int)geti("B200R_GEMM_KPCAP", 0);
     k.gemm_kprime = (int)geti("B200R_GEMM_KPRIME", 0);
     k.gemm_cluster = (int)geti("B200R_GEMM_CLUSTER", 0);
@@ -579,8 +580,14 @@ int leaf_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kin
 
     // host outputs: scores and ids packed for this nq*k so that one copy brings both back
     const size_t ids_off = round_up((size_t)nq * k * sizeof(float), 16);
-    float* od = out_mem_kind == B200R_DEVICE ? D : reinterpret_cast<float*>(ix->out_buf);
-    int64_t* oi = out_mem_kind == B200R_DEVICE ? I : reinterpret_cast<int64_t*>(ix->out_buf + ids_off);
+    // Small host results are written by the final writer straight into the pinned host buffer (mapped
+    // memory, posted stores over PCIe): no separate device-to-host copy sits between the kernel and the
+    // caller.  Larger ones go through device memory and one DMA.  (B200R_ZERO_COPY_OUT=0 switches it off.)
+    const bool zc_out = out_mem_kind == B200R_HOST && !use_gemm && kn.zero_copy_out != 0 &&
+                        (size_t)nq * k * 12 <= (size_t)16 << 10;
+    uint8_t* host_stage = zc_out ? ix->out_pin : ix->out_buf;
+    float* od = out_mem_kind == B200R_DEVICE ? D : reinterpret_cast<float*>(host_stage);
+    int64_t* oi = out_mem_kind == B200R_DEVICE ? I : reinterpret_cast<int64_t*>(host_stage + ids_off);
     if (xchg) {  // results go to the exchange slots; out_d / out_i stay unused placeholders
         od = ix->out_d;
         oi = ix->out_i;
@@ -735,7 +742,8 @@ int leaf_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kin
         float* pd = (float*)ix->out_pin;
         int64_t* pi = (int64_t*)(ix->out_pin + ids_off);
         // out_buf / out_pin hold cap*(4+8)+64 bytes, so the 16-byte rounding always fits
-        CU(cudaMemcpyAsync(ix->out_pin, ix->out_buf, ids_off + (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        if (!zc_out)
+            CU(cudaMemcpyAsync(ix->out_pin, ix->out_buf, ids_off + (size_t)nq * k * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
         memcpy(D, pd, (size_t)nq * k * sizeof(float));
         memcpy(I, pi, (size_t)nq * k * sizeof(int64_t));

@@ -36,6 +36,7 @@ import asyncio
 import logging
 import math
 import operator
+import struct
 import os
 import pickle
 import uuid
@@ -188,22 +189,40 @@ class InMemoryDocstore:
         return self._dict[search]
 
 
+_PACKERS: Dict[int, struct.Struct] = {}
+
+
+def _pack_row(row) -> np.ndarray:
+    """One Python list / tuple of floats -> float32 vector.  struct.pack converts C doubles to floats (round to
+    nearest, like numpy) about twice as fast as array.array('f') and three times as fast as numpy's object path:
+    11 vs 20 vs 37 us for the 1024 values of one query embedding, which is a third of a 10k-chunk search."""
+    n = len(row)
+    packer = _PACKERS.get(n)
+    if packer is None:
+        if len(_PACKERS) > 64:
+            _PACKERS.clear()
+        packer = _PACKERS[n] = struct.Struct(f"{n}f")
+    try:
+        return np.frombuffer(packer.pack(*row), dtype=np.float32)
+    except (OverflowError, struct.error, TypeError):  # values beyond float32 (numpy gives inf), ints mixed in ...
+        return np.frombuffer(array.array("f", [float(v) for v in row]), dtype=np.float32) \
+            if all(abs(float(v)) < 3.0e38 or v != v for v in row) else np.asarray(row, dtype=np.float32)
+
+
 def _to_matrix(embeddings) -> np.ndarray:
     """list-of-lists / ndarray -> C-contiguous float32 (n, d); the host marshal LangChain
     does with ``np.array(embeddings, dtype=np.float32)``."""
-    # Python lists of floats (what an embedder client returns) convert ~30 % faster through
-    # array.array('f') than through numpy's generic object path; same rounding (C double -> float)
     if isinstance(embeddings, (list, tuple)) and len(embeddings) > 0:
         first = embeddings[0]
         if isinstance(first, float):
-            return np.frombuffer(array.array("f", embeddings), dtype=np.float32)[None, :]
+            return _pack_row(embeddings)[None, :]
         if isinstance(first, (list, tuple)) and len(first) > 0 and isinstance(first[0], float):
             d = len(first)
             m = np.empty((len(embeddings), d), dtype=np.float32)
             for i, row in enumerate(embeddings):
                 if len(row) != d:
                     raise ValueError(f"embedding {i} has {len(row)} values, expected {d}")
-                m[i] = np.frombuffer(array.array("f", row), dtype=np.float32)
+                m[i] = _pack_row(row)
             return m
     m = np.asarray(embeddings, dtype=np.float32)
     if m.ndim == 1:

@@ -237,6 +237,53 @@ def test_coalescer_batches_concurrent_callers():
     assert co.n_requests == 32 and co.n_launches == len(slow.calls)
 
 
+def test_coalescer_hands_leadership_over_under_sustained_load():
+    """A caller that found the coalescer idle serves batches only until its OWN request is answered, then a
+    waiting caller takes over: under a steady stream of requests nobody is kept serving strangers."""
+    import threading
+    import time
+
+    from generativeaiexamples_b200.batching import SearchCoalescer
+
+    class SlowIndex:
+        def __init__(self):
+            self.ix = IndexFlatRef(D, METRIC_L2)
+
+        def search(self, x, k):
+            time.sleep(0.005)
+            return self.ix.search(x, k)
+
+    rng = np.random.default_rng(2)
+    x = rng.standard_normal((300, D)).astype(np.float32)
+    slow = SlowIndex()
+    slow.ix.add(x)
+    co = SearchCoalescer(slow)
+    stop = time.perf_counter() + 0.6
+    worst = [0.0] * 8
+    served = [0] * 8
+
+    def work(t):
+        i = t
+        while time.perf_counter() < stop:
+            t0 = time.perf_counter()
+            _, I = co.search(x[i % 300: i % 300 + 1], 2)
+            worst[t] = max(worst[t], time.perf_counter() - t0)
+            assert I[0, 0] == i % 300
+            served[t] += 1
+            i += 8
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(8)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join(timeout=10)
+    assert not any(t.is_alive() for t in th)
+    assert co.n_handoffs > 0 and min(served) > 5
+    # the queue never ran dry for 0.6 s, yet no single request took anywhere near that long
+    assert max(worst) < 0.2, worst
+    assert not co._busy and not co._pending
+
+
 def test_store_with_coalescing_and_async_gather():
     ours = B200FlatVectorStore(Emb(), IndexFlatRef(D, METRIC_L2), InMemoryDocstore(), {}, coalesce=True)
     ours.add_texts([f"t{i}" for i in range(50)])
