@@ -26,8 +26,19 @@
 
 namespace b200r {
 
-constexpr int kScanConsumerWarps = 16;
-constexpr int kScanThreads = 32 * (1 + kScanConsumerWarps);
+// Consumer warps and rows per warp task.  One query: 16 warps, a warp owns whole rows one at a time
+// (x and q are both read from shared memory: 2 bytes of LDS per corpus byte, 39 % of the LSU peak at
+// HBM speed).  Several queries: a warp takes FOUR consecutive rows at a time and holds each query
+// vector's slice in registers across them, so shared-memory traffic is (4 + NQ) / 4 bytes per corpus
+// byte instead of 1 + NQ (at NQ = 4 that was 5x, which made the four-query variants LSU-bound at half
+// the HBM rate); the 64 accumulators of 4 rows x 4 queries need more registers, hence 8 warps.
+template <int NQ>
+struct ScanShape {
+    static constexpr int kConsumerWarps = NQ == 1 ? 16 : 8;
+    static constexpr int kRowsPerTask = NQ == 1 ? 1 : 4;
+    static constexpr int kThreads = 32 * (1 + kConsumerWarps);
+};
+constexpr int kScanMaxThreads = ScanShape<1>::kThreads;
 constexpr int kScanMaxStages = 16;
 
 __device__ __forceinline__ unsigned long long global_ns() {
@@ -41,9 +52,11 @@ __device__ __forceinline__ unsigned long long global_ns() {
 // (the candidate scratch, the ticket and the shared-memory ring are reused); the pipeline position
 // (stage, phase) simply carries on from one group to the next.
 template <int NQ, int KPL, bool L2, bool BF16, bool FLAGGED>
-__global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanParams p) {
+__global__ void __launch_bounds__(ScanShape<NQ>::kThreads, 1) scan_topk_kernel(const ScanParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
-    constexpr int NCW = kScanConsumerWarps;
+    constexpr int NCW = ScanShape<NQ>::kConsumerWarps;
+    constexpr int RPW = ScanShape<NQ>::kRowsPerTask;
+    constexpr int kScanThreads = ScanShape<NQ>::kThreads;
     constexpr int KCAP = KPL * 32;
 
     const int warp = threadIdx.x >> 5;
@@ -222,6 +235,122 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
             const int64_t rem = p.n_rows - row0;
             const int rows = (int)(rem < R ? rem : R);
             const uint8_t* tile = stage_base + (size_t)s * p.stage_bytes;
+            if constexpr (RPW > 1) {
+                // round-robin ownership of groups of RPW consecutive rows across the CTA's row stream
+                const int ngroups = (rows + RPW - 1) / RPW;
+                int g = (int)(((int64_t)cw - seq) % NCW);
+                if (g < 0) g += NCW;
+                for (; g < ngroups; g += NCW) {
+                    const int r0 = g * RPW;
+                    const int nr = rows - r0 < RPW ? rows - r0 : RPW;
+                    const uint4* xr[RPW];
+#pragma unroll
+                    for (int rr = 0; rr < RPW; rr++)  // rows past the end of the tile repeat the last one (never offered)
+                        xr[rr] = reinterpret_cast<const uint4*>(tile + (size_t)(r0 + (rr < nr ? rr : nr - 1)) * p.row_bytes);
+                    float acc[RPW][NQ][4];
+#pragma unroll
+                    for (int rr = 0; rr < RPW; rr++)
+#pragma unroll
+                        for (int qi = 0; qi < NQ; qi++) acc[rr][qi][0] = acc[rr][qi][1] = acc[rr][qi][2] = acc[rr][qi][3] = 0.f;
+                    // same element order per (row, query) as the one-row path: scores are bit-identical
+                    for (int i0 = 0; i0 < nvec; i0 += 32 * 8) {
+#pragma unroll
+                        for (int u = 0; u < 8; u++) {
+                            const int i = i0 + u * 32 + lane;
+                            if (i < nvec) {
+                                if (!BF16) {
+                                    float4 qv[NQ];
+#pragma unroll
+                                    for (int qi = 0; qi < NQ; qi++) qv[qi] = reinterpret_cast<const float4*>(qs + (size_t)qi * p.d)[i];
+#pragma unroll
+                                    for (int rr = 0; rr < RPW; rr++) {
+                                        const uint4 xv = xr[rr][i];
+                                        const float x0 = __uint_as_float(xv.x), x1 = __uint_as_float(xv.y),
+                                                    x2 = __uint_as_float(xv.z), x3 = __uint_as_float(xv.w);
+#pragma unroll
+                                        for (int qi = 0; qi < NQ; qi++) {
+                                            if (L2) {
+                                                const float t0 = qv[qi].x - x0, t1 = qv[qi].y - x1, t2 = qv[qi].z - x2,
+                                                            t3 = qv[qi].w - x3;
+                                                acc[rr][qi][0] = fmaf(t0, t0, acc[rr][qi][0]);
+                                                acc[rr][qi][1] = fmaf(t1, t1, acc[rr][qi][1]);
+                                                acc[rr][qi][2] = fmaf(t2, t2, acc[rr][qi][2]);
+                                                acc[rr][qi][3] = fmaf(t3, t3, acc[rr][qi][3]);
+                                            } else {
+                                                acc[rr][qi][0] = fmaf(qv[qi].x, x0, acc[rr][qi][0]);
+                                                acc[rr][qi][1] = fmaf(qv[qi].y, x1, acc[rr][qi][1]);
+                                                acc[rr][qi][2] = fmaf(qv[qi].z, x2, acc[rr][qi][2]);
+                                                acc[rr][qi][3] = fmaf(qv[qi].w, x3, acc[rr][qi][3]);
+                                            }
+                                        }
+                                    }
+                                } else {
+                                    float x[RPW][8];
+#pragma unroll
+                                    for (int rr = 0; rr < RPW; rr++) {
+                                        const uint4 xv = xr[rr][i];  // 8 bf16 -> fp32 (exact: bf16 is the top half of an fp32)
+                                        x[rr][0] = __uint_as_float(xv.x << 16);
+                                        x[rr][1] = __uint_as_float(xv.x & 0xffff0000u);
+                                        x[rr][2] = __uint_as_float(xv.y << 16);
+                                        x[rr][3] = __uint_as_float(xv.y & 0xffff0000u);
+                                        x[rr][4] = __uint_as_float(xv.z << 16);
+                                        x[rr][5] = __uint_as_float(xv.z & 0xffff0000u);
+                                        x[rr][6] = __uint_as_float(xv.w << 16);
+                                        x[rr][7] = __uint_as_float(xv.w & 0xffff0000u);
+                                    }
+#pragma unroll
+                                    for (int qi = 0; qi < NQ; qi++) {
+                                        const float4* qp = reinterpret_cast<const float4*>(qs + (size_t)qi * p.d) + 2 * i;
+                                        const float4 qa = qp[0], qb = qp[1];
+                                        const float qq[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+#pragma unroll
+                                        for (int rr = 0; rr < RPW; rr++)
+#pragma unroll
+                                            for (int e = 0; e < 8; e++) {
+                                                if (L2) {
+                                                    const float tt = qq[e] - x[rr][e];
+                                                    acc[rr][qi][e & 3] = fmaf(tt, tt, acc[rr][qi][e & 3]);
+                                                } else {
+                                                    acc[rr][qi][e & 3] = fmaf(qq[e], x[rr][e], acc[rr][qi][e & 3]);
+                                                }
+                                            }
+                                    }
+                                }
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int rr = 0; rr < RPW; rr++) {
+                        if (rr < nr) {
+                            const uint32_t row = (uint32_t)(row0 + r0 + rr);
+#pragma unroll
+                            for (int qi = 0; qi < NQ; qi++) {
+                                const float sc = warp_sum((acc[rr][qi][0] + acc[rr][qi][2]) + (acc[rr][qi][1] + acc[rr][qi][3]));
+                                if (better_val<L2>(sc, top[qi].thr)) {  // row ids only grow: a tie never displaces
+                                    if (lane == npend[qi]) {
+                                        pend_v[qi] = sc;
+                                        pend_i[qi] = row;
+                                    }
+                                    if (++npend[qi] == 32) {
+                                        top[qi].offer_batch(pend_v[qi], pend_i[qi]);
+                                        pend_v[qi] = worst_val<L2>();
+                                        pend_i[qi] = kEmptyId;
+                                        npend[qi] = 0;
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty_bar[s]);
+                seq += ngroups;  // (counts row groups on this path)
+                if (++s == nst) {
+                    s = 0;
+                    ph ^= 1;
+                }
+                continue;
+            }
             // round-robin row ownership across the CTA's row stream
             int r = (int)(((int64_t)cw - seq) % NCW);
             if (r < 0) r += NCW;
@@ -349,7 +478,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) scan_topk_kernel(const ScanPa
     __threadfence();
 
     // phase A: every warp folds a strided subset of the CTA lists, per query
-    constexpr int NW = kScanThreads / 32;
+    constexpr int NW = kScanThreads / 32;  // every warp of this kernel shape
     for (int qi = 0; qi < NQ; qi++) {
         WarpTopK<KPL, L2> m;
         m.init(p.k);
@@ -439,13 +568,14 @@ static cudaError_t launch_one(const ScanParams& p, int grid, size_t smem, cudaSt
         if (e != cudaSuccess) return e;
         ScanParams pc = p;
         void* args[] = {&pc};
-        return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(grid), dim3(kScanThreads), args, smem, st);
+        return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(grid), dim3(ScanShape<NQ>::kThreads), args, smem,
+                                           st);
     }
     auto kern = scan_topk_kernel<NQ, KPL, L2, BF16, false>;
     static size_t granted[64] = {};
     cudaError_t e = ensure_smem_optin(kern, smem, granted);
     if (e != cudaSuccess) return e;
-    kern<<<grid, kScanThreads, smem, st>>>(p);
+    kern<<<grid, ScanShape<NQ>::kThreads, smem, st>>>(p);
     return cudaGetLastError();
 }
 
@@ -482,7 +612,7 @@ static cudaError_t launch_scan_impl(ScanParams p, int nq, bool l2, bool bf16, in
     smem_limit -= 1024;  // static shared + slack
     const size_t q_bytes = (size_t)NQ * p.d * sizeof(float);
     const size_t bar_bytes = 2 * 16 * sizeof(uint64_t);
-    const size_t merge_bytes = (size_t)NQ * (kScanThreads / 32) * KPL * 32 * sizeof(Cand);  // <= 139 KB (NQ=1, KPL=32)
+    const size_t merge_bytes = (size_t)NQ * (kScanMaxThreads / 32) * KPL * 32 * sizeof(Cand);  // <= 139 KB (NQ=1, KPL=32)
     // stage: as many whole rows as fit in 32 KB (at least one)
     // 64 KB stages: 16 rows at d = 1024 fp32, i.e. one row per consumer warp per stage, and fewer,
     // larger bulk copies.  Measured on B200 (tools/tune_scan.py, 10M rows): 64 KB x 3 = 5.66 ms,
