@@ -752,7 +752,10 @@ def main_gpu(args):
                                             (traffic["traffic_over_algorithmic"], traffic["source"])) if traffic else None,
                          "peak_source": peak_src,
                          "kernel": "scan_topk_kernel<1,1,IP,f32>", "kernel_ms": kernel_ms,
+                         # what a step costs beyond its slowest scan launch: exchange over NVLink + final select (+ the
+                         # skew between the GPUs); one process: measured with events inside the library
                          "exchange_us": exchange_us if n_dev > 1 else None,
+                         "step_minus_kernel_us": (ms_dev / args.steps - kernel_ms) * 1000.0,
                          "algorithmic_bytes_per_launch": algo_bytes,
                          "note": "kernel_ms = scan launch (+ query prep when needed), CUDA events on the launching stream; "
                                  "frac can exceed 1 because `peak` is a copy (read+write) figure while the scan only reads: "

@@ -142,14 +142,18 @@ extern "C" int b200r_search_exchange(b200r_index* ix, const float* q, int64_t nq
     const size_t ids_off = ((size_t)nq * k * sizeof(float) + 15) / 16 * 16;
     const size_t status_off = (ids_off + (size_t)nq * k * sizeof(int64_t) + 15) / 16 * 16;
     const bool host_out = out_mem_kind == B200R_HOST;
-    float* od = host_out ? reinterpret_cast<float*>(ix->out_buf) : D;
-    int64_t* oi = host_out ? reinterpret_cast<int64_t*>(ix->out_buf + ids_off) : I;
-    int* status_dev = host_out ? reinterpret_cast<int*>(ix->out_buf + status_off) : nullptr;
+    // (nq <= 4, k <= 128: the block is at most 6 KB, so the select kernel writes it straight into the pinned
+    // host buffer -- mapped memory -- unless B200R_ZERO_COPY_OUT=0 asks for a device-to-host copy)
+    const bool zc = host_out && knobs().zero_copy_out != 0;
+    uint8_t* stage = zc ? ix->out_pin : ix->out_buf;
+    float* od = host_out ? reinterpret_cast<float*>(stage) : D;
+    int64_t* oi = host_out ? reinterpret_cast<int64_t*>(stage + ids_off) : I;
+    int* status_dev = host_out ? reinterpret_cast<int*>(stage + status_off) : nullptr;
     CU(launch_merge_wait(ix->l2, reinterpret_cast<uint8_t*>(peer_bufs[rank]), world, (int)nq, k, epoch, od, oi, status_dev,
                          st));
     ix->st.n_kernel_launches++;
     if (host_out) {
-        CU(cudaMemcpyAsync(ix->out_pin, ix->out_buf, status_off + sizeof(int), cudaMemcpyDeviceToHost, st));
+        if (!zc) CU(cudaMemcpyAsync(ix->out_pin, ix->out_buf, status_off + sizeof(int), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
         ix->ws_ev_set = false;
         const int status = *reinterpret_cast<const int*>(ix->out_pin + status_off);

@@ -683,14 +683,17 @@ int multi_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_ki
     if (rc != B200R_OK) return rc;
 
     DeviceGuard dg(m->primary);
-    float* od = out_mem_kind == B200R_DEVICE ? D : reinterpret_cast<float*>(m->out_dev);
-    int64_t* oi = out_mem_kind == B200R_DEVICE ? I : reinterpret_cast<int64_t*>(m->out_dev + ids_off);
+    // small host results: the select kernel writes straight into the pinned host block (mapped memory)
+    const bool zc = out_mem_kind == B200R_HOST && kn.zero_copy_out != 0 && slot_bytes <= ((size_t)16 << 10);
+    uint8_t* stage = zc ? m->out_pin : m->out_dev;
+    float* od = out_mem_kind == B200R_DEVICE ? D : reinterpret_cast<float*>(stage);
+    int64_t* oi = out_mem_kind == B200R_DEVICE ? I : reinterpret_cast<int64_t*>(stage + ids_off);
     const int* seg_off = m->seg_off_dev;
     const int64_t* seg_ls = m->seg_tab_dev;
     const int64_t* seg_gb = m->seg_tab_dev + m->seg_tab_cap;
     // host results carry one more word: did every shard deliver (fused route)?
     const size_t status_off = (size_t)round_up64((int64_t)slot_bytes, 16);
-    int* status_dev = out_mem_kind == B200R_HOST ? reinterpret_cast<int*>(m->out_dev + status_off) : nullptr;
+    int* status_dev = out_mem_kind == B200R_HOST ? reinterpret_cast<int*>(stage + status_off) : nullptr;
     if (fused) {
         const size_t par = (size_t)(epoch & 1u) * kXchgParityBytes;
         CU(launch_merge_shards(ix->l2, m->xbuf + par, kXchgSlotBytes, kXchgIdOffset, G, (int)nq, k, k, seg_off, seg_ls,
@@ -704,7 +707,7 @@ int multi_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_ki
     if (timing) CU(cudaEventRecord(m->t1, fin));
     CU(cudaEventRecord(m->merge_ev, fin));
     if (out_mem_kind == B200R_HOST) {
-        CU(cudaMemcpyAsync(m->out_pin, m->out_dev, status_off + sizeof(int), cudaMemcpyDeviceToHost, fin));
+        if (!zc) CU(cudaMemcpyAsync(m->out_pin, m->out_dev, status_off + sizeof(int), cudaMemcpyDeviceToHost, fin));
         CU(cudaStreamSynchronize(fin));
         m->prev_async = false;
         const int status = *reinterpret_cast<const int*>(m->out_pin + status_off);

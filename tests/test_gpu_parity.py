@@ -611,6 +611,63 @@ def test_cross_stream_ordering(built_lib):
         ix.close()
 
 
+def test_adds_on_two_streams_with_growth(built_lib):
+    """Two device adds on different streams, the second one growing the buffer: the growth copies the rows the
+    first ingest kernel writes, so the second add must be ordered behind the first (it is: b200r_add waits for
+    the last writer's event before anything else).  Every row must be there afterwards."""
+    import torch
+
+    d = 1024
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    for rep in range(3):
+        ix = _mk("l2", d)  # no reserve_rows: the second add re-allocates
+        with torch.cuda.stream(s1):
+            a = torch.randn((300_000, d), device="cuda")
+            a = a * 1.0  # a few more kernels in front of the ingest on s1
+            ix.add(a)
+        with torch.cuda.stream(s2):
+            b = torch.randn((200_000, d), device="cuda")
+            ix.add(b)  # grows 300k -> 500k rows while the first ingest may still be running
+        host = torch.randn((1000, d)).numpy()
+        ix.add(host)   # and a host add on the index's own stream on top
+        assert ix.ntotal == 501_000
+        torch.cuda.synchronize()
+        ah, bh = a.cpu().numpy(), b.cpu().numpy()
+        keys = np.array([0, 1, 149_999, 299_999, 300_000, 300_001, 499_999, 500_000, 500_999], dtype=np.int64)
+        want = np.stack([ah[0], ah[1], ah[149_999], ah[299_999], bh[0], bh[1], bh[199_999], host[0], host[999]])
+        np.testing.assert_array_equal(ix.reconstruct_batch(keys), want)
+        D, I = ix.search(np.stack([ah[77], bh[77], host[77]]), 1)
+        assert I[:, 0].tolist() == [77, 300_077, 500_077] and (D[:, 0] == 0).all()
+        ix.close()
+
+
+def test_gemm_search_right_after_an_add_on_another_stream(built_lib):
+    """The GEMM route's containment check uses the largest row norm of the index, refreshed lazily by a small
+    kernel.  A search on one stream right after a device add of LARGE-norm rows on another stream must not compute
+    that maximum from norms the ingest kernel has not written yet (the search now waits for the last writer before
+    it enqueues anything)."""
+    import torch
+
+    d, n = 256, 200_000
+    side = torch.cuda.Stream()
+    for rep in range(3):
+        ix = _mk("ip", d, search_path=_lib.PATH_GEMM, reserve_rows=2 * n)
+        small = torch.randn((n, d), device="cuda") * 0.01
+        ix.add(small)
+        q = torch.randn((40, d), device="cuda")
+        ix.search(q, 10)  # the max-norm word now holds the small rows' maximum
+        with torch.cuda.stream(side):
+            big = torch.randn((n, d), device="cuda") * 30.0  # norms 3000x larger
+            big = big + 0.0
+            ix.add(big)
+        D, I = ix.search(q, 10)  # default stream: must be ordered behind the ingest on `side`
+        torch.cuda.synchronize()
+        x = np.concatenate([small.cpu().numpy(), big.cpu().numpy()])
+        _check("ip", D.cpu().numpy(), I.cpu().numpy(), q.cpu().numpy(), x, 10, "GEMM search after a side-stream add")
+        assert (I.cpu().numpy() >= n).all()  # every winner is one of the large rows
+        ix.close()
+
+
 # bf16 shadow of an fp32 corpus: the filter streams the shadow, the answers stay fp32-exact
 # ----------------------------------------------------------------------------------------
 @pytest.mark.parametrize("metric", ["ip", "l2"])
