@@ -849,6 +849,68 @@ def other_configs(args, world, rank, local_rank, n_dev, dev, dist, timed, errors
         del ix5, loc5
         torch.cuda.empty_cache()
 
+    # ---- C4 (--c4): 12.5M x 1024 bf16 rows per GPU (100M on 8), top-100, batch 1024; recall@100 vs fp32 truth -------
+    if args.c4:
+        n4 = 12_500_000 * n_gpus
+        lo, hi = shard_bounds(n4, world, rank)
+        if n_dev > 1:
+            ix4 = B200IndexFlat(DIM, METRIC_INNER_PRODUCT, devices=list(range(n_dev)), reserve_rows=n4, storage="bf16")
+            loc4 = ix4
+        else:
+            ix4 = ShardedFlatIndex(DIM, METRIC_INNER_PRODUCT, device=local_rank, reserve_rows=hi - lo, storage="bf16")
+            loc4 = ix4.local
+        g.manual_seed(synth.QUERY_SEED + 4)
+        q4 = torch.randn((1024, DIM), generator=g, device=dev)
+        xc = synth.corpus_chunk_device(300, min(CHUNK, n4), DIM, dev)
+        q4[::2] = xc[:512] + 0.3 * q4[::2] / DIM ** 0.5  # half of the queries near rows 0..511
+        del xc
+        q4 /= q4.norm(dim=1, keepdim=True)
+        n_truth = 64
+        tr = TruthTopK(q4[:n_truth], 100)  # on the fp32 ORIGINALS: the index stores them rounded to bf16
+        row = lo
+        while row < hi:
+            c = row // CHUNK
+            c_lo, c_hi = c * CHUNK, min((c + 1) * CHUNK, n4)
+            x = synth.corpus_chunk_device(300 + c, c_hi - c_lo, DIM, dev)
+            part = x[max(lo, c_lo) - c_lo: min(hi, c_hi) - c_lo]
+            loc4.add(part)
+            tr.update(part, max(lo, c_lo))
+            row = min(hi, c_hi)
+            del x, part
+        if n_dev <= 1:
+            ix4._sync_counts()
+        torch.cuda.synchronize()
+        _, It4 = tr.merged(world, dist)
+        res = {}
+
+        def c4_step(i):
+            res["r"] = ix4.search(q4, 100)
+
+        c4_step(0)
+        torch.cuda.synchronize()
+        I4 = res["r"][1][:n_truth].cpu().numpy()
+        hits = sum(len(set(a.tolist()) & set(b.tolist())) for a, b in zip(I4, It4))
+        recall = hits / float(n_truth * 100)
+        planted_ok = bool((res["r"][1][:1024:2, 0].cpu() == torch.arange(512)).all())
+        if recall < 0.95 or not planted_ok:
+            errors.append(f"C4: recall@100 {recall:.4f} vs fp32 truth (planted rows first: {planted_ok})")
+        parity["paths"].append({"path": "C4: bf16 corpus, recall@100 vs fp32 truth", "queries": n_truth,
+                                "ok": recall >= 0.95 and planted_ok})
+        parity["queries"] += n_truth
+        ms4, _ = timed(c4_step, 5, 2)
+        per = ms4 / 5
+        flops = 2.0 * 1024 * n4 * DIM
+        bf16_peak = _tensor_peaks()[1]
+        out["c4"] = {"workload": f"C4: {n4} x 1024 bf16 rows (25.6 GB per GPU), inner product, top-100, batch 1024",
+                     "value": 1024 * 1000.0 / per, "unit": "queries/s", "ms_per_batch": per, "steps": 5,
+                     "recall_at_100_vs_fp32_truth": recall, "recall_queries": n_truth,
+                     "achieved_tflops": flops / (per * 1e-3) / 1e12,
+                     "tensor_frac_bf16": flops / n_gpus / (per * 1e-3) / 1e12 / bf16_peak, "tensor_peak_tflops": bf16_peak,
+                     "gemm_fallbacks": loc4.stats()["n_gemm_fallbacks"]}
+        loc4.close() if hasattr(loc4, "close") else None
+        del ix4, loc4
+        torch.cuda.empty_cache()
+
     if n_gpus > 1 or rank != 0:
         return out
 
@@ -980,6 +1042,9 @@ if __name__ == "__main__":
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the secondary C1 / C2 / C5 lines")
     ap.add_argument("--c5-rows", type=int, default=5_000_000)
+    ap.add_argument("--c4", action="store_true",
+                    help="also run C4: 12.5M x 1024 bf16 rows per GPU (100M on 8 GPUs), top-100, batch 1024, with "
+                         "recall@100 against the fp32 truth of 64 queries")
     ap.add_argument("--cpu-sample-rows", type=int, default=0,
                     help="rows the CPU arm scans (0 = the full corpus when host RAM allows for --impl reference, "
                          "else 1M; scaled linearly to 10M rows and flagged `extrapolated`)")
