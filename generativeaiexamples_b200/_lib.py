@@ -11,7 +11,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200r.so")
+# (B200R_LIB: a developer override used by tools/ to compare two builds of the library; the product path is the in-tree file)
+LIB_PATH = os.environ.get("B200R_LIB") or os.path.join(_HERE, "libb200r.so")
 
 OK, E_INVALID, E_CUDA, E_UNSUPPORTED, E_NOMEM, E_IO = range(6)
 F32, BF16 = 0, 1

@@ -85,9 +85,11 @@ void reload_knobs() {
 }  // namespace b200r
 
 // corpus sizes from which small batches go to the GEMM path (measured crossovers with the device-side
-// fallback in place, tools/perf_small_nq.py / perf_bf16_small.py: 2..4 queries from ~110k x 1024 fp32 rows;
-// a single query on the bf16 shadow or on bf16 rows from ~250k / ~500k rows)
-constexpr int64_t kGemmSmallBatchBytes = 448ll << 20;
+// fallback in place, tools/perf_small_nq.py / perf_bf16_small.py).  2..4 queries: the four-rows-per-task scan
+// (round 2) matches the GEMM route up to ~1M x 1024 fp32 rows (0.60-0.66 ms against 0.62) and loses beyond
+// (4M rows: 2.7-2.85 ms against 2.4: it is bound by the SM clock, which drops under the power cap on long
+// launches), so the switch sits at 3 GB; a single query on the bf16 shadow or on bf16 rows from ~250k / ~500k rows
+constexpr int64_t kGemmSmallBatchBytes = 3072ll << 20;
 constexpr int64_t kGemmShadowSingleBytes = 1024ll << 20;
 constexpr int64_t kGemmBf16SmallBatchBytes = 64ll << 20;
 constexpr int64_t kGemmBf16SingleBytes = 1024ll << 20;

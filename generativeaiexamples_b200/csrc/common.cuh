@@ -90,6 +90,21 @@ __device__ __forceinline__ uint64_t policy_evict_first() {
     return p;
 }
 
+// Packed fp32 arithmetic (sm_100: FFMA2 / FADD2): two independent IEEE operations per instruction, the
+// same results as two scalar ones at half the issue slots.
+__device__ __forceinline__ void fma2(float& a0, float& a1, float x0, float x1, float y0, float y1) {
+    asm("{\n\t.reg .b64 ra, rx, ry;\n\tmov.b64 ra, {%0, %1};\n\tmov.b64 rx, {%2, %3};\n\tmov.b64 ry, {%4, %5};\n\t"
+        "fma.rn.f32x2 ra, rx, ry, ra;\n\tmov.b64 {%0, %1}, ra;\n\t}"
+        : "+f"(a0), "+f"(a1)
+        : "f"(x0), "f"(x1), "f"(y0), "f"(y1));
+}
+__device__ __forceinline__ void sub2(float& t0, float& t1, float a0, float a1, float b0, float b1) {
+    asm("{\n\t.reg .b64 ra, rx, ry;\n\tmov.b64 rx, {%2, %3};\n\tmov.b64 ry, {%4, %5};\n\t"
+        "sub.rn.f32x2 ra, rx, ry;\n\tmov.b64 {%0, %1}, ra;\n\t}"
+        : "=f"(t0), "=f"(t1)
+        : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
     v += __shfl_xor_sync(0xffffffffu, v, 16);
     v += __shfl_xor_sync(0xffffffffu, v, 8);

@@ -34,7 +34,10 @@ namespace b200r {
 // the HBM rate); the 64 accumulators of 4 rows x 4 queries need more registers, hence 8 warps.
 template <int NQ>
 struct ScanShape {
-    static constexpr int kConsumerWarps = NQ == 1 ? 16 : 8;
+#ifndef B200R_SCAN_NQ4_WARPS
+#define B200R_SCAN_NQ4_WARPS 8
+#endif
+    static constexpr int kConsumerWarps = NQ == 1 ? 16 : B200R_SCAN_NQ4_WARPS;
     static constexpr int kRowsPerTask = NQ == 1 ? 1 : 4;
     static constexpr int kThreads = 32 * (1 + kConsumerWarps);
 };
@@ -269,18 +272,17 @@ __global__ void __launch_bounds__(ScanShape<NQ>::kThreads, 1) scan_topk_kernel(c
                                                     x2 = __uint_as_float(xv.z), x3 = __uint_as_float(xv.w);
 #pragma unroll
                                         for (int qi = 0; qi < NQ; qi++) {
+                                            // packed fp32 (FFMA2 / FADD2): same IEEE results as the scalar code of the
+                                            // one-row path, half the issue slots -- these variants are issue-bound
                                             if (L2) {
-                                                const float t0 = qv[qi].x - x0, t1 = qv[qi].y - x1, t2 = qv[qi].z - x2,
-                                                            t3 = qv[qi].w - x3;
-                                                acc[rr][qi][0] = fmaf(t0, t0, acc[rr][qi][0]);
-                                                acc[rr][qi][1] = fmaf(t1, t1, acc[rr][qi][1]);
-                                                acc[rr][qi][2] = fmaf(t2, t2, acc[rr][qi][2]);
-                                                acc[rr][qi][3] = fmaf(t3, t3, acc[rr][qi][3]);
+                                                float t0, t1, t2, t3;
+                                                sub2(t0, t1, qv[qi].x, qv[qi].y, x0, x1);
+                                                sub2(t2, t3, qv[qi].z, qv[qi].w, x2, x3);
+                                                fma2(acc[rr][qi][0], acc[rr][qi][1], t0, t1, t0, t1);
+                                                fma2(acc[rr][qi][2], acc[rr][qi][3], t2, t3, t2, t3);
                                             } else {
-                                                acc[rr][qi][0] = fmaf(qv[qi].x, x0, acc[rr][qi][0]);
-                                                acc[rr][qi][1] = fmaf(qv[qi].y, x1, acc[rr][qi][1]);
-                                                acc[rr][qi][2] = fmaf(qv[qi].z, x2, acc[rr][qi][2]);
-                                                acc[rr][qi][3] = fmaf(qv[qi].w, x3, acc[rr][qi][3]);
+                                                fma2(acc[rr][qi][0], acc[rr][qi][1], qv[qi].x, qv[qi].y, x0, x1);
+                                                fma2(acc[rr][qi][2], acc[rr][qi][3], qv[qi].z, qv[qi].w, x2, x3);
                                             }
                                         }
                                     }
@@ -306,12 +308,14 @@ __global__ void __launch_bounds__(ScanShape<NQ>::kThreads, 1) scan_topk_kernel(c
 #pragma unroll
                                         for (int rr = 0; rr < RPW; rr++)
 #pragma unroll
-                                            for (int e = 0; e < 8; e++) {
+                                            for (int e = 0; e < 8; e += 2) {  // acc[e & 3] takes element e, then e + 4
                                                 if (L2) {
-                                                    const float tt = qq[e] - x[rr][e];
-                                                    acc[rr][qi][e & 3] = fmaf(tt, tt, acc[rr][qi][e & 3]);
+                                                    float t0, t1;
+                                                    sub2(t0, t1, qq[e], qq[e + 1], x[rr][e], x[rr][e + 1]);
+                                                    fma2(acc[rr][qi][e & 3], acc[rr][qi][(e & 3) + 1], t0, t1, t0, t1);
                                                 } else {
-                                                    acc[rr][qi][e & 3] = fmaf(qq[e], x[rr][e], acc[rr][qi][e & 3]);
+                                                    fma2(acc[rr][qi][e & 3], acc[rr][qi][(e & 3) + 1], qq[e], qq[e + 1],
+                                                         x[rr][e], x[rr][e + 1]);
                                                 }
                                             }
                                     }
@@ -319,13 +323,29 @@ __global__ void __launch_bounds__(ScanShape<NQ>::kThreads, 1) scan_topk_kernel(c
                             }
                         }
                     }
+                    // all RPW x NQ butterfly reductions advance together: one reduction is five DEPENDENT
+                    // shuffle + add steps (~30 cycles each), and done one after the other -- with a
+                    // data-dependent branch behind each -- they were two thirds of a task's time (ncu: the
+                    // FADDs behind the shuffles held 34 % of all stall samples)
+                    float scs[RPW][NQ];
+#pragma unroll
+                    for (int rr = 0; rr < RPW; rr++)
+#pragma unroll
+                        for (int qi = 0; qi < NQ; qi++)
+                            scs[rr][qi] = (acc[rr][qi][0] + acc[rr][qi][2]) + (acc[rr][qi][1] + acc[rr][qi][3]);
+#pragma unroll
+                    for (int o = 16; o >= 1; o >>= 1)
+#pragma unroll
+                        for (int rr = 0; rr < RPW; rr++)
+#pragma unroll
+                            for (int qi = 0; qi < NQ; qi++) scs[rr][qi] += __shfl_xor_sync(0xffffffffu, scs[rr][qi], o);
 #pragma unroll
                     for (int rr = 0; rr < RPW; rr++) {
                         if (rr < nr) {
                             const uint32_t row = (uint32_t)(row0 + r0 + rr);
 #pragma unroll
                             for (int qi = 0; qi < NQ; qi++) {
-                                const float sc = warp_sum((acc[rr][qi][0] + acc[rr][qi][2]) + (acc[rr][qi][1] + acc[rr][qi][3]));
+                                const float sc = scs[rr][qi];
                                 if (better_val<L2>(sc, top[qi].thr)) {  // row ids only grow: a tie never displaces
                                     if (lane == npend[qi]) {
                                         pend_v[qi] = sc;
