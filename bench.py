@@ -524,6 +524,10 @@ def main_gpu(args):
         parity["queries"] += POOL
         errors.extend(e)
 
+    # clocks and throttle reasons are sampled from here to the end of the batch-1 measurements: the parity gate
+    # runs the same searches as the timed regions (on 8 GPUs the device-timed region alone lasts ~15 ms, less than
+    # nvidia-smi needs to start), so every sample is taken under the load that is being measured
+    sampler = ClockSampler(local_rank) if rank == 0 else None
     check_batch1(index.search, "batch-1, device buffers", host=False)
     check_batch1(index.search, "batch-1, host buffers (e2e)", host=True)
     # the other exchange over the same shards (NCCL allgather + K4 when the fused NVLink exchange is the
@@ -547,7 +551,6 @@ def main_gpu(args):
             check_batch1(alt.search, "batch-1, " + alt_name + ", device buffers", host=False)
             check_batch1(alt.search, "batch-1, " + alt_name + ", host buffers", host=True)
 
-    sampler = ClockSampler(local_rank) if rank == 0 else None
     launches0 = local.stats()["n_kernel_launches"]
     ms_dev, _ = timed(dev_step, args.steps, args.warmup)
     launches = local.stats()["n_kernel_launches"] - launches0
@@ -566,6 +569,8 @@ def main_gpu(args):
     # (the sampler covers the device-timed region, the end-to-end region and the per-call latency loop: on 8 GPUs
     # the device-timed region alone is a few milliseconds, shorter than nvidia-smi's sampling period)
     clocks = sampler.stop() if sampler else None
+    if clocks is not None:
+        clocks["window"] = "parity gate + device-timed + end-to-end + per-call latency loop (batch-1 searches throughout)"
     alt_line = None
     if alt is not None:
         ms_f, _ = timed(lambda i: results.__setitem__("last_f", alt.search(Q[i % POOL: i % POOL + 1], TOPK)),

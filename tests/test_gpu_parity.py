@@ -1218,3 +1218,34 @@ def _mk_scan_result(metric, d, x, q, k):
     out = ix.search(q, k)
     ix.close()
     return out
+
+
+def test_route_query_and_exchange_status(built_lib):
+    """The two small helpers of the one-process-per-GPU form: b200r_auto_route answers for a shard of a given size
+    (every rank asks with the largest shard, so all of them pick the same exchange), b200r_exchange_status reads
+    and clears the "a peer did not deliver" word of an exchange buffer."""
+    import torch
+
+    ix = _mk("ip", 64)
+    ix.add(np.random.default_rng(0).standard_normal((1000, 64), dtype=np.float32))
+    route = ctypes.c_int32(-1)
+
+    def ask(nq, rows):
+        _lib.check(built_lib.b200r_auto_route(ix._h, nq, rows, ctypes.byref(route)))
+        return route.value
+
+    assert ask(1, -1) == _lib.PATH_SCAN and ask(4, -1) == _lib.PATH_SCAN and ask(5, -1) == _lib.PATH_GEMM
+    assert ask(3, 100_000_000) == _lib.PATH_GEMM and ask(1, 100_000_000) == _lib.PATH_SCAN
+    assert ask(64, 0) == _lib.PATH_SCAN  # an empty shard has nothing to multiply
+    nbytes = int(built_lib.b200r_exchange_buffer_bytes())
+    buf = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
+    status = ctypes.c_int32(-1)
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.check(built_lib.b200r_exchange_status(ctypes.c_void_p(buf.data_ptr()), 0, stream, ctypes.byref(status)))
+    assert status.value == 0
+    buf[-256:-252] = torch.tensor([3, 0, 0, 0], dtype=torch.uint8, device="cuda")  # "rank 2 never arrived"
+    _lib.check(built_lib.b200r_exchange_status(ctypes.c_void_p(buf.data_ptr()), 0, stream, ctypes.byref(status)))
+    assert status.value == 3
+    _lib.check(built_lib.b200r_exchange_status(ctypes.c_void_p(buf.data_ptr()), 0, stream, ctypes.byref(status)))
+    assert status.value == 0  # cleared by the previous call
+    ix.close()
