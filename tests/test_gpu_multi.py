@@ -220,3 +220,35 @@ def test_multi_routes_timing_and_errors(built_lib, devices, monkeypatch):
         ix.close()
     with pytest.raises(RuntimeError):
         B200IndexFlat(d, 1, devices=[0, 99])
+
+
+@pytest.mark.parametrize("devices", DEVICE_SETS[:3], ids=_ids)
+def test_multi_concurrent_callers(built_lib, devices):
+    """Searches from many threads on one multi-GPU index (the Morpheus pattern, faiss_vdb_service.py:169-174: B
+    executor threads with one query each) serialise inside the library and all return the right rows; a writer
+    between two waves of readers is seen by the second wave."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from generativeaiexamples_b200 import B200IndexFlat
+
+    rng = np.random.default_rng(41)
+    d = 256
+    x = rng.standard_normal((20000, d), dtype=np.float32)
+    ix = B200IndexFlat(d, 1, devices=devices)
+    ix.add(x[:15000])
+
+    def one(i):
+        D, I = ix.search(x[i: i + 1], 3)
+        return int(I[0, 0]), float(D[0, 0])
+
+    rows = rng.integers(0, 15000, 200).tolist()
+    with ThreadPoolExecutor(16) as ex:
+        got = list(ex.map(one, rows))
+    assert [g[0] for g in got] == rows and all(g[1] == 0.0 for g in got)
+    ix.add(x[15000:])
+    assert ix.remove_ids(np.arange(0, 100, dtype=np.int64)) == 100  # positions shift down by 100
+    rows = rng.integers(100, 20000, 200).tolist()
+    with ThreadPoolExecutor(16) as ex:
+        got = list(ex.map(one, rows))
+    assert [g[0] for g in got] == [r - 100 for r in rows] and all(g[1] == 0.0 for g in got)
+    ix.close()
