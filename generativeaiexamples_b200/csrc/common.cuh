@@ -395,6 +395,19 @@ struct WarpTopK {
         }
     }
 
+    // take over a stored sorted list (the inverse of store)
+    __device__ __forceinline__ void load(const Cand* src, int k_) {
+        const int lane = threadIdx.x & 31;
+        k = k_;
+#pragma unroll
+        for (int j = 0; j < KPL; j++) {
+            const Cand c = src[j * 32 + lane];
+            v[j] = c.v;
+            id[j] = c.id;
+        }
+        refresh_thr();
+    }
+
     __device__ __forceinline__ void store(Cand* dst) const {
         const int lane = threadIdx.x & 31;
 #pragma unroll
@@ -406,5 +419,45 @@ struct WarpTopK {
         }
     }
 };
+
+// Folds the n sorted lists of each of `nsets` independent sets (list l of set s at lists + s*set_stride + l*KPL*32,
+// shared memory) into list 0 of the set by pairwise bitonic merges: ceil(log2 n) rounds with a CTA barrier after
+// each, the pairs of a round spread over the warps -- instead of one warp folding the n lists one after the other
+// (a merge is ~14 dependent shuffles: 16 of them in a row were most of a CTA's epilogue).  Every thread of the CTA
+// must call it (barriers inside).
+template <int KPL, bool SMALL>
+__device__ __forceinline__ void tree_merge_lists(Cand* lists, int n, int nsets, size_t set_stride, int k) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    constexpr int KCAP = KPL * 32;
+    for (int step = 1; step < n; step <<= 1) {
+        const int pairs = (n + 2 * step - 1) / (2 * step);
+        for (int task = warp; task < nsets * pairs; task += nwarps) {
+            const int sidx = task / pairs, pi = task - sidx * pairs;
+            const int left = pi * 2 * step, right = left + step;
+            if (right < n) {
+                Cand* a = lists + (size_t)sidx * set_stride + (size_t)left * KCAP;
+                const Cand* b = lists + (size_t)sidx * set_stride + (size_t)right * KCAP;
+                WarpTopK<KPL, SMALL> m;
+                m.load(a, k);
+                float bv[KPL];
+                uint32_t bi[KPL];
+#pragma unroll
+                for (int j = 0; j < KPL; j++) {
+                    const Cand c = b[j * 32 + lane];
+                    bv[j] = c.v;
+                    bi[j] = c.id;
+                }
+                // a list whose best entry cannot enter changes nothing
+                const float head_v = __shfl_sync(0xffffffffu, bv[0], 0);
+                const uint32_t head_i = __shfl_sync(0xffffffffu, bi[0], 0);
+                if (head_i != kEmptyId && better<SMALL>(head_v, head_i, m.thr, m.thr_id)) {
+                    m.merge_sorted(bv, bi);
+                    m.store(a);
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
 
 }  // namespace b200r

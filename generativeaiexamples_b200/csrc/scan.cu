@@ -480,11 +480,13 @@ __global__ void __launch_bounds__(ScanShape<NQ>::kThreads, 1) scan_topk_kernel(c
         for (int qi = 0; qi < NQ; qi++) top[qi].store(sm_lists + ((size_t)qi * NCW + (warp - 1)) * KCAP);
     }
     __syncthreads();
+    // the NCW warp lists of every query fold into one by a tree of pairwise merges (log2 NCW rounds)
+    tree_merge_lists<KPL, L2>(sm_lists, NCW, NQ, (size_t)NCW * KCAP, p.k);
     if (warp < NQ) {
-        WarpTopK<KPL, L2> m;
-        m.init(p.k);
-        m.template merge_from<false>(sm_lists + (size_t)warp * NCW * KCAP, 0, NCW, 1, KCAP);
-        m.store(p.scratch + ((size_t)blockIdx.x * NQ + warp) * KCAP);
+        const Cand* src = sm_lists + (size_t)warp * NCW * KCAP;
+        Cand* dst = p.scratch + ((size_t)blockIdx.x * NQ + warp) * KCAP;
+#pragma unroll
+        for (int j = 0; j < KPL; j++) dst[j * 32 + lane] = src[j * 32 + lane];
     }
     __threadfence();
     __syncthreads();
@@ -506,11 +508,12 @@ __global__ void __launch_bounds__(ScanShape<NQ>::kThreads, 1) scan_topk_kernel(c
         m.store(sm_lists + ((size_t)qi * NW + warp) * KCAP);
     }
     __syncthreads();
-    // phase B: one warp per query folds the NW partial lists and writes the result
+    // phase B: the NW partial lists of every query fold into one (tree of pairwise merges); one warp per
+    // query writes the result
+    tree_merge_lists<KPL, L2>(sm_lists, NW, NQ, (size_t)NW * KCAP, p.k);
     if (warp < NQ && warp < nq_active) {
         WarpTopK<KPL, L2> m;
-        m.init(p.k);
-        m.template merge_from<false>(sm_lists + (size_t)warp * NW * KCAP, 0, NW, 1, KCAP);
+        m.load(sm_lists + (size_t)warp * NW * KCAP, p.k);
         if (FLAGGED || p.xchg_ntargets == 0) {
             // result row: the query's own position (flagged re-run) or its slot in this launch
             const size_t orow = FLAGGED ? (size_t)p.flag_list[grp * NQ + warp] : (size_t)warp;
