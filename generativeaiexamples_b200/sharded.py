@@ -109,13 +109,48 @@ class ShardedFlatIndex:
         self._sync_counts()
 
     def add(self, x) -> None:
-        """Every rank passes the same (n, d) matrix; rank r keeps its contiguous block.  Only
-        valid on an empty index or when appending would keep blocks contiguous per rank
-        (a growing corpus re-shards lazily: SURVEY.md section 7 "Mutable corpus")."""
-        if self.ntotal != 0:
-            raise NotImplementedError("add() after the first batch needs a re-shard; use add_local()")
-        lo, hi = shard_bounds(len(x), self.world, self.rank)
-        self.add_local(x[lo:hi])
+        """Every rank passes the same (n, d) matrix.  On an empty index rank r keeps its contiguous block; a later
+        batch is appended to the LAST rank's shard, which keeps the blocks contiguous in rank order, i.e. the new
+        rows get the positions ``ntotal ..`` exactly as faiss would give them (the shards drift out of balance as
+        such a corpus grows: the multi-GPU index inside one process, ``B200IndexFlat(devices=[...])``, levels its
+        shards on every add and is the form meant for an incrementally built corpus)."""
+        if self.ntotal == 0:
+            lo, hi = shard_bounds(len(x), self.world, self.rank)
+            self.add_local(x[lo:hi])
+        else:
+            self.add_local(x if self.rank == self.world - 1 else None)
+
+    def remove_ids(self, ids) -> int:
+        """faiss ``remove_ids`` on the sharded corpus (collective, same ``ids`` on every rank): each rank drops the
+        positions that fall into its block and compacts; the blocks stay contiguous in rank order, so later rows
+        shift down exactly as in faiss.  Returns the number of rows removed over all ranks."""
+        ids = np.unique(np.asarray(ids, dtype=np.int64).reshape(-1))
+        lo = self.id_base
+        mine = ids[(ids >= lo) & (ids < lo + self.local.ntotal)] - lo
+        before = self.ntotal
+        if mine.size:
+            self.local.remove_ids(mine)
+        self._sync_counts()
+        return before - self.ntotal
+
+    def reconstruct(self, key: int) -> np.ndarray:
+        """The stored row at global position ``key`` on every rank (collective: the owner sends it)."""
+        key = int(key)
+        if key < 0 or key >= self.ntotal:
+            raise RuntimeError(f"reconstruct: key {key} out of range [0, {self.ntotal})")
+        bases = np.cumsum([0] + self._counts)
+        owner = int(np.searchsorted(bases, key, side="right") - 1)
+        row = torch.zeros(self.d, dtype=torch.float32, device=self._buf_device())
+        if owner == self.rank:
+            row.copy_(torch.from_numpy(np.asarray(self.local.reconstruct(key - self.id_base), dtype=np.float32)))
+        if self.world > 1:
+            dist.broadcast(row, owner if self.group is None else dist.get_global_rank(self.group, owner),
+                           group=self.group)
+        return row.cpu().numpy()
+
+    def reset(self) -> None:
+        self.local.reset()
+        self._sync_counts()
 
     def _exchange(self):
         """Peer pointers of every rank's exchange buffer, or None (then NCCL is used)."""

@@ -32,6 +32,15 @@ class _LocalRef:
     def add(self, x):
         self.ix.add(np.asarray(x, dtype=np.float32))
 
+    def remove_ids(self, ids):
+        return self.ix.remove_ids(np.asarray(ids, dtype=np.int64))
+
+    def reconstruct(self, key):
+        return self.ix.reconstruct(int(key))
+
+    def reset(self):
+        self.ix.reset()
+
     def set_id_base(self, b):
         self.base = b
 
@@ -117,3 +126,55 @@ def test_single_process_world1():
     idx.add(x)
     D, I = idx.search(x[:2], 3)
     assert I[:, 0].tolist() == [0, 1] and idx.ntotal == 8
+
+
+def _mutating_worker(rank, world, port, q_out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle.flat_ref import IndexFlatRef
+
+        rng = np.random.default_rng(11)
+        d = 16
+        idx = ShardedFlatIndex(d, 1, local_index=_LocalRef(d, 1), merge_fn=_merge_ref)
+        ref = IndexFlatRef(d, 1)
+        log = []
+        for step in range(6):
+            x = rng.standard_normal((int(rng.integers(5, 60)), d)).astype(np.float32)
+            idx.add(x)          # the first batch is split into blocks, later ones go to the last rank
+            ref.add(x)
+            if step % 2:
+                ids = rng.integers(-2, ref.ntotal + 2, 9).astype(np.int64)
+                assert idx.remove_ids(ids) == ref.remove_ids(ids)
+            assert idx.ntotal == ref.ntotal
+            key = int(rng.integers(0, ref.ntotal))
+            np.testing.assert_array_equal(idx.reconstruct(key), ref.reconstruct(key))
+            q = rng.standard_normal((3, d)).astype(np.float32)
+            D, I = idx.search(q, 7)
+            Dr, Ir = ref.search(q, 7)
+            np.testing.assert_array_equal(I, Ir)
+            np.testing.assert_allclose(D, Dr, rtol=1e-6)
+            log.append(int(idx.ntotal))
+        idx.reset()
+        assert idx.ntotal == 0 and (idx.search(q, 2)[1] == -1).all()
+        if rank == 0:
+            q_out.put(log)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_index_is_mutable_like_faiss():
+    """add after the first batch, remove_ids, reconstruct and reset on the row-sharded index (world 3, gloo): ids
+    stay faiss positions -- later rows shift down on removal -- because the blocks stay contiguous in rank order."""
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_mutating_worker, args=(r, 3, port, out)) for r in range(3)]
+    for p in procs:
+        p.start()
+    log = out.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert len(log) == 6 and log[-1] > 0
