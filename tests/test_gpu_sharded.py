@@ -47,6 +47,13 @@ def _worker(rank, world, port, out, fused):
             res[(metric, "run")] = (np.concatenate([o[0].cpu().numpy() for o in outs]),
                                     np.concatenate([o[1].cpu().numpy() for o in outs]))
             res[(metric, "fused")] = idx._xchg is not None
+            # the corpus keeps growing and shrinking like one faiss index: a later batch (appended to the last
+            # rank), deletions across both blocks, then searches and a reconstruct on the new positions
+            extra = np.random.default_rng(12).standard_normal((777, d), dtype=np.float32)
+            idx.add(extra)
+            gone = np.array([0, 5, 24999, 25001, 50000, 50001 + 3, 50001 + 776, 10 ** 9], dtype=np.int64)
+            assert idx.remove_ids(gone) == 7 and idx.ntotal == n + 777 - 7
+            res[(metric, "mut")] = idx.search(q[:6], 10) + (idx.reconstruct(n + 100),)
         if rank == 0:
             out.put(res)
     finally:
@@ -85,4 +92,11 @@ def test_sharded_nccl_two_ranks(built_lib, fused):
         D, I = res[(metric, "run")]
         Dt, It = truth_topk("l2" if metric else "ip", q[:12], x, 18)
         assert_topk_parity(D, I, Dt, It, what="sharded back-to-back run")
+        D, I, row = res[(metric, "mut")]
+        extra = np.random.default_rng(12).standard_normal((777, 256), dtype=np.float32)
+        gone = [0, 5, 24999, 25001, 50000, 50001 + 3, 50001 + 776]
+        xm = np.delete(np.concatenate([x, extra]), gone, axis=0)
+        Dt, It = truth_topk("l2" if metric else "ip", q[:6], xm, 18)
+        assert_topk_parity(D, I, Dt, It, what="sharded index after add + remove_ids")
+        np.testing.assert_array_equal(row, xm[50001 + 100])
     assert res[(0, "fused")] == (fused == "1")
