@@ -109,6 +109,19 @@ def load():
     return lib
 
 
+_c_char, _addressof = ctypes.c_char, ctypes.addressof
+
+
+def addr(a) -> int:
+    """Address of a C-contiguous numpy array's data.  ``a.ctypes.data_as(c_void_p)`` costs ~3.9 us per array and a
+    host search passes three of them; going through the buffer protocol costs ~0.5 us.  Read-only and empty arrays
+    (which the buffer route refuses) take numpy's own accessor."""
+    try:
+        return _addressof(_c_char.from_buffer(a))
+    except (TypeError, ValueError):
+        return a.ctypes.data
+
+
 def check(rc):
     if rc != OK:
         msg = load().b200r_last_error()

@@ -106,7 +106,7 @@ class B200IndexFlat:
         n, d = x.shape
         assert d == self.d
         x = np.ascontiguousarray(x, dtype="float32")
-        _lib.check(self._L.b200r_add(self._h, x.ctypes.data_as(ctypes.c_void_p), n, _lib.F32, _lib.HOST, None))
+        _lib.check(self._L.b200r_add(self._h, _lib.addr(x), n, _lib.F32, _lib.HOST, None))
 
     # -- search ---------------------------------------------------------------
     def search(self, x, k: int, D=None, I=None):
@@ -137,6 +137,13 @@ class B200IndexFlat:
         assert d == self.d
         x = np.ascontiguousarray(x, dtype="float32")
         assert k > 0
+        if D is None and I is None:
+            # one allocation for both results (two views of it): numpy's per-array overhead is what is left of a
+            # small search's host time
+            ids_off = (n * k * 4 + 7) // 8 * 8
+            buf = np.empty(ids_off + n * k * 8, dtype=np.uint8)
+            D = np.frombuffer(buf, np.float32, n * k, 0).reshape(n, k)
+            I = np.frombuffer(buf, np.int64, n * k, ids_off).reshape(n, k)
         if D is None:
             D = np.empty((n, k), dtype=np.float32)
         else:
@@ -145,8 +152,8 @@ class B200IndexFlat:
             I = np.empty((n, k), dtype=np.int64)
         else:
             assert I.shape == (n, k)
-        _lib.check(self._L.b200r_search(self._h, x.ctypes.data_as(ctypes.c_void_p), n, k, _lib.HOST,
-                                        D.ctypes.data_as(ctypes.c_void_p), I.ctypes.data_as(ctypes.c_void_p),
+        _lib.check(self._L.b200r_search(self._h, _lib.addr(x), n, k, _lib.HOST,
+                                        _lib.addr(D), _lib.addr(I),
                                         _lib.HOST, None))
         return D, I
 
@@ -168,10 +175,10 @@ class B200IndexFlat:
         counts = np.empty(n, dtype=np.int32)
         oor = np.empty(n, dtype=np.int32)
         _lib.check(self._L.b200r_search_threshold(
-            self._h, x.ctypes.data_as(ctypes.c_void_p), n, k, self.RELEVANCE_KINDS[relevance],
+            self._h, _lib.addr(x), n, k, self.RELEVANCE_KINDS[relevance],
             0.0 if score_threshold is None else float(score_threshold), int(score_threshold is not None),
-            R.ctypes.data_as(ctypes.c_void_p), D.ctypes.data_as(ctypes.c_void_p), I.ctypes.data_as(ctypes.c_void_p),
-            counts.ctypes.data_as(ctypes.c_void_p), oor.ctypes.data_as(ctypes.c_void_p)))
+            _lib.addr(R), _lib.addr(D), _lib.addr(I),
+            _lib.addr(counts), _lib.addr(oor)))
         return R, D, I, counts, oor
 
     def mmr_select(self, query, keys, k: int, lambda_mult: float = 0.5) -> np.ndarray:
@@ -183,8 +190,8 @@ class B200IndexFlat:
         assert keys.ndim == 1 and k > 0
         sel = np.empty(k, dtype=np.int32)
         n_sel = ctypes.c_int32(0)
-        _lib.check(self._L.b200r_mmr(self._h, query.ctypes.data_as(ctypes.c_void_p), keys.ctypes.data_as(ctypes.c_void_p),
-                                     keys.size, k, float(lambda_mult), sel.ctypes.data_as(ctypes.c_void_p),
+        _lib.check(self._L.b200r_mmr(self._h, _lib.addr(query), _lib.addr(keys),
+                                     keys.size, k, float(lambda_mult), _lib.addr(sel),
                                      ctypes.byref(n_sel)))
         return sel[: n_sel.value].copy()
 
@@ -194,7 +201,7 @@ class B200IndexFlat:
         x = np.ascontiguousarray(x, dtype="int64")
         assert x.ndim == 1
         out = ctypes.c_int64()
-        _lib.check(self._L.b200r_remove_ids(self._h, x.ctypes.data_as(ctypes.c_void_p), x.size, ctypes.byref(out)))
+        _lib.check(self._L.b200r_remove_ids(self._h, _lib.addr(x), x.size, ctypes.byref(out)))
         return out.value
 
     def reconstruct(self, key: int, x: Optional[np.ndarray] = None) -> np.ndarray:
@@ -202,7 +209,7 @@ class B200IndexFlat:
             x = np.empty(self.d, dtype=np.float32)
         else:
             assert x.shape == (self.d,)
-        _lib.check(self._L.b200r_reconstruct(self._h, int(key), x.ctypes.data_as(ctypes.c_void_p)))
+        _lib.check(self._L.b200r_reconstruct(self._h, int(key), _lib.addr(x)))
         return x
 
     def reconstruct_batch(self, keys) -> np.ndarray:
@@ -210,8 +217,8 @@ class B200IndexFlat:
         keys = np.ascontiguousarray(keys, dtype="int64")
         assert keys.ndim == 1
         out = np.empty((keys.size, self.d), dtype=np.float32)
-        _lib.check(self._L.b200r_reconstruct_batch(self._h, keys.ctypes.data_as(ctypes.c_void_p), keys.size,
-                                                   out.ctypes.data_as(ctypes.c_void_p)))
+        _lib.check(self._L.b200r_reconstruct_batch(self._h, _lib.addr(keys), keys.size,
+                                                   _lib.addr(out)))
         return out
 
     def reset(self) -> None:
@@ -298,4 +305,4 @@ def normalize_L2(x, device: int = 0) -> None:
     if _is_torch(x):
         x = x.numpy()
     assert x.dtype == np.float32 and x.flags.c_contiguous and x.ndim == 2
-    _lib.check(L.b200r_normalize_l2(x.ctypes.data_as(ctypes.c_void_p), x.shape[0], x.shape[1], _lib.HOST, device, None))
+    _lib.check(L.b200r_normalize_l2(_lib.addr(x), x.shape[0], x.shape[1], _lib.HOST, device, None))
