@@ -82,7 +82,9 @@ typedef struct b200r_config {
                                   over the GPUs device_ids[0..n_devices) of this process (SURVEY.md section 8e:
                                   the reference's chain server is a single process,
                                   RAG/src/chain_server/server.py:203-238).  Rows keep faiss's "id == position"
-                                  contract; every entry point below works on such an index. */
+                                  contract; every entry point below works on such an index.  (A device may be
+                                  listed more than once -- every entry is one shard -- which is how the tests run
+                                  this code path on a 1-GPU box.) */
     int32_t device_ids[B200R_MAX_DEVICES];
 } b200r_config;
 
