@@ -1,0 +1,11 @@
+// Instances of the scan kernel (scan_kernel.cuh): <NQ=1, KPL=1>, <NQ=1, KPL=4>
+#include "scan_kernel.cuh"
+
+namespace b200r {
+cudaError_t scan_launch_1_1(const ScanParams& p, bool l2, bool bf16, int grid, size_t smem, cudaStream_t st, bool flagged) {
+    return launch_mk<1, 1>(p, l2, bf16, grid, smem, st, flagged);
+}
+cudaError_t scan_launch_1_4(const ScanParams& p, bool l2, bool bf16, int grid, size_t smem, cudaStream_t st, bool flagged) {
+    return launch_mk<1, 4>(p, l2, bf16, grid, smem, st, flagged);
+}
+}  // namespace b200r

@@ -119,7 +119,7 @@ except Exception:
         def get_relevant_documents(self, query: str, *, callbacks: Any = None, tags: Any = None,
                                    metadata: Any = None, run_name: Any = None, **kwargs: Any) -> List[Document]:
             handlers = list(callbacks) if isinstance(callbacks, (list, tuple)) else []
-            run_id = uuid.uuid4()
+            run_id = uuid.uuid4() if handlers else None  # (os.urandom costs ~3 us: only when somebody listens)
             for h in handlers:  # same hook names the OpenTelemetry handler implements
                 fn = getattr(h, "on_retriever_start", None)
                 if fn:
