@@ -627,14 +627,18 @@ class B200FlatVectorStore(_VSBase):
                              "if you trust the source of the file.")
         storage = kwargs.pop("storage", "f32")
         device = kwargs.pop("device", 0)
+        devices = kwargs.pop("devices", None)  # [0, 1, ...]: load straight into an index spread over those GPUs
+        if devices is None and os.getenv("B200R_DEVICES"):
+            devices = [int(t) for t in os.getenv("B200R_DEVICES").replace(" ", "").split(",") if t != ""]
         normalize = bool(kwargs.get("normalize_L2", False))
         index = B200IndexFlat.read(os.path.join(folder_path, f"{index_name}.faiss"), storage=storage, device=device,
-                                   normalize_on_add=normalize, normalize_queries=normalize)
+                                   devices=devices, normalize_on_add=normalize, normalize_queries=normalize)
         with open(os.path.join(folder_path, f"{index_name}.pkl"), "rb") as f:
             docstore, index_to_docstore_id = pickle.load(f)
         if "distance_strategy" not in kwargs and index.metric_type == METRIC_INNER_PRODUCT:
             kwargs["distance_strategy"] = DistanceStrategy.MAX_INNER_PRODUCT
-        return cls(embeddings, index, docstore, index_to_docstore_id, storage=storage, device=device, **kwargs)
+        return cls(embeddings, index, docstore, index_to_docstore_id, storage=storage, device=device, devices=devices,
+                   **kwargs)
 
 
 def _cosine_similarity(X: np.ndarray, Y: np.ndarray) -> np.ndarray:

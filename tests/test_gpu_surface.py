@@ -193,3 +193,28 @@ def test_mmr_on_device_matches_langchain(built_lib, devices, monkeypatch):
             .get_relevant_documents(q)
         want = ref.max_marginal_relevance_search_by_vector(_vec(q), k=5, fetch_k=30, lambda_mult=0.3)
         _same_docs(got, want)
+
+
+def test_save_local_load_local_across_gpu_layouts(built_lib, tmp_path, monkeypatch):
+    """FAISS.save_local / load_local (llm-prompt-design-helper/vector_store/faiss_vector_store.py:123-133): a store saved
+    from one GPU loads into an index spread over two shards and the other way round; answers and ids do not change."""
+    from generativeaiexamples_b200 import B200FlatVectorStore
+
+    monkeypatch.setenv("B200R_MULTI_MIN_PIECE", "16")
+    texts = [f"chunk {i}" for i in range(500)]
+    one = B200FlatVectorStore(Emb(), D_EMB)
+    one.add_texts(texts, [{"source": f"f{i % 3}.pdf"} for i in range(500)])
+    one.delete([one.index_to_docstore_id[7]])
+    one.save_local(str(tmp_path / "a"))
+    two = B200FlatVectorStore.load_local(str(tmp_path / "a"), Emb(), allow_dangerous_deserialization=True, devices=[0, 0])
+    assert two.index.stats()["n_devices"] == 2 and two.index.ntotal == 499
+    two.add_texts(["late chunk"])
+    two.save_local(str(tmp_path / "b"))
+    back = B200FlatVectorStore.load_local(str(tmp_path / "b"), Emb(), allow_dangerous_deserialization=True)
+    assert back.index.stats()["n_devices"] == 1 and back.index.ntotal == 500
+    one.add_texts(["late chunk"])
+    for q in ("about chunk 3", "late chunk", "chunk 7"):
+        want = [(d.page_content, float(s)) for d, s in one.similarity_search_with_score(q, k=5)]
+        for store in (two, back):
+            got = [(d.page_content, float(s)) for d, s in store.similarity_search_with_score(q, k=5)]
+            assert got == want, q
