@@ -518,7 +518,14 @@ static int multi_add_locked(b200r_index* ix, const void* x, int64_t n, int dtype
         } else {
             rc = leaf_add(s.leaf, src, piece[g], dtype, B200R_HOST, nullptr, allow_normalize);
         }
-        if (rc != B200R_OK) return rc;  // earlier pieces stay added: the map below only lists what succeeded
+        if (rc != B200R_OK) {
+            // earlier pieces stay added (a prefix of x): publish the map of what succeeded, then report
+            const std::string keep = last_error_cstr();
+            coalesce_segments(m);
+            m->st.n_rows_added += off;
+            upload_segments(m);
+            return fail(rc, "%s", keep.c_str());
+        }
         m->segs.push_back({g, before, piece[g]});
         m->ntotal += piece[g];
         off += piece[g];
@@ -632,7 +639,9 @@ int multi_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_ki
         }
     const size_t ids_off = (size_t)round_up64(nq * k * (int64_t)sizeof(float), 16);
     const size_t slot_bytes = ids_off + (size_t)nq * k * sizeof(int64_t);
-    const uint32_t epoch = fused ? ++m->epoch : 0;
+    // epochs are never 0 and alternate in parity (two are buffered): after 0xFFFFFFFF comes 2
+    if (fused) m->epoch = m->epoch == 0xFFFFFFFFu ? 2u : m->epoch + 1u;
+    const uint32_t epoch = fused ? m->epoch : 0;
     const bool timing = m->timing;
     const bool wait_prev = m->prev_async;
 
@@ -799,19 +808,27 @@ int multi_remove_ids(b200r_index* ix, const int64_t* ids, int64_t n, int64_t* n_
             return fail(B200R_E_CUDA, "shard removed %lld of %lld rows", (long long)got, (long long)local[g].size());
         return r;
     });
-    if (rc != B200R_OK) return rc;
+    // a shard that failed kept its rows: the map follows what each shard actually did, so the index
+    // stays consistent, and the error is reported after the map has been published
+    const std::string keep = rc != B200R_OK ? last_error_cstr() : "";
     std::vector<int64_t> shard_pos(m->G, 0);  // rows of each shard seen so far, after the removal
+    int64_t gone = 0;
     for (size_t i = 0; i < m->segs.size(); i++) {
         Segment& s = m->segs[i];
-        s.len -= seg_removed[i];
+        if (m->rc[s.shard] == B200R_OK) {
+            s.len -= seg_removed[i];
+            gone += seg_removed[i];
+        }
         s.lstart = shard_pos[s.shard];
         shard_pos[s.shard] += s.len;
     }
     coalesce_segments(m);
-    m->ntotal -= (int64_t)del.size();
-    m->st.n_rows_removed += (int64_t)del.size();
-    if (n_removed) *n_removed = (int64_t)del.size();
-    return upload_segments(m);
+    m->ntotal -= gone;
+    m->st.n_rows_removed += gone;
+    if (n_removed) *n_removed = gone;
+    const int up = upload_segments(m);
+    if (rc != B200R_OK) return fail(rc, "%s", keep.c_str());
+    return up;
 }
 
 int multi_reconstruct_batch(b200r_index* ix, const int64_t* keys, int64_t n, float* out) {

@@ -52,6 +52,12 @@ def _merge_on_device(metric, packed_all, nq, world, k_in, k_out, device_index, D
                                   ctypes.c_void_p(torch.cuda.current_stream(device_index).cuda_stream)))
 
 
+def _next_epoch(e: int) -> int:
+    """Exchange epochs are uint32, never 0, and alternate in parity (two epochs are buffered):
+    after 0xFFFFFFFF comes 2."""
+    return 2 if e >= 0xFFFFFFFF else e + 1
+
+
 class ShardedFlatIndex:
     """faiss-IndexFlat-shaped index whose rows are spread over the ranks of a process group."""
 
@@ -230,7 +236,7 @@ class ShardedFlatIndex:
                 qh = np.ascontiguousarray(q, dtype=np.float32)
                 D = np.empty((nq, k), dtype=np.float32)
                 I = np.empty((nq, k), dtype=np.int64)
-                self._epoch += 1
+                self._epoch = _next_epoch(self._epoch)
                 _lib.check(_lib.load().b200r_search_exchange(
                     self.local._h, qh.ctypes.data_as(ctypes.c_void_p), nq, k, _lib.HOST, xchg["ptrs"], self.world,
                     self.rank, self._epoch, D.ctypes.data_as(ctypes.c_void_p), I.ctypes.data_as(ctypes.c_void_p),
@@ -251,7 +257,7 @@ class ShardedFlatIndex:
             if xchg is not None:
                 # device caller: scan kernel -> NVLink stores into every rank's buffer -> waiting select kernel
                 qd = qd.contiguous().to(torch.float32)
-                self._epoch += 1
+                self._epoch = _next_epoch(self._epoch)
                 D = out[: nq * k * 4].view(torch.float32).view(nq, k)
                 I = out[d_bytes:].view(torch.int64).view(nq, k)
                 _lib.check(_lib.load().b200r_search_exchange(

@@ -229,8 +229,9 @@ int b200r_search_noalloc(const void* corpus, int64_t n_rows, int32_t dim, int32_
  * rank's buffer (NVLink stores) and raises a per-(epoch parity, rank) flag there; the select kernel
  * that follows on the same stream waits (bounded, ~2 s) for the `world` flags of this epoch in its
  * own buffer and writes the global top-k to the DEVICE arrays D / I.  All ranks must call it
- * collectively with the same nq, k and epoch; epoch starts at 1 and grows by 1 per call (two
- * epochs are buffered, which the stream order of scan -> select on every rank makes sufficient).
+ * collectively with the same nq, k and epoch; epoch starts at 1 and grows by 1 per call, and
+ * 0xFFFFFFFF is followed by 2 (never 0, parity alternates: two epochs are buffered, which the
+ * stream order of scan -> select on every rank makes sufficient).
  * q (nq, d) and D / I may each live on the host or the device, as for b200r_search; with device buffers
  * the call is asynchronous on `stream`, with host results it returns when they have arrived (one packed
  * copy) and fails if a peer's candidates did not show up within the bound. */

@@ -363,3 +363,19 @@ def test_morpheus_service_mirror(tmp_path):
             call()
     empty = B200VectorDBResourceService(B200FlatVectorStore(Emb(), None))
     assert asyncio.run(empty.similarity_search(embs[:2], k=3)) == [[], []]
+
+
+def test_exchange_epochs_never_zero_and_alternate():
+    """The fused exchange buffers two epochs by parity and treats 0 as "no wait": the uint32 counter must
+    skip 0 and keep alternating when it wraps."""
+    from generativeaiexamples_b200.sharded import _next_epoch
+
+    assert _next_epoch(0) == 1 and _next_epoch(1) == 2
+    e = 0xFFFFFFFE
+    seen = []
+    for _ in range(4):
+        e = _next_epoch(e)
+        seen.append(e)
+    assert seen == [0xFFFFFFFF, 2, 3, 4]
+    assert all(0 < v <= 0xFFFFFFFF for v in seen)
+    assert all((a ^ b) & 1 for a, b in zip(seen, seen[1:]))
