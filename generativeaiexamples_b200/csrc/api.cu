@@ -64,7 +64,6 @@ static void read_knobs_locked() {
     k.gemm_prefetch = (int)geti("B200R_GEMM_PREFETCH", 0);
     k.gemm_noselect = (int)geti("B200R_GEMM_DEBUG_NOSELECT", 0);
     k.gemm_warmup = (int)geti("B200R_GEMM_WARMUP", -1);
-    k.small_gemm = (int)geti("B200R_SMALL_GEMM", -1);
     k.multi_workers = (int)geti("B200R_MULTI_WORKERS", -1);
     k.multi_spin_us = (int)geti("B200R_MULTI_SPIN_US", 2000);
     k.multi_fused = (int)geti("B200R_MULTI_FUSED", -1);

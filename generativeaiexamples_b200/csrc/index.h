@@ -59,7 +59,6 @@ struct Knobs {
     int gemm_prefetch = 0;          // B200R_GEMM_PREFETCH
     int gemm_noselect = 0;          // B200R_GEMM_DEBUG_NOSELECT
     int gemm_warmup = -1;           // B200R_GEMM_WARMUP      (-1 = unset)
-    int small_gemm = -1;            // B200R_SMALL_GEMM       (-1 = default)
     int multi_workers = -1;         // B200R_MULTI_WORKERS    (-1 = default: on for >= 2 shards)
     int multi_spin_us = 2000;       // B200R_MULTI_SPIN_US    how long an idle shard worker polls before it sleeps
     int multi_fused = -1;           // B200R_MULTI_FUSED      (-1 = default)
