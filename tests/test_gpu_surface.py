@@ -218,3 +218,51 @@ def test_save_local_load_local_across_gpu_layouts(built_lib, tmp_path, monkeypat
         for store in (two, back):
             got = [(d.page_content, float(s)) for d, s in store.similarity_search_with_score(q, k=5)]
             assert got == want, q
+
+
+def test_direct_faiss_caller_flow_through_faiss_compat(built_lib, tmp_path):
+    """The RAGService path (community/chat-llama-nemotron/backend-rag/src/rag_service.py:88,190-197,289-301,
+    364-422) with ``import generativeaiexamples_b200.faiss_compat as faiss`` as its only change:
+    normalise -> add -> normalise the query -> search -> write_index -> read_index -> same answers;
+    checked against the faiss restatement (T1) fed the same normalised rows."""
+    import generativeaiexamples_b200.faiss_compat as faiss
+    from oracle.flat_ref import IndexFlatRef
+
+    rng = np.random.default_rng(77)
+    dim, n = 384, 5000
+    index = faiss.IndexFlatL2(dim)
+    embeddings = rng.standard_normal((n, dim)).astype("float32") * rng.uniform(0.2, 3.0, (n, 1)).astype("float32")
+    faiss.normalize_L2(embeddings)
+    assert np.allclose(np.linalg.norm(embeddings, axis=1), 1.0, atol=1e-5)
+    index.add(np.array(embeddings).astype("float32"))
+    assert index.ntotal == n and index.d == dim and index.is_trained
+
+    query_embedding = (embeddings[123] + 0.05 * rng.standard_normal(dim)).astype("float32")
+    faiss.normalize_L2(query_embedding.reshape(1, -1))
+    search_k = 5 * 3
+    distances, indices = index.search(np.array([query_embedding]).astype("float32"), search_k)
+    assert distances.shape == (1, search_k) and indices.dtype == np.int64 and indices[0, 0] == 123
+
+    ref = IndexFlatRef(dim, 1)
+    ref.add(embeddings)
+    Dr, Ir = ref.search(query_embedding.reshape(1, -1), search_k)
+    np.testing.assert_array_equal(indices, Ir)
+    np.testing.assert_allclose(distances, Dr, rtol=1e-5, atol=1e-5)
+
+    path = tmp_path / "faiss.index"
+    faiss.write_index(index, str(path))
+    with open(path, "rb") as f:
+        assert f.read(4) == b"IxF2"
+    again = faiss.read_index(str(path))
+    assert again.ntotal == n and again.d == dim
+    D2, I2 = again.search(np.array([query_embedding]).astype("float32"), search_k)
+    np.testing.assert_array_equal(I2, indices)
+    np.testing.assert_array_equal(D2, distances)
+    ip = faiss.IndexFlatIP(dim)
+    ip.add(embeddings)
+    Di, Ii = ip.search(query_embedding.reshape(1, -1), 3)
+    assert Ii[0, 0] == 123 and Di[0, 0] > Di[0, 1]
+    with pytest.raises(ValueError):
+        faiss.IndexFlat(dim, 23)
+    for ix in (index, again, ip):
+        ix.close()

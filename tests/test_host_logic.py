@@ -379,3 +379,14 @@ def test_exchange_epochs_never_zero_and_alternate():
     assert seen == [0xFFFFFFFF, 2, 3, 4]
     assert all(0 < v <= 0xFFFFFFFF for v in seen)
     assert all((a ^ b) & 1 for a, b in zip(seen, seen[1:]))
+
+
+def test_faiss_compat_exports_the_names_direct_callers_use():
+    """rag_service.py:88,194,376,399 -- module-level names only; nothing is created without a GPU."""
+    import generativeaiexamples_b200.faiss_compat as faiss
+
+    for name in ("IndexFlatL2", "IndexFlatIP", "IndexFlat", "normalize_L2", "write_index", "read_index"):
+        assert callable(getattr(faiss, name)), name
+    assert faiss.METRIC_L2 == 1 and faiss.METRIC_INNER_PRODUCT == 0
+    with pytest.raises(TypeError):
+        faiss.write_index(object(), "/nonexistent")
