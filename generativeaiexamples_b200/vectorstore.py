@@ -191,6 +191,10 @@ class InMemoryDocstore:
 
 _PACKERS: Dict[int, struct.Struct] = {}
 
+# distance strategy -> the engine's relevance function (b200r_search_threshold)
+_DEVICE_RELEVANCE_KINDS = {"EUCLIDEAN_DISTANCE": "EUCLIDEAN_DISTANCE", "COSINE": "COSINE",
+                           "MAX_INNER_PRODUCT": "MAX_INNER_PRODUCT"}
+
 
 def _pack_row(row) -> np.ndarray:
     """One Python list / tuple of floats -> float32 vector.  struct.pack converts C doubles to floats (round to
@@ -440,27 +444,29 @@ class B200FlatVectorStore(_VSBase):
         if (self.override_relevance_score_fn is not None or self._coalesce or self.index is None
                 or not hasattr(self.index, "search_threshold")):
             return None
-        kinds = {DistanceStrategy.EUCLIDEAN_DISTANCE: "EUCLIDEAN_DISTANCE", DistanceStrategy.COSINE: "COSINE",
-                 DistanceStrategy.MAX_INNER_PRODUCT: "MAX_INNER_PRODUCT"}
-        if self.distance_strategy not in kinds:
+        kind = _DEVICE_RELEVANCE_KINDS.get(self.distance_strategy)
+        if kind is None:
             return None
-        R, _, I, counts, oor = self.index.search_threshold(_to_matrix(self._embed_query(query)), k,
-                                                           kinds[self.distance_strategy], score_threshold)
+        R, _, I, counts, oor = self.index.search_threshold(_to_matrix(self._embed_query(query)), k, kind,
+                                                           score_threshold)
+        ids, rel = I[0].tolist(), R[0].tolist()  # one conversion each instead of a numpy scalar per hit
+        id_of, find = self.index_to_docstore_id, self.docstore.search
 
         def docs(lo, hi):
             out = []
             for j in range(lo, hi):
-                _id = self.index_to_docstore_id[int(I[0, j])]
-                doc = self.docstore.search(_id)
+                _id = id_of[ids[j]]
+                doc = find(_id)
                 if not isinstance(doc, Document):
                     raise ValueError(f"Could not find document for id {_id}, got {doc}")
-                out.append((doc, float(R[0, j])))
+                out.append((doc, rel[j]))
             return out
 
-        kept = docs(0, int(counts[0]))
+        n_kept = int(counts[0])
+        kept = docs(0, n_kept)
         if oor[0] > 0:  # LangChain's warning lists every hit, also the ones the threshold drops
-            n_valid = int((I[0] >= 0).sum())
-            warnings.warn(f"Relevance scores must be between 0 and 1, got {kept + docs(int(counts[0]), n_valid)}")
+            n_valid = sum(1 for v in ids if v >= 0)
+            warnings.warn(f"Relevance scores must be between 0 and 1, got {kept + docs(n_kept, n_valid)}")
         return kept
 
     def similarity_search_with_relevance_scores(self, query: str, k: int = 4,
