@@ -43,6 +43,20 @@ def dev_sync(i):
 
 
 rec["device_synced_us"] = wall(dev_sync)
+# query already on the device, results to the host: what the host-to-device copy of the query costs
+import ctypes
+Dh = np.empty((1, k), dtype=np.float32)
+Ih = np.empty((1, k), dtype=np.int64)
+L = _lib.load()
+
+
+def dev_q_host_out(i):
+    _lib.check(L.b200r_search(ix._h, ctypes.c_void_p(qd[i % 64: i % 64 + 1].data_ptr()), 1, k, _lib.DEVICE,
+                              _lib.addr(Dh), _lib.addr(Ih), _lib.HOST, None))
+
+
+torch.cuda.synchronize()
+rec["device_query_host_results_us"] = wall(dev_q_host_out)
 os.environ["B200R_ZERO_COPY_OUT"] = "0"
 _lib.reload_env()
 rec["host_search_with_d2h_copy_us"] = wall(lambda i: ix.search(q[i % 64: i % 64 + 1], k))
