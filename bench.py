@@ -382,6 +382,8 @@ def main_gpu(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
     n_dev = args.devices  # > 1: ONE process, the index spans the GPUs
+    if world == 1 and args.gpus > 1 and n_dev <= 1:
+        n_dev = args.gpus  # `python bench.py --gpus N` without torch.distributed.run: the one-process form
     if n_dev > 1 and world > 1:
         raise SystemExit("--devices is the single-process mode: do not combine it with torch.distributed.run")
     if n_dev > torch.cuda.device_count():
