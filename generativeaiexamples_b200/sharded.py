@@ -19,6 +19,7 @@ packing, gather layout -- runs without a GPU.
 from __future__ import annotations
 
 import ctypes
+import struct
 from typing import Callable, Optional
 
 import numpy as np
@@ -50,6 +51,22 @@ def _merge_on_device(metric, packed_all, nq, world, k_in, k_out, device_index, D
                                   block // 4, block // 8, k_out, ctypes.c_void_p(D.data_ptr()),
                                   ctypes.c_void_p(I.data_ptr()), device_index,
                                   ctypes.c_void_p(torch.cuda.current_stream(device_index).cuda_stream)))
+
+
+# faiss flat-index file: fourcc, d, ntotal, two unused int64, is_trained, metric_type, number of floats; rows follow
+_FAISS_FLAT_HEADER = struct.Struct("<4siqqqBiQ")
+
+
+def read_flat_header(path: str):
+    """(fourcc, d, ntotal, metric, offset of the first row) of an ``IxF2`` / ``IxFI`` / ``IxFl`` file."""
+    with open(path, "rb") as f:
+        head = f.read(_FAISS_FLAT_HEADER.size)
+    if len(head) != _FAISS_FLAT_HEADER.size:
+        raise RuntimeError(f"{path} is not a faiss flat index file")
+    fourcc, d, nt, _, _, _, metric, nfloats = _FAISS_FLAT_HEADER.unpack(head)
+    if fourcc not in (b"IxF2", b"IxFI", b"IxFl") or metric not in (0, 1) or d <= 0 or nt < 0 or nfloats != nt * d:
+        raise RuntimeError(f"{path} is not a faiss flat index file this engine reads (fourcc {fourcc!r}, metric {metric})")
+    return fourcc, d, nt, metric, _FAISS_FLAT_HEADER.size
 
 
 def _next_epoch(e: int) -> int:
@@ -157,6 +174,71 @@ class ShardedFlatIndex:
     def reset(self) -> None:
         self.local.reset()
         self._sync_counts()
+
+    # -- persistence (faiss.write_index / read_index on the sharded corpus) ------------------
+    def _barrier(self):
+        if self.world > 1:
+            t = torch.zeros(1, dtype=torch.int32, device=self._buf_device())
+            dist.all_reduce(t, group=self.group)
+            if t.is_cuda:
+                torch.cuda.current_stream(self.device).synchronize()
+
+    def _local_rows(self, lo: int, hi: int) -> np.ndarray:
+        """Local rows [lo, hi) as fp32 (bf16 storage is converted back, as b200r_save does)."""
+        if hasattr(self.local, "reconstruct_batch"):
+            return np.ascontiguousarray(self.local.reconstruct_batch(np.arange(lo, hi, dtype=np.int64)), dtype=np.float32)
+        return np.stack([np.asarray(self.local.reconstruct(i), dtype=np.float32) for i in range(lo, hi)]) \
+            if hi > lo else np.empty((0, self.d), dtype=np.float32)
+
+    def write(self, path: str, chunk_rows: int = 65536) -> None:
+        """``faiss.write_index`` for the whole sharded corpus (collective): ONE ``IxF2`` / ``IxFI`` file, the same
+        bytes a single index holding all the rows would write.  Rank 0 writes the header and sizes the file, then
+        every rank writes its block of rows at its own offset."""
+        path = str(path)
+        nt, row = self.ntotal, self.d * 4
+        if self.rank == 0:
+            with open(path, "wb") as f:
+                f.write(_FAISS_FLAT_HEADER.pack(b"IxF2" if self.metric_type == METRIC_L2 else b"IxFI", self.d, nt,
+                                                1 << 20, 1 << 20, 1, self.metric_type, nt * self.d))
+                f.truncate(_FAISS_FLAT_HEADER.size + nt * row)
+        self._barrier()
+        n_mine = int(self.local.ntotal)
+        with open(path, "r+b") as f:
+            f.seek(_FAISS_FLAT_HEADER.size + self.id_base * row)
+            for lo in range(0, n_mine, chunk_rows):
+                f.write(self._local_rows(lo, min(n_mine, lo + chunk_rows)).tobytes())
+            f.flush()
+            import os as _os
+
+            _os.fsync(f.fileno())
+        self._barrier()
+
+    def read_rows_from(self, path: str, chunk_rows: int = 65536) -> None:
+        """Append the rows of a faiss flat-index file to this (empty) sharded index (collective): rank r loads the
+        contiguous block ``shard_bounds(ntotal, world, r)`` straight from its offset in the file."""
+        if self.ntotal != 0:
+            raise RuntimeError("read_rows_from needs an empty index")
+        fourcc, d, nt, metric, offset = read_flat_header(str(path))
+        if d != self.d or metric != self.metric_type:
+            raise RuntimeError(f"{path}: d={d} metric={metric}, this index has d={self.d} metric={self.metric_type}")
+        lo, hi = shard_bounds(nt, self.world, self.rank)
+        for r0 in range(lo, hi, chunk_rows):
+            m = min(chunk_rows, hi - r0)
+            rows = np.fromfile(str(path), dtype=np.float32, count=m * d, offset=offset + r0 * d * 4)
+            if rows.size != m * d:
+                raise RuntimeError(f"{path} is truncated")
+            self.local.add(rows.reshape(m, d))
+        self._sync_counts()
+
+    @classmethod
+    def read(cls, path: str, *, group=None, device: Optional[int] = None, local_index_factory=None,
+             merge_fn: Optional[Callable] = None, **index_kw) -> "ShardedFlatIndex":
+        """``faiss.read_index`` into a sharded index (collective): d and the metric come from the file."""
+        _, d, _, metric, _ = read_flat_header(str(path))
+        local = local_index_factory(d, metric) if local_index_factory is not None else None
+        self = cls(d, metric, group=group, device=device, local_index=local, merge_fn=merge_fn, **index_kw)
+        self.read_rows_from(path)
+        return self
 
     def _exchange(self):
         """Peer pointers of every rank's exchange buffer, or None (then NCCL is used)."""

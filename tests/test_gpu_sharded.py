@@ -54,6 +54,23 @@ def _worker(rank, world, port, out, fused):
             gone = np.array([0, 5, 24999, 25001, 50000, 50001 + 3, 50001 + 776, 10 ** 9], dtype=np.int64)
             assert idx.remove_ids(gone) == 7 and idx.ntotal == n + 777 - 7
             res[(metric, "mut")] = idx.search(q[:6], 10) + (idx.reconstruct(n + 100),)
+            # one faiss file for the whole sharded corpus; loads back re-levelled over the ranks and, on rank 0,
+            # into a plain single-GPU index -- same answers either way
+            path = os.path.join(os.environ["B200R_TEST_TMP"], f"sharded_{metric}_{fused}.faiss")
+            idx.write(path)
+            again = ShardedFlatIndex.read(path, device=rank)
+            assert again.ntotal == idx.ntotal and again.metric_type == metric
+            Da, Ia = again.search(q[:6], 10)
+            np.testing.assert_array_equal(Ia, res[(metric, "mut")][1])
+            np.testing.assert_array_equal(Da, res[(metric, "mut")][0])
+            if rank == 0:
+                from generativeaiexamples_b200 import B200IndexFlat
+
+                one = B200IndexFlat.read(path, device=rank)
+                D1, I1 = one.search(q[:6], 10)
+                np.testing.assert_array_equal(I1, Ia)
+                np.testing.assert_array_equal(D1, Da)
+                one.close()
         if rank == 0:
             out.put(res)
     finally:
@@ -61,12 +78,13 @@ def _worker(rank, world, port, out, fused):
 
 
 @pytest.mark.parametrize("fused", ["0", "1"])
-def test_sharded_nccl_two_ranks(built_lib, fused):
+def test_sharded_nccl_two_ranks(built_lib, fused, tmp_path):
     import torch
     import torch.multiprocessing as mp
 
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
+    os.environ["B200R_TEST_TMP"] = str(tmp_path)
     from oracle import assert_topk_parity, truth_topk
 
     ctx = mp.get_context("spawn")

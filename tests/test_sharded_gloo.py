@@ -178,3 +178,59 @@ def test_sharded_index_is_mutable_like_faiss():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert len(log) == 6 and log[-1] > 0
+
+
+def _persist_worker(rank, world, port, path, q_out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(21)
+        d, n = 24, 517
+        x = rng.standard_normal((n, d), dtype=np.float32)
+        q = rng.standard_normal((4, d), dtype=np.float32)
+        idx = ShardedFlatIndex(d, 0, local_index=_LocalRef(d, 0), merge_fn=_merge_ref)
+        idx.add(x[:400])
+        idx.add(x[400:])          # a later batch: goes to the last rank, positions 400..516
+        idx.remove_ids([3, 250, 516])
+        idx.write(path, chunk_rows=100)
+        D0, I0 = idx.search(q, 7)
+        again = ShardedFlatIndex.read(path, local_index_factory=lambda d_, m_: _LocalRef(d_, m_), merge_fn=_merge_ref)
+        assert again.ntotal == n - 3 and again.d == d and again.metric_type == 0
+        lo, hi = shard_bounds(n - 3, world, rank)
+        assert again.local.ntotal == hi - lo and again.id_base == lo   # re-levelled on load
+        D1, I1 = again.search(q, 7)
+        np.testing.assert_array_equal(I0, I1)
+        np.testing.assert_array_equal(D0, D1)
+        with pytest.raises(RuntimeError):
+            again.read_rows_from(path)  # not empty
+        if rank == 0:
+            q_out.put("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_write_read_faiss_file(tmp_path):
+    """One faiss flat-index file for the whole sharded corpus: the bytes a single index would write, loadable
+    by any number of ranks (and by a single-GPU index)."""
+    import struct
+
+    world = 3
+    path = str(tmp_path / "sharded.faiss")
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_persist_worker, args=(r, world, port, path, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    assert out.get(timeout=120) == "ok"
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    rng = np.random.default_rng(21)
+    x = rng.standard_normal((517, 24), dtype=np.float32)
+    keep = np.delete(x, [3, 250, 516], axis=0)
+    raw = open(path, "rb").read()
+    head = struct.pack("<4siqqqBiQ", b"IxFI", 24, 514, 1 << 20, 1 << 20, 1, 0, 514 * 24)
+    assert raw[:45] == head
+    assert raw[45:] == keep.tobytes()
