@@ -54,6 +54,7 @@ class B200IndexFlat:
         self.metric_type = int(metric)
         self.is_trained = True
         self.storage = storage
+        self.normalize_on_add = bool(normalize_on_add)
         # devices=[0, 1, ...]: one index spread over several GPUs of this process (rows keep faiss's
         # "id == position" contract; see csrc/multi.cu).  self.device is then the primary GPU, the one
         # that CUDA tensors handed to add()/search() are expected on.
@@ -245,6 +246,7 @@ class B200IndexFlat:
         _lib.check(L.b200r_load(str(path).encode(), ctypes.byref(cfg), ctypes.byref(h)))
         self._h = h
         self.storage, self.device, self.is_trained = storage, self.devices[0], True
+        self.normalize_on_add = bool(kw.get("normalize_on_add", False))
         # d and metric come from the file: recover them through a zero-row probe
         st = self.stats()
         self.d, self.metric_type = _read_header(path)

@@ -213,11 +213,69 @@ class ShardedFlatIndex:
             _os.fsync(f.fileno())
         self._barrier()
 
+    def _verbatim_add_ok(self, what: str) -> None:
+        # rows that come back from a file or from another rank are already what the index stored; add() of an
+        # index that normalises on add would normalise them a second time (a last-bit change)
+        if getattr(self.local, "normalize_on_add", False):
+            raise RuntimeError(f"{what}: the local index normalises on add; stored rows must be re-added verbatim "
+                               "(create the sharded index with normalize_on_add=False for this)")
+
+    def rebalance(self) -> bool:
+        """Re-level the shards (collective).  Batches added after the first go to the last rank, so a corpus that
+        grows incrementally drifts out of balance; this moves rows between the ranks (point-to-point, NVLink under
+        NCCL) until rank r holds the block ``shard_bounds(ntotal, world, r)`` again.  Global positions do not change.
+        Returns whether anything moved."""
+        nt = self.ntotal
+        bases = [0]
+        for c in self._counts:
+            bases.append(bases[-1] + c)
+        target = [shard_bounds(nt, self.world, r) for r in range(self.world)]
+        if all(target[r] == (bases[r], bases[r + 1]) for r in range(self.world)):
+            return False
+        self._verbatim_add_ok("rebalance")
+        dev = self._buf_device()
+        my_lo, my_hi = bases[self.rank], bases[self.rank + 1]
+        new_lo, new_hi = target[self.rank]
+
+        def peer(r):
+            return r if self.group is None else dist.get_global_rank(self.group, r)
+
+        ops, keep_alive, pieces = [], [], {}
+        for t in range(self.world):  # what I hold of rank t's new block
+            lo, hi = max(my_lo, target[t][0]), min(my_hi, target[t][1])
+            if hi <= lo:
+                continue
+            rows = torch.from_numpy(self._local_rows(lo - my_lo, hi - my_lo)).to(dev)
+            if t == self.rank:
+                pieces[self.rank] = rows
+            else:
+                keep_alive.append(rows)
+                ops.append(dist.P2POp(dist.isend, rows, peer(t), group=self.group))
+        for s_ in range(self.world):  # what rank s_ holds of my new block
+            lo, hi = max(bases[s_], new_lo), min(bases[s_ + 1], new_hi)
+            if hi <= lo or s_ == self.rank:
+                continue
+            buf = torch.empty((hi - lo, self.d), dtype=torch.float32, device=dev)
+            pieces[s_] = buf
+            ops.append(dist.P2POp(dist.irecv, buf, peer(s_), group=self.group))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+            if dev.type == "cuda":
+                torch.cuda.current_stream(self.device).synchronize()
+        self.local.reset()
+        if pieces:
+            block = torch.cat([pieces[s_] for s_ in sorted(pieces)], dim=0)  # source ranks in order = global order
+            self.local.add(block if self._on_gpu else block.numpy())
+        self._sync_counts()
+        return True
+
     def read_rows_from(self, path: str, chunk_rows: int = 65536) -> None:
         """Append the rows of a faiss flat-index file to this (empty) sharded index (collective): rank r loads the
         contiguous block ``shard_bounds(ntotal, world, r)`` straight from its offset in the file."""
         if self.ntotal != 0:
             raise RuntimeError("read_rows_from needs an empty index")
+        self._verbatim_add_ok("read_rows_from")
         fourcc, d, nt, metric, offset = read_flat_header(str(path))
         if d != self.d or metric != self.metric_type:
             raise RuntimeError(f"{path}: d={d} metric={metric}, this index has d={self.d} metric={self.metric_type}")

@@ -71,6 +71,14 @@ def _worker(rank, world, port, out, fused):
                 np.testing.assert_array_equal(I1, Ia)
                 np.testing.assert_array_equal(D1, Da)
                 one.close()
+            # re-level the blocks (the later batch sits on the last rank): rows move over NCCL, positions stay
+            assert idx._counts[0] != idx._counts[1]
+            assert idx.rebalance() is True and abs(idx._counts[0] - idx._counts[1]) <= 1
+            Db, Ib = idx.search(q[:6], 10)
+            np.testing.assert_array_equal(Ib, res[(metric, "mut")][1])
+            np.testing.assert_array_equal(Db, res[(metric, "mut")][0])
+            np.testing.assert_array_equal(idx.reconstruct(n + 100), res[(metric, "mut")][2])
+            assert idx.rebalance() is False
         if rank == 0:
             out.put(res)
     finally:

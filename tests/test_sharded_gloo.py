@@ -234,3 +234,51 @@ def test_sharded_write_read_faiss_file(tmp_path):
     head = struct.pack("<4siqqqBiQ", b"IxFI", 24, 514, 1 << 20, 1 << 20, 1, 0, 514 * 24)
     assert raw[:45] == head
     assert raw[45:] == keep.tobytes()
+
+
+def _rebalance_worker(rank, world, port, q_out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(31)
+        d = 16
+        x = rng.standard_normal((900, d), dtype=np.float32)
+        q = rng.standard_normal((5, d), dtype=np.float32)
+        idx = ShardedFlatIndex(d, 1, local_index=_LocalRef(d, 1), merge_fn=_merge_ref)
+        idx.add(x[:90])
+        assert idx.rebalance() is False          # level already
+        for lo in range(90, 900, 90):            # nine later batches: all land on the last rank
+            idx.add(x[lo:lo + 90])
+        first_lo, first_hi = shard_bounds(90, world, world - 1)
+        assert idx._counts[-1] == (first_hi - first_lo) + 810 and idx.ntotal == 900
+        idx.remove_ids([0, 1, 2, 899])
+        D0, I0 = idx.search(q, 9)
+        rows0 = [idx.reconstruct(k_) for k_ in (0, 29, 30, 500, 895)]
+        assert idx.rebalance() is True
+        lo, hi = shard_bounds(896, world, rank)
+        assert idx.local.ntotal == hi - lo and idx.id_base == lo and idx.ntotal == 896
+        D1, I1 = idx.search(q, 9)
+        np.testing.assert_array_equal(I0, I1)   # positions did not change
+        np.testing.assert_array_equal(D0, D1)
+        for k_, r0 in zip((0, 29, 30, 500, 895), rows0):
+            np.testing.assert_array_equal(idx.reconstruct(k_), r0)
+        assert idx.rebalance() is False
+        if rank == 0:
+            q_out.put("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_rebalance_moves_rows_not_positions(world):
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_rebalance_worker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    assert out.get(timeout=120) == "ok"
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
