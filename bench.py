@@ -99,7 +99,7 @@ def _traffic():
 class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_power_cap,power.limit")
 
     def __init__(self, gpu_index: int):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
@@ -122,11 +122,16 @@ class ClockSampler:
         self.f.flush()
         rows = [r.strip().split(", ") for r in open(self.f.name) if r.strip()]
         os.unlink(self.f.name)
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, pl, reasons = [], [], [], [], set()
         for r in rows:
             try:
                 sm.append(float(r[1]))
                 mx.append(float(r[2]))
+                try:
+                    pw.append(float(r[3]))
+                    pl.append(float(r[8]))
+                except (ValueError, IndexError):
+                    pass
                 for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
                     if v.strip().lower().startswith("active"):
                         reasons.add(name)
@@ -135,6 +140,9 @@ class ClockSampler:
         if sm:
             sm.sort()
             out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        if pw and pl:
+            pw.sort()
+            out.update(power_w=pw[len(pw) // 2], power_limit_w=max(pl))
         return out
 
 
@@ -652,7 +660,9 @@ def main_gpu(args):
         parity["paths"].append({"path": "batch-256, device buffers", "queries": N_CHECK_256, "ok": not e})
         parity["queries"] += N_CHECK_256
         errors.extend(e)
+        s256 = ClockSampler(local_rank) if rank == 0 else None
         ms256, _ = timed(b256_step, args.batch256_steps, 3)
+        clocks256 = s256.stop() if s256 else None
         per = ms256 / args.batch256_steps
         flops = 2.0 * 256 * n_total * DIM
         tf32_peak, _, tf32_src = _tensor_peaks()
@@ -665,7 +675,8 @@ def main_gpu(args):
                 else "tcgen05 tf32 GEMM filter + exact fp32 re-score", "gemm_fallbacks": st_["n_gemm_fallbacks"],
                 "achieved_tflops": flops / (per * 1e-3) / 1e12,
                 "hbm_frac": (max_rows * DIM * 4 / (per * 1e-3) / 1e9) / peak,
-                "note": "crossover config (128 flop/B): both fractions reported; flops = 2*nq*N*d, bytes = N*d*4"}
+                "note": "crossover config (128 flop/B): both fractions reported; flops = 2*nq*N*d, bytes = N*d*4",
+                "clocks": clocks256}
         if use_shadow:
             # same batch, filter pass on the bf16 shadow of the rows; the fp32 re-score makes the answers identical
             local.set_shadow_filter(True)
