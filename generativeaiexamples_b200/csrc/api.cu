@@ -56,6 +56,7 @@ static void read_knobs_locked() {
     k.scan_stages = (int)geti("B200R_SCAN_STAGES", 0);
     k.scan_dynamic = (int)geti("B200R_SCAN_DYNAMIC", -1);
     k.scan_trace = (int)geti("B200R_SCAN_TRACE", 0);
+    k.scan_tile_block = (int)geti("B200R_SCAN_TILE_BLOCK", 1);
     k.zero_copy_out = (int)geti("B200R_ZERO_COPY_OUT", 1);
     k.gemm_kpcap = (int)geti("B200R_GEMM_KPCAP", 0);
     k.gemm_kprime = (int)geti("B200R_GEMM_KPRIME", 0);
@@ -647,6 +648,7 @@ int leaf_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kin
     // instead of the static walk.  Measured (tools/perf_scan_tail.py): it levels the CTAs' finishing times
     // (20 us spread -> 2 us on a 1.25M-row shard) but the stream as a whole gets 1-2 % slower, so it is off.
     p.tile_counter = kn.scan_dynamic == 1 ? ix->counter + 16 : nullptr;
+    p.tile_block = kn.scan_tile_block;
     p.id_base = ix->cfg.id_base;
     if (kn.scan_trace) {
         if (!ix->trace_dev) CU(cudaMalloc(&ix->trace_dev, 256 * 8 * sizeof(unsigned long long)));

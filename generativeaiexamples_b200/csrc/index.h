@@ -51,6 +51,7 @@ struct Knobs {
     int scan_stages = 0;            // B200R_SCAN_STAGES      (0 = default)
     int scan_dynamic = -1;          // B200R_SCAN_DYNAMIC     (-1 = default)
     int scan_trace = 0;             // B200R_SCAN_TRACE       1: per-CTA timestamps of every scan launch to stderr
+    int scan_tile_block = 1;        // B200R_SCAN_TILE_BLOCK  (consecutive tiles per CTA and round)
     int zero_copy_out = 1;          // B200R_ZERO_COPY_OUT    0: small host results also go through a device-to-host copy
     int gemm_kpcap = 0;             // B200R_GEMM_KPCAP       (0 = unset)
     int gemm_kprime = 0;            // B200R_GEMM_KPRIME      (0 = unset)

@@ -43,6 +43,7 @@ struct ScanParams {
     // dynamic tile assignment (tile_counter != null): CTAs draw tiles from a global counter instead of
     // walking t = blockIdx.x, +grid, ...; zero on entry, reset by the final writer
     unsigned* tile_counter;
+    int tile_block;            // static assignment: consecutive tiles per CTA and round (<= 1: cyclic)
 };
 
 // Exchange buffer of one rank (symmetric: same layout on every rank, peer-mapped over NVLink):

@@ -83,12 +83,18 @@ __global__ void __launch_bounds__(ScanShape<NQ>::kThreads, 1) scan_topk_kernel(c
     const int64_t n_tiles = p.n_tiles;
     const int R = p.rows_per_tile;
     // producer state (thread 0 only): the next tile of this CTA
-    int64_t t_next = blockIdx.x;
+    // static assignment: runs of tile_block consecutive tiles per CTA while whole rounds of grid * tile_block
+    // tiles remain, the rest dealt one by one (tile_block = 1: tile t -> CTA t mod grid)
+    int64_t t_next = 0;  // how many tiles this CTA has drawn
+    const int64_t tb = p.tile_block > 1 ? p.tile_block : 1;
+    const int64_t round_tiles = (int64_t)gridDim.x * tb;
+    const int64_t blocked_tiles = (n_tiles / round_tiles) * round_tiles;  // tiles covered by whole rounds
+    const int64_t blocked_mine = blocked_tiles / gridDim.x;              // of which this CTA's
     auto draw_tile = [&]() -> int64_t {
         if (dyn) return (int64_t)atomicAdd(p.tile_counter, 1u);
-        const int64_t t = t_next;
-        t_next += gridDim.x;
-        return t;
+        const int64_t i = t_next++;
+        if (i < blocked_mine) return (i / tb) * round_tiles + (int64_t)blockIdx.x * tb + (i % tb);
+        return blocked_tiles + (i - blocked_mine) * gridDim.x + blockIdx.x;
     };
     auto issue_tile = [&](int64_t t, uint64_t pol) {
         const uint8_t* g = reinterpret_cast<const uint8_t*>(p.corpus);
@@ -173,7 +179,7 @@ __global__ void __launch_bounds__(ScanShape<NQ>::kThreads, 1) scan_topk_kernel(c
         if (lane == 0) {
             const uint64_t pol = policy_evict_first();
             if (FLAGGED) {  // every group starts a fresh walk over the tiles
-                t_next = blockIdx.x;
+                t_next = 0;
                 pro_s = s;
                 pro_ph = ph;
                 prologue = 0;
