@@ -644,10 +644,13 @@ int leaf_search(b200r_index* ix, const void* q, int64_t nq, int k, int q_mem_kin
     if (kn.evict_first >= 0) p.evict_first = kn.evict_first;  // tuning knob
     p.scratch = ix->scratch;
     p.counter = ix->counter;
-    // B200R_SCAN_DYNAMIC=1: tiles are drawn from a global counter (second word group of the ticket buffer)
-    // instead of the static walk.  Measured (tools/perf_scan_tail.py): it levels the CTAs' finishing times
-    // (20 us spread -> 2 us on a 1.25M-row shard) but the stream as a whole gets 1-2 % slower, so it is off.
-    p.tile_counter = kn.scan_dynamic == 1 ? ix->counter + 16 : nullptr;
+    // Tile assignment (B200R_SCAN_DYNAMIC; tools/perf_scan_tail.py).  0: static, tile t -> CTA t mod grid.
+    // 1: every tile is drawn from a global counter (second word group of the ticket buffer): the CTAs finish
+    // within 2 us of each other instead of 20 (1.25M rows) .. 110 us (10M rows), but the stream itself gets
+    // 1.7 % slower on 10M rows.  2 (default): static for the first 7/8 of the tiles, the tail from the counter:
+    // levels the finish without the cost -- 1.25M rows 716 -> 706 us, 10M rows 5573 -> 5558 us.
+    p.tile_counter = scan_dynamic_mode() >= 1 ? ix->counter + 16 : nullptr;
+    p.dyn_from = -1;  // resolved by launch_scan once the tile count is known (scan_dynamic == 2: static head)
     p.tile_block = kn.scan_tile_block;
     p.id_base = ix->cfg.id_base;
     if (kn.scan_trace) {

@@ -49,7 +49,7 @@ struct Knobs {
     bool debug_fails = false;       // B200R_DEBUG_FAILS
     int scan_stage_kb = 0;          // B200R_SCAN_STAGE_KB    (0 = default)
     int scan_stages = 0;            // B200R_SCAN_STAGES      (0 = default)
-    int scan_dynamic = -1;          // B200R_SCAN_DYNAMIC     (-1 = default)
+    int scan_dynamic = -1;          // B200R_SCAN_DYNAMIC     (-1 = default = 2: static head, dynamic tail)
     int scan_trace = 0;             // B200R_SCAN_TRACE       1: per-CTA timestamps of every scan launch to stderr
     int scan_tile_block = 1;        // B200R_SCAN_TILE_BLOCK  (consecutive tiles per CTA and round)
     int zero_copy_out = 1;          // B200R_ZERO_COPY_OUT    0: small host results also go through a device-to-host copy
@@ -65,6 +65,7 @@ struct Knobs {
     int multi_fused = -1;           // B200R_MULTI_FUSED      (-1 = default)
 };
 const Knobs& knobs();
+inline int scan_dynamic_mode() { return knobs().scan_dynamic < 0 ? 2 : knobs().scan_dynamic; }
 void reload_knobs();
 
 // ---------------------------------------------------------------------------

@@ -44,6 +44,7 @@ struct ScanParams {
     // walking t = blockIdx.x, +grid, ...; zero on entry, reset by the final writer
     unsigned* tile_counter;
     int tile_block;            // static assignment: consecutive tiles per CTA and round (<= 1: cyclic)
+    long long dyn_from;        // with a tile counter: tiles below this index are dealt statically (0: all dynamic)
 };
 
 // Exchange buffer of one rank (symmetric: same layout on every rank, peer-mapped over NVLink):

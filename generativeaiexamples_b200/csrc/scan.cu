@@ -80,6 +80,16 @@ static cudaError_t launch_scan_impl(ScanParams p, int nq, bool l2, bool bf16, in
     p.rows_per_tile = R;
     p.n_tiles = (p.n_rows + R - 1) / R;
     p.nq_active = nq;
+    // mode 2 (the default) is for streams of many rounds; a corpus of a few rounds (L2-resident sizes, where a
+    // search costs tens of microseconds) keeps the static walk and pays for no counter round trips
+    if (p.tile_counter && scan_dynamic_mode() == 2 && p.n_tiles < 32ll * num_sms) p.tile_counter = nullptr;
+    if (p.tile_counter) {
+        // mode 2: the last eighth of the tiles (at least four rounds) is drawn dynamically
+        long long tail = p.n_tiles / 8;
+        const long long min_tail = 4ll * num_sms;
+        if (tail < min_tail) tail = min_tail;
+        p.dyn_from = scan_dynamic_mode() == 2 && p.n_tiles > tail ? p.n_tiles - tail : 0;
+    }
     int grid = (int)(p.n_tiles < num_sms ? p.n_tiles : num_sms);
     if (grid < 1) grid = 1;
     if (grid_out) *grid_out = grid;

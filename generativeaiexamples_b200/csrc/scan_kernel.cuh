@@ -56,8 +56,8 @@ __global__ void __launch_bounds__(ScanShape<NQ>::kThreads, 1) scan_topk_kernel(c
     uint64_t* empty_bar = full_bar + nst;
     __shared__ int s_is_last;
     // tile held by each stage (-1: the stream has ended).  With a global tile counter the CTAs draw
-    // tiles as they go, so the slowest SM no longer decides when the kernel ends; the producer tells
-    // the consumers which tile a stage holds through this array (written before the barrier arrive).
+    // (the tail of) their tiles as they go, so the slowest SM no longer decides when the kernel ends; the
+    // producer tells the consumers which tile a stage holds through this array (written before the arrive).
     __shared__ long long s_tile[kScanMaxStages];
     const bool dyn = !FLAGGED && p.tile_counter != nullptr;
     if (p.trace && threadIdx.x == 0) p.trace[blockIdx.x * 8 + 0] = global_ns();
@@ -90,8 +90,17 @@ __global__ void __launch_bounds__(ScanShape<NQ>::kThreads, 1) scan_topk_kernel(c
     const int64_t round_tiles = (int64_t)gridDim.x * tb;
     const int64_t blocked_tiles = (n_tiles / round_tiles) * round_tiles;  // tiles covered by whole rounds
     const int64_t blocked_mine = blocked_tiles / gridDim.x;              // of which this CTA's
+    // hybrid (dyn_from > 0): tiles below dyn_from are dealt statically (t mod grid), the tail is drawn from
+    // the counter, so the CTAs level out at the end without a counter round trip per tile before that
+    const int64_t dyn_from = dyn ? (p.dyn_from < n_tiles ? p.dyn_from : n_tiles) : 0;
     auto draw_tile = [&]() -> int64_t {
-        if (dyn) return (int64_t)atomicAdd(p.tile_counter, 1u);
+        if (dyn) {
+            if (dyn_from > 0) {
+                const int64_t t = (t_next++) * gridDim.x + blockIdx.x;
+                if (t < dyn_from) return t;
+            }
+            return dyn_from + (int64_t)atomicAdd(p.tile_counter, 1u);
+        }
         const int64_t i = t_next++;
         if (i < blocked_mine) return (i / tb) * round_tiles + (int64_t)blockIdx.x * tb + (i % tb);
         return blocked_tiles + (i - blocked_mine) * gridDim.x + blockIdx.x;

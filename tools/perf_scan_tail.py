@@ -33,8 +33,8 @@ def timed(reps=200, warm=20):
 
 
 ref = None
-for rnd in range(2):
-    for dyn in ("0", "1"):
+for rnd in range(3):
+    for dyn in ("0", "1", "2"):
         os.environ["B200R_SCAN_DYNAMIC"] = dyn
         _lib.reload_env()
         us = timed()
@@ -45,7 +45,7 @@ for rnd in range(2):
         assert torch.equal(I, ref[1]) and torch.equal(D, ref[0])
         print(json.dumps({"rows": n, "dynamic_tiles": dyn, "us_per_query": round(us, 1),
                           "GBps": round(n * 4096 / us / 1e3, 1)}), flush=True)
-for dyn in ("0", "1"):
+for dyn in ("0", "2"):
     os.environ["B200R_SCAN_DYNAMIC"] = dyn
     os.environ["B200R_SCAN_TRACE"] = "1"
     _lib.reload_env()
