@@ -334,7 +334,10 @@ class B200FlatVectorStore(_VSBase):
     def _hits(self, scores, indices, k: int, filter: Optional[Dict[str, Any]], kwargs: dict):
         out = []
         wanted = None
-        if filter is not None:
+        accept = None  # langchain-community >= 0.0.21 also takes a callable over the metadata
+        if callable(filter):
+            accept = filter
+        elif filter is not None:
             wanted = {key: (value if isinstance(value, list) else [value]) for key, value in filter.items()}
         for score, pos in zip(scores, indices):
             if pos == -1:  # fewer than k rows in the index
@@ -343,7 +346,10 @@ class B200FlatVectorStore(_VSBase):
             doc = self.docstore.search(_id)
             if not isinstance(doc, Document):
                 raise ValueError(f"Could not find document for id {_id}, got {doc}")
-            if wanted is None or all(doc.metadata.get(key) in value for key, value in wanted.items()):
+            if accept is not None:
+                if accept(doc.metadata):
+                    out.append((doc, score))
+            elif wanted is None or all(doc.metadata.get(key) in value for key, value in wanted.items()):
                 out.append((doc, score))
         score_threshold = kwargs.get("score_threshold")
         if score_threshold is not None:

@@ -96,6 +96,9 @@ def test_scores_filters_thresholds(metric, strategy):
     flt = {"source": "/tmp-data/uploaded_files/doc1.pdf"}
     _same(ours.similarity_search("chunk 3", k=3, filter=flt, fetch_k=30),
           ref.similarity_search("chunk 3", k=3, filter=flt, fetch_k=30))
+    # a callable over the metadata (langchain-community >= 0.0.21) selects the same documents as the dict form
+    _same(ours.similarity_search("chunk 3", k=3, filter=lambda md: md.get("source") == flt["source"], fetch_k=30),
+          ref.similarity_search("chunk 3", k=3, filter=flt, fetch_k=30))
     thr = 1.0 if metric == METRIC_L2 else 0.2
     a = ours.similarity_search_with_score_by_vector(Emb()._v("chunk 3"), k=10, score_threshold=thr)
     b = ref.similarity_search_with_score_by_vector(Emb()._v("chunk 3"), k=10, score_threshold=thr)
