@@ -507,7 +507,13 @@ class B200FlatVectorStore(_VSBase):
         scores, indices = self.index.search(_to_matrix(embedding), fetch_k if filter is None else fetch_k * 2)
         scores, indices = scores[0], indices[0]
         if filter is not None:
-            wanted = {key: (value if isinstance(value, list) else [value]) for key, value in filter.items()}
+            if callable(filter):
+                accept = filter
+            else:
+                wanted = {key: (value if isinstance(value, list) else [value]) for key, value in filter.items()}
+
+                def accept(md):
+                    return all(md.get(key) in value for key, value in wanted.items())
             keep = []
             for pos in indices:
                 if pos == -1:
@@ -515,7 +521,7 @@ class B200FlatVectorStore(_VSBase):
                 doc = self.docstore.search(self.index_to_docstore_id[int(pos)])
                 if not isinstance(doc, Document):
                     raise ValueError(f"Could not find document for id {self.index_to_docstore_id[int(pos)]}, got {doc}")
-                if all(doc.metadata.get(key) in value for key, value in wanted.items()):
+                if accept(doc.metadata):
                     keep.append(int(pos))
             order = {int(p_): j for j, p_ in enumerate(indices)}
             scores = np.array([scores[order[p_]] for p_ in keep], dtype=np.float32)
