@@ -1249,3 +1249,45 @@ def test_route_query_and_exchange_status(built_lib):
     _lib.check(built_lib.b200r_exchange_status(ctypes.c_void_p(buf.data_ptr()), 0, stream, ctypes.byref(status)))
     assert status.value == 0  # cleared by the previous call
     ix.close()
+
+
+def test_scan_tile_assignment_modes_agree(built_lib, monkeypatch):
+    """K2 deals its tiles statically (B200R_SCAN_DYNAMIC=0), from a global counter (1), or statically with a dynamic
+    tail (2, the default on corpora of >= 32 rounds of tiles): which CTA scores a row must never show in the answer.
+    350k x 256 fp32 rows = 5469 tiles of 64 rows over 148 CTAs, so mode 2 really draws its last rounds dynamically."""
+    import torch
+
+    from generativeaiexamples_b200 import _lib
+
+    dev = torch.device("cuda", 0)
+    n, d = 350_000, 256
+    g = torch.Generator(device=dev)
+    g.manual_seed(99)
+    x = torch.randn((n, d), generator=g, device=dev)
+    x[1000:1040] = x[7]          # exact duplicates: ties must go to the lowest id in every mode
+    q = torch.randn((4, d), generator=g, device=dev)
+    q[0] = x[7]
+    xh, qh = x.cpu().numpy(), q.cpu().numpy()
+    for metric in ("ip", "l2"):
+        ix = _mk(metric, d, search_path=_lib.PATH_SCAN, reserve_rows=n)
+        ix.add(x)
+        seen = {}
+        for mode in ("0", "1", "2", "0"):
+            monkeypatch.setenv("B200R_SCAN_DYNAMIC", mode)
+            _lib.reload_env()
+            for nq, k in ((1, 10), (1, 100), (4, 10), (3, 50), (1, 300)):
+                D, I = ix.search(q[:nq], k)
+                D, I = D.cpu().numpy(), I.cpu().numpy()
+                if (nq, k) in seen:
+                    np.testing.assert_array_equal(I, seen[(nq, k)][1], err_msg=f"{metric} mode {mode} nq={nq} k={k}")
+                    np.testing.assert_array_equal(D, seen[(nq, k)][0], err_msg=f"{metric} mode {mode} nq={nq} k={k}")
+                else:
+                    seen[(nq, k)] = (D, I)
+                    _check(metric, D, I, qh[:nq], xh, k, f"tile modes {metric} nq={nq} k={k}")
+            for rep in range(5):     # back to back: the counter is reset by every launch's final writer
+                D2, I2 = ix.search(q[:1], 10)
+                np.testing.assert_array_equal(I2.cpu().numpy(), seen[(1, 10)][1])
+        assert seen[(1, 10)][1][0, 0] == 7   # the duplicate with the lowest id
+        ix.close()
+    monkeypatch.delenv("B200R_SCAN_DYNAMIC", raising=False)
+    _lib.reload_env()
