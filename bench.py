@@ -800,8 +800,9 @@ def main_gpu(args):
                          "frac_of_ncu_dram_peak": achieved / ncu_peak, "ncu_dram_peak": ncu_peak,
                          "traffic": (algo_bytes * traffic["traffic_over_algorithmic"]) if traffic else None,
                          "traffic_source": ("ncu dram__bytes_read+write per launch = %.4f x algorithmic bytes, measured on a "
-                                            "2M-row shard (%s), scaled to this shard" %
-                                            (traffic["traffic_over_algorithmic"], traffic["source"])) if traffic else None,
+                                            "%d-row shard (%s), scaled to this shard" %
+                                            (traffic["traffic_over_algorithmic"], traffic.get("rows", 0),
+                                             traffic["source"])) if traffic else None,
                          "peak_source": peak_src,
                          "kernel": "scan_topk_kernel<1,1,IP,f32>", "kernel_ms": kernel_ms,
                          # what a step costs beyond its slowest scan launch: exchange over NVLink + final select (+ the
